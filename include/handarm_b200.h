@@ -1,0 +1,264 @@
+/*
+ * handarm_b200 -- C-ABI of the B200-native task-side hot path of the Isaac Gym
+ * hand / hand-arm environments.
+ *
+ * The reference (maltemosbach/isaacgym-hand-arm) has no FFI for this path: the
+ * boundary is the Python VecTask class contract (isaacgymenvs/tasks/base/
+ * vec_task.py:390-441 `step`, :378-388 the `pre_physics_step` /
+ * `post_physics_step` hooks).  This library is the engine behind a drop-in
+ * Python VecTask: each entry point replaces one Python hook of one task family
+ * and works directly on the tensors that hook works on.
+ *
+ * Conventions
+ *   - every pointer in a *Buffers struct is a DEVICE pointer, row-major, fp32
+ *     unless the field name / comment says otherwise; quaternions are xyzw;
+ *   - no allocation, no host synchronisation, stream-ordered, capturable in a
+ *     CUDA graph; the library never frees or retains caller memory;
+ *   - return value: 0 = ok, <0 = error (see ha_last_error());
+ *   - there is NO CPU fallback: without a CUDA device every compute entry
+ *     point fails with HA_ERR_CUDA.
+ */
+#ifndef HANDARM_B200_H
+#define HANDARM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HA_ABI_VERSION 1
+
+#define HA_OK 0
+#define HA_ERR_INVALID (-1)   /* bad argument / unsupported dimension */
+#define HA_ERR_CUDA (-2)      /* CUDA runtime error (message in ha_last_error) */
+#define HA_ERR_ALIGN (-3)     /* a pointer violates the alignment contract */
+
+#define HA_MAX_DOFS 48        /* two arms: 2 x (7 + 16) */
+#define HA_MAX_TIPS 8
+#define HA_MAX_KEYPOINTS 4
+#define HA_MAX_ARMS 2
+#define HA_ENVS_PER_CTA 32    /* env tile handled by one thread block */
+#define HA_STATS_LEN 16
+
+/* opaque CUDA stream handle (cudaStream_t); 0 = legacy default stream */
+typedef void* ha_stream_t;
+
+/* ------------------------------------------------------------------------ */
+/* AllegroKuka family (single arm: reorientation / regrasping / throw;       */
+/* two arms: regrasping / reorientation)                                     */
+/* replaces allegro_kuka_base.py:1355-1424 (pre_physics_step incl. reset_idx  */
+/* :1246-1353, reset_target_pose :1191-1196, reset_object_pose :1198-1224) and */
+/* :1426-1443 (post_physics_step: compute_observations :991-1089,             */
+/* compute_full_state :1091-1172, compute_kuka_reward :854-930) and the       */
+/* VecTask.step tail vec_task.py:424-432.                                     */
+/* ------------------------------------------------------------------------ */
+
+enum { HA_KUKA_REORIENTATION = 0, HA_KUKA_REGRASPING = 1, HA_KUKA_THROW = 2 };
+
+/* reward terms kept per episode, in the reference's key order
+ * (allegro_kuka_base.py:355-368) */
+enum {
+  HA_KUKA_RAW_FINGERTIP_DELTA = 0, HA_KUKA_RAW_HAND_DELTA, HA_KUKA_RAW_LIFTING, HA_KUKA_RAW_KEYPOINT,
+  HA_KUKA_FINGERTIP_DELTA, HA_KUKA_HAND_DELTA, HA_KUKA_LIFTING, HA_KUKA_LIFT_BONUS,
+  HA_KUKA_KEYPOINT, HA_KUKA_BONUS, HA_KUKA_KUKA_PENALTY, HA_KUKA_ALLEGRO_PENALTY,
+  HA_KUKA_N_EPISODE_TERMS
+};
+/* per-step terms exported as extras["episode_cumulative"]
+ * (allegro_kuka_base.py:912-927), same order as the reference's list */
+enum {
+  HA_KUKA_CUM_FINGERTIP_DELTA = 0, HA_KUKA_CUM_HAND_DELTA, HA_KUKA_CUM_LIFTING, HA_KUKA_CUM_LIFT_BONUS,
+  HA_KUKA_CUM_KEYPOINT, HA_KUKA_CUM_KUKA_PENALTY, HA_KUKA_CUM_ALLEGRO_PENALTY, HA_KUKA_CUM_BONUS,
+  HA_KUKA_N_STEP_TERMS
+};
+
+/* layout of one env's row of externally supplied random numbers (parity mode);
+ * raw U(0,1) / N(0,1) draws, in the order the reference consumes them
+ * (SURVEY.md appendix B).  Fast mode generates the same slots with Philox. */
+enum {
+  HA_KUKA_RND_GOAL_POS = 0,      /* 3: target position, goal-only reset        */
+  HA_KUKA_RND_GOAL_ROT = 3,      /* 3: target rotation uvw, goal-only reset    */
+  HA_KUKA_RND_RESET_GOAL_POS = 6,/* 3: target position inside reset_idx        */
+  HA_KUKA_RND_RESET_GOAL_ROT = 9,/* 3                                          */
+  HA_KUKA_RND_OBJ_POS = 12,      /* 3: object position noise                   */
+  HA_KUKA_RND_OBJ_ROT = 15,      /* 3: object rotation uvw                     */
+  HA_KUKA_RND_FORCE_PROB = 18,   /* 1                                          */
+  HA_KUKA_RND_FORCE_TEST = 19,   /* 1: Bernoulli test of the random force      */
+  HA_KUKA_RND_FORCE_NORMAL = 20, /* 3: N(0,1)                                  */
+  HA_KUKA_RND_SIDE = 23,         /* 2: two-arm coin flips (object side, goal side) */
+  HA_KUKA_RND_DOF_POS = 25,      /* n_dofs                                     */
+  /* HA_KUKA_RND_DOF_POS + n_dofs : n_dofs DOF velocity draws                   */
+};
+#define HA_KUKA_RND_STRIDE(n_dofs) (25 + 2 * (n_dofs))
+
+typedef struct HaKukaParams {
+  int32_t abi_version;
+  int32_t n_envs;
+  int32_t n_arms;           /* 1 or 2 */
+  int32_t n_dofs;           /* n_arms * 23 hand-arm DOFs that the task uses */
+  int32_t dofs_per_env;     /* row count per env of dof_state / targets (>= n_dofs) */
+  int32_t n_bodies;         /* rigid bodies per env */
+  int32_t n_tips;           /* fingertips, all arms (4 or 8) */
+  int32_t n_keypoints;      /* 1 or 4 */
+  int32_t obs_dim;          /* 117 single arm K=4; see ha_kuka_obs_dim() */
+  int32_t subtask;          /* HA_KUKA_* */
+  int32_t palm_body[HA_MAX_ARMS];
+  int32_t tip_body[HA_MAX_TIPS];
+  int32_t object_body;      /* rigid-body handle of the object (object_rb_handles[0]) */
+  int32_t max_episode_length;
+  int32_t max_consecutive_successes;
+  int32_t success_steps;
+  int32_t use_fast_rng;     /* 0: consume ext_rand, 1: in-kernel Philox */
+  int32_t force_enabled;    /* force_scale > 0 */
+  int32_t reserved_i[4];
+
+  float palm_offset[3];
+  float tip_offset[HA_MAX_TIPS][3];
+  float dof_lower[HA_MAX_DOFS];
+  float dof_upper[HA_MAX_DOFS];
+  float dof_default[HA_MAX_DOFS];
+  float dof_reset_noise[HA_MAX_DOFS];   /* 0.1 arm / 0.1 fingers coefficients */
+  float clamp_abs_obs;      /* <=0: no clamp; VecTask clip_obs already folded in (min) */
+  /* reward */
+  float lifting_bonus_threshold, lifting_bonus, lifting_rew_scale;
+  float keypoint_rew_scale, distance_delta_rew_scale, hand_delta_rew_scale /* = dist*0 */;
+  float bonus_per_step;     /* reach_goal_bonus / success_steps */
+  float kuka_actions_penalty_scale, allegro_actions_penalty_scale;
+  float fall_z;             /* 0.1 */
+  float far_tip_dist;       /* 1.5; reorientation `_extra_reset_rules` */
+  /* pre-physics */
+  float arm_action_gain;    /* dofSpeedScale * dt (relative control of the 7 arm DOFs) */
+  float act_moving_average, one_minus_act_moving_average;
+  float force_decay_pow;    /* force_decay ** (dt / force_decay_interval) */
+  float force_gain[2];      /* object mass, force_scale (applied in this order) */
+  float force_log_c0, force_log_c1; /* log(lo) - log(hi), log(hi) */
+  /* reset */
+  float target_min[3], target_size[3];      /* target volume */
+  float reset_pos_noise[3];
+  float reset_dof_vel_noise;
+  float two_arm_x_ofs;      /* two arms: +-x offset of object/goal sides */
+  float reserved_f[7];
+} HaKukaParams;
+
+/* values that change while training (tolerance curriculum); they live in
+ * device memory so that captured CUDA graphs see the updates */
+typedef struct HaKukaDynamic {
+  float keypoint_success_tolerance;  /* success_tolerance * keypoint_scale, rounded to fp32 */
+  float true_objective_scale;        /* true_objective = successes * scale + offset */
+  float true_objective_offset;
+  float pad0;
+  uint64_t rng_seed;
+  uint64_t rng_step;                 /* advanced by ha_kuka_pre_step when use_fast_rng */
+} HaKukaDynamic;
+
+typedef struct HaKukaBuffers {
+  /* ---- simulator-owned state (Isaac Gym layout, AoS) ---- */
+  float* root_state;          /* [n_envs*n_actors, 13] */
+  const float* rigid_body_state; /* [n_envs, n_bodies, 13] */
+  float* dof_state;           /* [n_envs, dofs_per_env, 2] */
+  /* ---- index tables ---- */
+  const int32_t* object_actor;   /* [n_envs] row of the object in root_state */
+  const int32_t* goal_actor;     /* [n_envs] row of the goal object (-1 if none) */
+  const int32_t* hand_actor;     /* [n_envs, n_arms] rows of the arm actors */
+  /* ---- task constants per env ---- */
+  const float* object_init_state;     /* [n_envs, 13] */
+  const float* object_keypoint_offsets; /* [n_envs, K, 3] */
+  const float* object_scales;         /* [n_envs, 3] */
+  const float* finger_rew_coeffs;     /* [n_envs, n_tips] */
+  /* ---- task state ---- */
+  float* goal_states;         /* [n_envs, 13] */
+  float* obs_buf;             /* [n_envs, obs_dim] */
+  float* rew_buf;             /* [n_envs] */
+  int64_t* reset_buf;         /* [n_envs] */
+  int64_t* reset_goal_buf;    /* [n_envs] */
+  int64_t* progress_buf;      /* [n_envs] */
+  int64_t* randomize_buf;     /* [n_envs] (nullable) */
+  uint8_t* timeout_buf;       /* [n_envs] bool */
+  float* successes;           /* [n_envs] */
+  float* prev_episode_successes;
+  float* true_objective;
+  float* prev_episode_true_objective;
+  int32_t* near_goal_steps;   /* [n_envs] */
+  uint8_t* lifted_object;     /* [n_envs] bool */
+  float* closest_keypoint_max_dist; /* [n_envs] */
+  float* closest_fingertip_dist;    /* [n_envs, n_tips] */
+  float* furthest_hand_dist;        /* [n_envs] (single arm only) */
+  float* rewards_episode;     /* [HA_KUKA_N_EPISODE_TERMS, n_envs] */
+  float* episode_cumulative;  /* [HA_KUKA_N_STEP_TERMS, n_envs] */
+  /* ---- control ---- */
+  float* prev_targets;        /* [n_envs, dofs_per_env] */
+  float* cur_targets;         /* [n_envs, dofs_per_env] */
+  float* actions;             /* [n_envs, n_dofs] task-owned copy */
+  float* rb_forces;           /* [n_envs, n_bodies, 3] */
+  float* random_force_prob;   /* [n_envs] */
+  /* ---- outputs for the simulator's *_indexed setters ---- */
+  int32_t* root_reset_indices;  /* [2*n_envs] ascending actor rows */
+  int32_t* hand_reset_indices;  /* [n_arms*n_envs] ascending actor rows */
+  int32_t* reset_counts;        /* [4]: n_root, n_hand, n_reset_envs, n_goal_resets */
+  /* ---- reductions ---- */
+  float* stats;                 /* [HA_STATS_LEN], see HA_KUKA_STAT_* */
+  float* scratch;               /* [ha_kuka_scratch_floats(n_envs)] */
+  uint32_t* tickets;            /* [8], zero-initialised once by the caller */
+  /* ---- dynamic scalars ---- */
+  HaKukaDynamic* dynamic;       /* device */
+} HaKukaBuffers;
+
+/* stats[] written by ha_kuka_post_step (sums over this GPU's env block) */
+enum {
+  HA_KUKA_STAT_N = 0,            /* n_envs */
+  HA_KUKA_STAT_SUM_REWARD,
+  HA_KUKA_STAT_SUM_RESETS,
+  HA_KUKA_STAT_SUM_SUCCESS_EVENTS,  /* is_success this step */
+  HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES,
+  HA_KUKA_STAT_SUM_TRUE_OBJECTIVE,
+  HA_KUKA_STAT_MAX_TRUE_OBJECTIVE,
+  HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE, /* -min, so one MAX all-reduce covers both */
+  HA_KUKA_STAT_SUM_TIMEOUTS,
+  HA_KUKA_STAT_SUM_LIFTED,
+  HA_KUKA_N_PARTIAL_STATS,          /* the entries above are per-rank partials (all-reduce SUM / MAX) */
+  HA_KUKA_STAT_MEAN_REWARD = HA_KUKA_N_PARTIAL_STATS,   /* derived on device for extras[] */
+  HA_KUKA_STAT_MEAN_PREV_EP_SUCCESSES,
+  HA_KUKA_STAT_MEAN_TRUE_OBJECTIVE,
+  HA_KUKA_STAT_MIN_TRUE_OBJECTIVE,
+  HA_KUKA_N_STATS
+};
+
+int ha_abi_version(void);
+const char* ha_last_error(void);
+size_t ha_sizeof_kuka_params(void);
+size_t ha_sizeof_kuka_buffers(void);
+size_t ha_sizeof_kuka_dynamic(void);
+
+/* obs row width for (n_arms, n_keypoints); allegro_kuka_base.py:185-220,
+ * allegro_kuka_two_arms.py:176-211 */
+int ha_kuka_obs_dim(int n_arms, int n_keypoints);
+/* algorithmic bytes per env-step, pre + post */
+size_t ha_kuka_bytes_per_env_step(const HaKukaParams* p);
+size_t ha_kuka_post_bytes_per_env_step(const HaKukaParams* p);
+size_t ha_kuka_pre_bytes_per_env_step(const HaKukaParams* p);
+size_t ha_kuka_scratch_floats(int n_envs);
+
+/* pre_physics_step: consume reset / reset_goal masks, reset scatter and
+ * re-randomisation, action -> DOF targets, random forces.
+ * actions: [n_envs, n_dofs] device, already clamped to +-clip_actions.
+ * ext_rand: [n_envs, HA_KUKA_RND_STRIDE(n_dofs)] device, or NULL iff use_fast_rng. */
+int ha_kuka_pre_step(const HaKukaParams* p, const HaKukaBuffers* b, const float* actions,
+                     const float* ext_rand, ha_stream_t stream);
+
+/* reset_idx outside of a step (VecTask.reset_done, vec_task.py:476-491; allegro_kuka_base.py:1246-1353):
+ * resets exactly the envs whose reset_buf is non-zero; no action / force / goal-only processing. */
+int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float* ext_rand, ha_stream_t stream);
+
+/* post_physics_step + VecTask.step tail: progress += 1, gather, keypoints,
+ * observations, reward, reset masks, episode accumulators, timeout, stats. */
+int ha_kuka_post_step(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream);
+
+/* compute_observations only (VecTask.reset(), vec_task.py:459-474): fills
+ * obs_buf from the current state without touching reward / reset state. */
+int ha_kuka_observe(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HANDARM_B200_H */

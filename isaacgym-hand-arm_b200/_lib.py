@@ -1,0 +1,153 @@
+"""ctypes binding of ``libhandarm_b200.so`` (C-ABI declared in ``include/handarm_b200.h``).
+
+The ctypes structures are generated from the header itself, so the Python side can never drift
+from the C side; struct sizes are cross-checked against ``ha_sizeof_*`` at load time.
+
+There is no fallback: if the shared library is missing or was built for a different ABI the import
+of the compute path raises ``HandArmLibraryError``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+from typing import Dict, List, Tuple
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+_REPO_DIR = os.path.dirname(_PKG_DIR)
+HEADER_PATH = os.path.join(_REPO_DIR, "include", "handarm_b200.h")
+LIB_PATH = os.path.join(_PKG_DIR, "libhandarm_b200.so")
+
+
+class HandArmLibraryError(RuntimeError):
+    pass
+
+
+class HandArmError(RuntimeError):
+    """Raised when a C-ABI call returns a negative status."""
+
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"handarm_b200 error {code}: {msg}")
+        self.code = code
+
+
+_CTYPES = {
+    "int32_t": ctypes.c_int32,
+    "uint32_t": ctypes.c_uint32,
+    "int64_t": ctypes.c_int64,
+    "uint64_t": ctypes.c_uint64,
+    "uint8_t": ctypes.c_uint8,
+    "float": ctypes.c_float,
+    "int": ctypes.c_int,
+    "size_t": ctypes.c_size_t,
+}
+
+
+def _strip_comments(src: str) -> str:
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return re.sub(r"//[^\n]*", "", src)
+
+
+def _parse_header(path: str):
+    src = _strip_comments(open(path).read())
+    consts: Dict[str, int] = {}
+    for m in re.finditer(r"#define\s+(HA_\w+)\s+\(?(-?\d+)\)?\s*$", src, flags=re.M):
+        consts[m.group(1)] = int(m.group(2))
+    # enums (anonymous): sequential values with optional "= n"
+    for m in re.finditer(r"enum\s*\{(.*?)\}\s*;", src, flags=re.S):
+        val = -1
+        for item in m.group(1).split(","):
+            item = item.strip()
+            if not item:
+                continue
+            if "=" in item:
+                name, expr = [t.strip() for t in item.split("=")]
+                val = int(eval(expr, {}, dict(consts)))
+            else:
+                name, val = item, val + 1
+            consts[name] = val
+    structs: Dict[str, List[Tuple[str, object]]] = {}
+    for m in re.finditer(r"typedef\s+struct\s+(\w+)\s*\{(.*?)\}\s*(\w+)\s*;", src, flags=re.S):
+        name, body = m.group(3), m.group(2)
+        fields: List[Tuple[str, object]] = []
+        for decl in body.split(";"):
+            decl = " ".join(decl.split())
+            if not decl:
+                continue
+            is_const = decl.startswith("const ")
+            if is_const:
+                decl = decl[len("const "):]
+            tname, rest = decl.split(" ", 1)
+            ptr = False
+            if tname.endswith("*"):
+                tname, ptr = tname[:-1], True
+            for var in rest.split(","):
+                var = var.strip()
+                vptr = ptr
+                while var.startswith("*"):
+                    var, vptr = var[1:].strip(), True
+                dims = [int(eval(d, {}, dict(consts))) for d in re.findall(r"\[([^\]]+)\]", var)]
+                var = var.split("[")[0].strip()
+                if vptr:
+                    ctype = ctypes.c_void_p
+                else:
+                    ctype = _CTYPES[tname] if tname in _CTYPES else structs_ctypes[tname]
+                for d in reversed(dims):
+                    ctype = ctype * d
+                fields.append((var, ctype))
+        cls = type(name, (ctypes.Structure,), {"_fields_": fields})
+        structs_ctypes[name] = cls
+        structs[name] = fields
+    return consts, structs_ctypes
+
+
+structs_ctypes: Dict[str, type] = {}
+CONSTS, STRUCTS = _parse_header(HEADER_PATH)
+
+HaKukaParams = STRUCTS["HaKukaParams"]
+HaKukaBuffers = STRUCTS["HaKukaBuffers"]
+HaKukaDynamic = STRUCTS["HaKukaDynamic"]
+
+_lib = None
+
+
+def exported_functions() -> List[str]:
+    """Names of every function the header declares (used by the CPU-side ABI test)."""
+    src = _strip_comments(open(HEADER_PATH).read())
+    return sorted(set(re.findall(r"\b(ha_\w+)\s*\(", src)) - {"ha_stream_t"})
+
+
+def load():
+    """Load the shared library (once). Fails loudly when it is absent or ABI-incompatible."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise HandArmLibraryError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C isaacgym-hand-arm_b200/csrc`). There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.ha_last_error.restype = ctypes.c_char_p
+    for fn in ("ha_sizeof_kuka_params", "ha_sizeof_kuka_buffers", "ha_sizeof_kuka_dynamic", "ha_kuka_bytes_per_env_step",
+               "ha_kuka_post_bytes_per_env_step", "ha_kuka_pre_bytes_per_env_step", "ha_kuka_scratch_floats"):
+        getattr(lib, fn).restype = ctypes.c_size_t
+    if lib.ha_abi_version() != CONSTS["HA_ABI_VERSION"]:
+        raise HandArmLibraryError(f"ABI mismatch: library {lib.ha_abi_version()} vs header {CONSTS['HA_ABI_VERSION']}")
+    for cls, fn in ((HaKukaParams, lib.ha_sizeof_kuka_params), (HaKukaBuffers, lib.ha_sizeof_kuka_buffers),
+                    (HaKukaDynamic, lib.ha_sizeof_kuka_dynamic)):
+        if ctypes.sizeof(cls) != fn():
+            raise HandArmLibraryError(f"struct {cls.__name__}: ctypes size {ctypes.sizeof(cls)} != C size {fn()}")
+    lib.ha_kuka_pre_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_kuka_post_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_kuka_observe.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_kuka_scratch_floats.argtypes = [ctypes.c_int]
+    lib.ha_kuka_obs_dim.argtypes = [ctypes.c_int, ctypes.c_int]
+    for fn in ("ha_kuka_bytes_per_env_step", "ha_kuka_post_bytes_per_env_step", "ha_kuka_pre_bytes_per_env_step"):
+        getattr(lib, fn).argtypes = [ctypes.c_void_p]
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise HandArmError(rc, load().ha_last_error().decode())

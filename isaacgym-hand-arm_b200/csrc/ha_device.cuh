@@ -1,0 +1,128 @@
+// Device-side building blocks shared by the task kernels (sm_100a).
+//
+// Arithmetic contract: this translation unit is compiled with -fmad=false and
+// every helper spells out the association order of the reference's eager
+// PyTorch ops (isaacgymenvs/utils/torch_jit_utils.py), so +,-,*,/ and sqrt are
+// bit-identical to the CPU reference; only transcendental functions (log, exp,
+// sin, cos) may differ in the last ulp.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ha {
+
+constexpr int kEnvsPerCta = 32;   // == HA_ENVS_PER_CTA
+constexpr int kThreads = 128;     // 4 warps: lane = env in tile, warp = work part
+
+struct f3 { float x, y, z; };
+struct f4 { float x, y, z, w; };   // quaternion xyzw
+
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+
+// torch_jit_utils.py:80-90 quat_rotate:  a = v*(2w^2-1);  b = cross(q,v)*w*2;
+// c = q*(q.v)*2;  a+b+c
+__device__ __forceinline__ f3 quat_rotate(f4 q, f3 v) {
+  const float s = 2.0f * (q.w * q.w) - 1.0f;
+  const f3 a = {v.x * s, v.y * s, v.z * s};
+  const f3 cr = {q.y * v.z - q.z * v.y, q.z * v.x - q.x * v.z, q.x * v.y - q.y * v.x};
+  const f3 b = {cr.x * q.w * 2.0f, cr.y * q.w * 2.0f, cr.z * q.w * 2.0f};
+  const float d = q.x * v.x + q.y * v.y + q.z * v.z;
+  const f3 c = {q.x * d * 2.0f, q.y * d * 2.0f, q.z * d * 2.0f};
+  return {a.x + b.x + c.x, a.y + b.y + c.y, a.z + b.z + c.z};
+}
+
+// torch_jit_utils.py:41-62 quat_mul (8-multiply factored form)
+__device__ __forceinline__ f4 quat_mul(f4 a, f4 b) {
+  const float ww = (a.z + a.x) * (b.x + b.y);
+  const float yy = (a.w - a.y) * (b.w + b.z);
+  const float zz = (a.w + a.y) * (b.w - b.z);
+  const float xx = ww + yy + zz;
+  const float qq = 0.5f * (xx + (a.z - a.x) * (b.x - b.y));
+  f4 r;
+  r.w = qq - ww + (a.z - a.y) * (b.y - b.z);
+  r.x = qq - xx + (a.x + a.w) * (b.x + b.w);
+  r.y = qq - yy + (a.w - a.x) * (b.y + b.z);
+  r.z = qq - zz + (a.z + a.y) * (b.w - b.x);
+  return r;
+}
+
+// torch_jit_utils.py:106-110
+__device__ __forceinline__ f4 quat_conjugate(f4 a) { return {-a.x, -a.y, -a.z, a.w}; }
+
+__device__ __forceinline__ float norm3(f3 v) { return sqrtf(v.x * v.x + v.y * v.y + v.z * v.z); }
+
+// torch_jit_utils.py:233-240
+__device__ __forceinline__ float scale_to(float x, float lo, float hi) { return 0.5f * (x + 1.0f) * (hi - lo) + lo; }
+__device__ __forceinline__ float unscale_from(float x, float lo, float hi) { return (2.0f * x - hi - lo) / (hi - lo); }
+// torch_jit_utils.py:228-230 tensor_clamp = max(min(t, hi), lo)
+__device__ __forceinline__ float clamp_to(float t, float lo, float hi) { return fmaxf(fminf(t, hi), lo); }
+// torch.clip(x, lo, hi) = min(max(x, lo), hi)
+__device__ __forceinline__ float clipf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// get_random_quat (allegro_kuka_base.py:1178-1189): uniform SO(3) from 3 uniforms
+__device__ __forceinline__ f4 random_quat(float u, float v, float w) {
+  const float two_pi = 6.2831854820251465f;  // float32(2*pi)
+  const float s1 = sqrtf(1.0f - u), s2 = sqrtf(u);
+  f4 q;
+  q.w = s1 * sinf(two_pi * v);
+  q.x = s1 * cosf(two_pi * v);
+  q.y = s2 * sinf(two_pi * w);
+  q.z = s2 * cosf(two_pi * w);
+  return q;
+}
+
+// ---------------------------------------------------------------------------
+// Philox4x32-10 counter-based RNG (fast mode): value = f(seed, step, env, slot)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+
+__device__ __forceinline__ float u32_to_unit(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-08f; }  // [0,1)
+
+struct Rng {
+  uint64_t seed, step;
+  // uniform [0,1) for (env, slot)
+  __device__ __forceinline__ float uniform(int env, int slot) const {
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)env, (uint32_t)(slot >> 2), (uint32_t)step, (uint32_t)(step >> 32)),
+                                  make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    const int c = slot & 3;
+    return u32_to_unit(c == 0 ? r.x : c == 1 ? r.y : c == 2 ? r.z : r.w);
+  }
+  // standard normal for (env, slot): Box-Muller over an independent counter block
+  __device__ __forceinline__ float normal(int env, int slot) const {
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)env, 0x80000000u | (uint32_t)(slot >> 1), (uint32_t)step, (uint32_t)(step >> 32)),
+                                  make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    const float u1 = 1.0f - u32_to_unit((slot & 1) ? r.z : r.x);  // (0,1]
+    const float u2 = u32_to_unit((slot & 1) ? r.w : r.y);
+    return sqrtf(-2.0f * logf(u1)) * cosf(6.2831854820251465f * u2);
+  }
+};
+
+// ---------------------------------------------------------------------------
+// warp / block reductions in a fixed order (deterministic)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float ldg(const float* p) { return __ldg(p); }
+
+}  // namespace ha

@@ -1,0 +1,132 @@
+// C-ABI entry points of the AllegroKuka family (see include/handarm_b200.h).
+#include <cuda_runtime.h>
+
+#include "../../include/handarm_b200.h"
+#include "ha_host.h"
+#include "ha_kuka_post.cuh"
+#include "ha_kuka_pre.cuh"
+
+namespace {
+
+int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
+  HA_REQUIRE(p != nullptr && b != nullptr, "null params / buffers");
+  HA_REQUIRE(p->abi_version == HA_ABI_VERSION, "HaKukaParams.abi_version %d != %d", p->abi_version, HA_ABI_VERSION);
+  HA_REQUIRE(p->n_envs > 0, "n_envs must be positive (got %d)", p->n_envs);
+  HA_REQUIRE(p->n_arms == 1, "n_arms=%d: only the single-arm kernels are built into this entry point", p->n_arms);
+  HA_REQUIRE(p->n_dofs == 23 && p->dofs_per_env == 23, "single-arm AllegroKuka needs n_dofs == dofs_per_env == 23 (got %d/%d)",
+             p->n_dofs, p->dofs_per_env);
+  HA_REQUIRE(p->n_tips == 4, "n_tips must be 4 (got %d)", p->n_tips);
+  HA_REQUIRE(p->n_keypoints == 1 || p->n_keypoints == 4, "n_keypoints must be 1 or 4 (got %d)", p->n_keypoints);
+  HA_REQUIRE(p->obs_dim == ha_kuka_obs_dim(p->n_arms, p->n_keypoints), "obs_dim %d does not match the task layout %d", p->obs_dim,
+             ha_kuka_obs_dim(p->n_arms, p->n_keypoints));
+  HA_REQUIRE(p->n_bodies > 0 && p->object_body >= 0 && p->object_body < p->n_bodies, "object_body out of range");
+  HA_REQUIRE(p->palm_body[0] >= 0 && p->palm_body[0] < p->n_bodies, "palm_body out of range");
+  for (int t = 0; t < p->n_tips; ++t)
+    HA_REQUIRE(p->tip_body[t] >= 0 && p->tip_body[t] < p->n_bodies, "tip_body[%d] out of range", t);
+  HA_REQUIRE(p->success_steps >= 1, "success_steps must be >= 1");
+  const void* need[] = {b->root_state, b->rigid_body_state, b->dof_state, b->object_actor, b->goal_actor, b->hand_actor,
+                        b->object_init_state, b->object_keypoint_offsets, b->object_scales, b->finger_rew_coeffs, b->goal_states,
+                        b->obs_buf, b->rew_buf, b->reset_buf, b->reset_goal_buf, b->progress_buf, b->timeout_buf, b->successes,
+                        b->prev_episode_successes, b->true_objective, b->prev_episode_true_objective, b->near_goal_steps,
+                        b->lifted_object, b->closest_keypoint_max_dist, b->closest_fingertip_dist, b->furthest_hand_dist,
+                        b->rewards_episode, b->episode_cumulative, b->prev_targets, b->cur_targets, b->actions, b->rb_forces,
+                        b->random_force_prob, b->root_reset_indices, b->hand_reset_indices, b->reset_counts, b->stats, b->scratch,
+                        b->tickets, b->dynamic};
+  for (size_t i = 0; i < sizeof(need) / sizeof(need[0]); ++i) HA_REQUIRE(need[i] != nullptr, "HaKukaBuffers field #%zu is null", i);
+  HA_REQUIRE_ALIGNED16(b->dof_state);
+  HA_REQUIRE_ALIGNED16(b->obs_buf);
+  HA_REQUIRE_ALIGNED16(b->closest_fingertip_dist);
+  HA_REQUIRE_ALIGNED16(b->finger_rew_coeffs);
+  return HA_OK;
+}
+
+template <int K>
+int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {
+  using S = ha::KukaPostSmem<K>;
+  static bool configured = false;
+  if (!configured) {
+    int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka_post_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
+                            "cudaFuncSetAttribute(kuka_post_kernel)");
+    if (rc) return rc;
+    configured = true;
+  }
+  const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  ha::kuka_post_kernel<K><<<grid, ha::kThreads, sizeof(S), st>>>(*p, *b, mode);
+  return ha::check_cuda(cudaGetLastError(), "kuka_post_kernel launch");
+}
+
+}  // namespace
+
+extern "C" {
+
+int ha_kuka_obs_dim(int n_arms, int n_keypoints) {
+  if (n_arms == 1) return ha::kuka_layout(23, 4, n_keypoints).dim;
+  // allegro_kuka_two_arms.py:176-211: no closest_fingertip_dist slots, keypoints relative to both palms
+  if (n_arms == 2) return 46 + 46 + 6 + 20 + 10 + 24 + 6 * n_keypoints + 3 * n_keypoints + 3 + 1 + 1 + 1 + 1 + 1;
+  return -1;
+}
+
+size_t ha_kuka_post_bytes_per_env_step(const HaKukaParams* p) {
+  if (!p) return 0;
+  const size_t D = (size_t)p->n_dofs, T = (size_t)p->n_tips, K = (size_t)p->n_keypoints, A = (size_t)p->n_arms;
+  // reads: dof pos+vel, object root row, goal pose, palm rows, fingertip pos+rot, per-env constants, state, accumulators
+  size_t rd = 8 * D + 52 + 28 + 52 * A + 28 * T + (12 * K + 12 + 4 + (A == 1 ? 4 * T : 0));
+  rd += 4 + 4 * T + (A == 1 ? 4 : 0) + 1 + 4 + 4 + 8 + 8 + 4;
+  const size_t n_ep = (A == 1) ? HA_KUKA_N_EPISODE_TERMS : 8, n_step = (A == 1) ? HA_KUKA_N_STEP_TERMS : 5;
+  rd += 4 * n_ep;
+  // writes: obs row, reward, 3 int64 flags, per-env state, accumulators, per-step terms
+  size_t wr = 4 * (size_t)p->obs_dim + 4 + 24 + (4 + 4 * T + (A == 1 ? 4 : 0) + 1 + 4 + 4 + 4) + 4 * n_ep + 4 * n_step;
+  return rd + wr;
+}
+
+size_t ha_kuka_pre_bytes_per_env_step(const HaKukaParams* p) {
+  if (!p) return 0;
+  const size_t D = (size_t)p->n_dofs;
+  // actions r, prev_targets r, cur_targets w, prev_targets w, actions copy w, 2 int64 masks r, force row r+w, force prob r
+  return 5 * 4 * D + 16 + 24 + 4;
+}
+
+size_t ha_kuka_bytes_per_env_step(const HaKukaParams* p) {
+  return ha_kuka_post_bytes_per_env_step(p) + ha_kuka_pre_bytes_per_env_step(p);
+}
+
+size_t ha_kuka_scratch_floats(int n_envs) {
+  const size_t ctas = ((size_t)n_envs + HA_ENVS_PER_CTA - 1) / HA_ENVS_PER_CTA;
+  return ctas * HA_STATS_LEN;
+}
+
+int ha_kuka_pre_step(const HaKukaParams* p, const HaKukaBuffers* b, const float* actions, const float* ext_rand, ha_stream_t stream) {
+  int rc = validate_kuka(p, b);
+  if (rc) return rc;
+  HA_REQUIRE(actions != nullptr, "actions is null");
+  HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
+  const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, actions, ext_rand, ha::kPreFull);
+  return ha::check_cuda(cudaGetLastError(), "kuka_pre_kernel launch");
+}
+
+int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float* ext_rand, ha_stream_t stream) {
+  int rc = validate_kuka(p, b);
+  if (rc) return rc;
+  HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
+  const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);
+  return ha::check_cuda(cudaGetLastError(), "kuka_pre_kernel(reset_only) launch");
+}
+
+static int post_dispatch(const HaKukaParams* p, const HaKukaBuffers* b, int mode, ha_stream_t stream) {
+  int rc = validate_kuka(p, b);
+  if (rc) return rc;
+  if (p->n_keypoints == 4) return launch_post<4>(p, b, mode, (cudaStream_t)stream);
+  return launch_post<1>(p, b, mode, (cudaStream_t)stream);
+}
+
+int ha_kuka_post_step(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream) {
+  return post_dispatch(p, b, ha::kPostFull, stream);
+}
+
+int ha_kuka_observe(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream) {
+  return post_dispatch(p, b, ha::kPostObserveOnly, stream);
+}
+
+}  // extern "C"

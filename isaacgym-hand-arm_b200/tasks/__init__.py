@@ -1,0 +1,14 @@
+"""Task registry (subset of ``isaacgymenvs/tasks/__init__.py:66-123`` that lies on the hot path)."""
+from .allegro_kuka import AllegroKukaBase, AllegroKukaReorientation
+
+
+def resolve_allegro_kuka(cfg, *args, **kwargs):
+    """``tasks/__init__.py:66-76``: dispatch on ``env.subtask``."""
+    subtask = cfg["env"]["subtask"]
+    table = {"reorientation": AllegroKukaReorientation}
+    if subtask not in table:
+        raise ValueError(f"Unknown subtask={subtask} in {list(table)}")
+    return table[subtask](cfg, *args, **kwargs)
+
+
+isaacgym_task_map = {"AllegroKuka": resolve_allegro_kuka, "AllegroKukaLSTM": resolve_allegro_kuka}
