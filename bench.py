@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""Headline benchmark: task env-steps/s of the AllegroKuka reorientation hot path (BASELINE.json configs[2]).
+
+One "step" = pre_physics_step + post_physics_step (+ the VecTask.step tail) over one block of
+32768 envs per GPU, on synthetic simulator state (PhysX is the opaque producer).  Prints ONE JSON
+line (see the driver contract in the task statement): ``value`` is device-resident throughput,
+``e2e`` goes through ``VecTask.step`` with host buffers, ``roofline`` is the post-physics kernel
+against the measured HBM peak, ``cpu_baseline`` is the CPU oracle port on this box's host cores.
+
+``--impl reference`` times the reference's CPU implementation of the same path (the oracle port,
+or the real reference classes when /root/reference is present) instead of the CUDA path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "task env-steps/s (obs+reward+reset)"
+UNIT = "env-steps/s"
+WORKLOAD = "AllegroKuka reorientation (23-DOF, keypoint reward), 32768 envs/GPU"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4000)
+    ap.add_argument("--warmup", type=int, default=200)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs", type=int, default=32768, help="envs per GPU")
+    ap.add_argument("--blocks", type=int, default=4, help="independent env blocks stepped round-robin so state does not stay in L2")
+    ap.add_argument("--snapshots", type=int, default=4, help="rotating simulator snapshots per env block")
+    ap.add_argument("--cpu-steps", type=int, default=0, help="steps of the CPU baseline sample (0 = auto, about 10-20 s)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self.nv is not None:
+            self.t.join()
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arms
+# ------------------------------------------------------------------------------------------------
+def cpu_port_rate(n_envs: int, steps: int, warmup: int = 2):
+    """env-steps/s of the CPU oracle port (torch eager on all host cores), pre + post per step."""
+    from oracle import kuka_oracle as ko, kuka_state as ks
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    c = ko.KukaConsts()
+    st = ks.make_state(n_envs, seed=1, c=c, fresh=False)
+    acts = [ks.make_actions(n_envs, s) for s in range(2)]
+    rnds = [ks.make_rnd(n_envs, s) for s in range(2)]
+    if steps <= 0:
+        t0 = time.perf_counter()
+        ko.pre_step(st, c, acts[0], rnds[0]); ko.post_step(st, c)
+        one = time.perf_counter() - t0
+        steps = max(3, min(200, int(12.0 / max(one, 1e-3))))
+    for i in range(warmup):
+        ko.pre_step(st, c, acts[i % 2], rnds[i % 2]); ko.post_step(st, c)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        ko.pre_step(st, c, acts[i % 2], rnds[i % 2]); ko.post_step(st, c)
+    dt = time.perf_counter() - t0
+    return n_envs * steps / dt, cores, steps, dt
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    rate, cores, steps, dt = cpu_port_rate(args.envs, args.steps if args.steps < 1000 else 0, warmup=min(args.warmup, 3))
+    sample = f"{steps} steps x {args.envs} envs, torch-CPU oracle port of pre+post physics step, {dt:.1f} s"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 3), "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "envs_per_gpu": args.envs},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# CUDA arm
+# ------------------------------------------------------------------------------------------------
+def build_blocks(args, device):
+    import handarm_b200.config as hcfg
+    from handarm_b200.sim import KUKA_LAYOUT, SyntheticSim
+    from handarm_b200.tasks.allegro_kuka import AllegroKukaReorientation
+    rank = int(os.environ.get("RANK", "0"))
+    tasks, actions = [], []
+    for b in range(args.blocks):
+        cfg = hcfg.load_task_config("AllegroKuka", num_envs=args.envs, sim_device=device)
+        sim = SyntheticSim(args.envs, KUKA_LAYOUT, device, seed=1234 + 100 * rank + b, snapshots=args.snapshots)
+        task = AllegroKukaReorientation(cfg, device, device, 0, True, sim=sim, seed=1234 + rank)
+        task.seed_rng(1234 + 100 * rank + b)
+        sim.fill_kuka(goal_states=None)
+        sim.record_calls = False
+        gen = torch.Generator().manual_seed(99 + b + 100 * rank)
+        actions.append((2.0 * torch.rand(args.envs, 23, generator=gen) - 1.0).to(device))
+        tasks.append(task)
+    return tasks, actions
+
+
+def one_step(task, act):
+    task.pre_physics_step(act)
+    task.sim.simulate()
+    task.post_physics_step()
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = f"cuda:{local}"
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(device))
+    hbm_gbs, peak_src = peaks()
+    tasks, actions = build_blocks(args, device)
+    B, S, N = args.blocks, args.snapshots, args.envs
+    stream = torch.cuda.Stream()
+    stats_sum = torch.zeros(16, device=device)
+
+    # first pass: every env resets (reset_buf starts as ones), then a few eager steps
+    with torch.cuda.stream(stream):
+        for t, a in zip(tasks, actions):
+            for _ in range(2):
+                one_step(t, a)
+    stream.synchronize()
+    for t in tasks:                       # curriculum host logic must not fire inside graph capture
+        t.frame_since_restart = 0
+        t.last_curriculum_update = 0
+
+    # one CUDA graph = S rounds over the B env blocks (B*S steps, 2 kernels each)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=stream):
+        for _ in range(S):
+            for t, a in zip(tasks, actions):
+                one_step(t, a)
+    per_graph = B * S
+
+    def run_steps(k):
+        n_graph, rest = divmod(k, per_graph)
+        for _ in range(n_graph):
+            graph.replay()
+            for t in tasks:
+                t.advance_frames(S)
+            if world > 1:
+                # episode statistics: one tiny all-reduce per replay (sum half; the max half is analogous)
+                stats_sum.copy_(tasks[0].stats, non_blocking=True)
+                dist.all_reduce(stats_sum, async_op=True)
+        for i in range(rest):
+            one_step(tasks[i % B], actions[i % B])
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        run_steps(max(args.warmup, 3))
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as clk:
+            e0.record(stream)
+            run_steps(args.steps)
+            e1.record(stream)
+            barrier()
+        ms = e0.elapsed_time(e1)
+    if world > 1:
+        tms = torch.tensor([ms], device=device)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms)
+    value = world * N * args.steps / (ms * 1e-3)
+
+    # ---- per-kernel device times (direct launches, CUDA events on the launching stream) ----
+    n_probe = min(args.steps, 400)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(n_probe)]
+    with torch.cuda.stream(stream):
+        for i in range(n_probe):
+            t, a = tasks[i % B], actions[i % B]
+            evs[i][0].record(stream)
+            t.pre_physics_step(a)
+            evs[i][1].record(stream)
+            t.sim.simulate()
+            t.post_physics_step()
+            evs[i][2].record(stream)
+        stream.synchronize()
+    pre_us = sorted(e[0].elapsed_time(e[1]) * 1e3 for e in evs)
+    post_us = sorted(e[1].elapsed_time(e[2]) * 1e3 for e in evs)
+    pre_avg, post_avg = sum(pre_us) / n_probe, sum(post_us) / n_probe
+    lib = tasks[0]._lib
+    import ctypes
+    post_bytes = int(lib.ha_kuka_post_bytes_per_env_step(ctypes.byref(tasks[0]._params)))
+    pre_bytes = int(lib.ha_kuka_pre_bytes_per_env_step(ctypes.byref(tasks[0]._params)))
+    achieved = N * post_bytes / (post_avg * 1e-6) / 1e9
+    step_frac = (N * (post_bytes + pre_bytes) / (ms * 1e-3 / args.steps) / 1e9) / hbm_gbs
+
+    # ---- L2-warm variant: a single env block stepped back to back (task state stays in L2) ----
+    with torch.cuda.stream(stream):
+        g1 = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g1, stream=stream):
+            for _ in range(S):
+                one_step(tasks[0], actions[0])
+        for _ in range(5):
+            g1.replay()
+        w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = max(1, args.steps // S)
+        w0.record(stream)
+        for _ in range(reps):
+            g1.replay()
+        w1.record(stream)
+        stream.synchronize()
+    warm_value = N * reps * S / (w0.elapsed_time(w1) * 1e-3)
+
+    # ---- end to end through VecTask.step with host buffers ----
+    e2e = None
+    if not args.no_e2e:
+        k = min(args.steps, 200)
+        h_act = [(a.cpu()).pin_memory() for a in actions]
+        t0 = tasks[0]
+        h_obs = torch.empty((N, t0.num_obs), dtype=torch.float32).pin_memory()
+        h_rew = torch.empty(N, dtype=torch.float32).pin_memory()
+        h_rst = torch.empty(N, dtype=torch.int64).pin_memory()
+        h_to = torch.empty(N, dtype=torch.bool).pin_memory()
+
+        def e2e_step(i):
+            t = tasks[i % B]
+            obs, rew, rst, extras = t.step(h_act[i % B])          # H2D of the actions happens inside step()
+            h_obs.copy_(obs["obs"], non_blocking=True)
+            h_rew.copy_(rew, non_blocking=True)
+            h_rst.copy_(rst, non_blocking=True)
+            h_to.copy_(extras["time_outs"], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        with torch.cuda.stream(stream):
+            for i in range(5):
+                e2e_step(i)
+            barrier()
+            t_start = time.perf_counter()
+            for i in range(k):
+                e2e_step(i)
+            barrier()
+            dt = time.perf_counter() - t_start
+        if world > 1:
+            tdt = torch.tensor([dt], device=device)
+            dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
+            dt = float(tdt)
+        e2e = {"value": world * N * k / dt, "unit": UNIT, "h2d_bytes_per_step": N * 23 * 4,
+               "d2h_bytes_per_step": N * (t0.num_obs * 4 + 4 + 8 + 1), "steps": k}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        rate, cores, csteps, cdt = cpu_port_rate(N, args.cpu_steps)
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{csteps} steps x {N} envs, torch-CPU oracle port of pre+post physics step, {cdt:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "envs_per_gpu": N, "env_blocks": B, "snapshots_per_block": S,
+                       "l2": f"inputs larger than L2: {B} env blocks stepped round-robin, {B}x{N * (post_bytes + pre_bytes) / 1e6:.0f} MB "
+                             "algorithmic bytes per round", "launch": f"CUDA graph of {per_graph} steps", "rng": "in-kernel Philox"},
+            "roofline": {"bound": "hbm", "kernel": "kuka_post_kernel<4>", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
+                         "frac": achieved / hbm_gbs, "traffic": None, "peak_source": peak_src, "kernel_us": post_avg,
+                         "bytes_per_env": post_bytes, "pre_kernel_us": pre_avg, "pre_bytes_per_env": pre_bytes,
+                         "step_frac": step_frac, "post_us_median": post_us[n_probe // 2], "pre_us_median": pre_us[n_probe // 2]},
+            "value_l2_warm": warm_value,
+            "clocks": clk.summary(),
+            "gpu_launches": 2 * args.steps,
+        }
+        if e2e is not None:
+            line["e2e"] = e2e
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -408,6 +408,13 @@ class AllegroKukaBase(VecTask):
     def _extra_curriculum(self):
         pass
 
+    def advance_frames(self, n: int) -> None:
+        """Host-side frame accounting for steps that were replayed from a CUDA graph (the kernels ran,
+        the Python hooks did not): keeps ``frame_since_restart`` and the tolerance curriculum going."""
+        self.frame_since_restart += n
+        self.control_steps += n
+        self._extra_curriculum()
+
     def post_physics_step(self):
         """allegro_kuka_base.py:1426-1443 + vec_task.py:424-432 as one kernel."""
         self._require_engine()

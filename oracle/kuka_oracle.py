@@ -132,3 +132,263 @@ def true_objective_coeffs(tol: float, initial: float, target: float) -> Tuple[fl
     """allegro_kuka_utils.py:118-158."""
     offset = (initial - tol) / (initial - target) if initial > target else 1.0
     return (0.01 if tol > target else 1.0), offset
+
+
+# ---------------------------------------------------------------------------------------------
+# pre-physics step
+# ---------------------------------------------------------------------------------------------
+def _reset_target(st: Dict[str, Tensor], c: KukaConsts, ids: Tensor, pos_u: Tensor, rot_u: Tensor) -> None:
+    """allegro_kuka_reorientation.py:104-128 + allegro_kuka_base.py:1191-1196 for env ids ``ids``."""
+    org = torch.tensor(c.target_volume_origin, dtype=torch.float32)
+    ext = torch.tensor(c.target_volume_extent, dtype=torch.float32)
+    lo = org + ext[:, 0]
+    size = (org + ext[:, 1]) - lo
+    pose = torch.cat((lo + pos_u * size, random_quat(rot_u)), dim=-1)
+    st["goal_states"][ids, 0:7] = pose
+    rows = st["goal_object_indices"][ids]
+    st["root_state"][rows, 0:7] = pose
+    st["root_state"][rows, 7:13] = 0.0
+    st["reset_goal_buf"][ids] = 0
+    st["near_goal_steps"][ids] = 0
+    st["closest_keypoint_max_dist"][ids] = -1.0
+
+
+def pre_step(st: Dict[str, Tensor], c: KukaConsts, actions: Tensor, rnd: Tensor) -> Dict[str, Tensor]:
+    """One ``pre_physics_step``; mutates ``st`` in place and returns the simulator-facing index lists."""
+    D, A = c.n_dofs, c.n_arm_dofs
+    lo, hi = st["dof_lower"], st["dof_upper"]
+    st["actions"] = actions.clone()
+    reset_ids = st["reset_buf"].nonzero(as_tuple=False).squeeze(-1)
+    goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
+    root_lists: List[Tensor] = []
+
+    # goal-only resets (always executed, also for an empty id list)
+    _reset_target(st, c, goal_ids, rnd[goal_ids, RND_GOAL_POS:RND_GOAL_POS + 3], rnd[goal_ids, RND_GOAL_ROT:RND_GOAL_ROT + 3])
+    root_lists.append(st["goal_object_indices"][goal_ids])
+
+    hand_rows = torch.zeros(0, dtype=torch.int32)
+    if len(reset_ids) > 0:
+        ids = reset_ids
+        _reset_target(st, c, ids, rnd[ids, RND_RESET_GOAL_POS:RND_RESET_GOAL_POS + 3], rnd[ids, RND_RESET_GOAL_ROT:RND_RESET_GOAL_ROT + 3])
+        root_lists.append(st["goal_object_indices"][ids])
+        st["rb_forces"][ids] = 0.0
+        # object pose (allegro_kuka_base.py:1198-1224)
+        rows = st["object_indices"][ids]
+        noise = 2.0 * rnd[ids, RND_OBJ_POS:RND_OBJ_POS + 3] + (-1.0)
+        new_row = st["object_init_state"][ids].clone()
+        for k in range(3):
+            new_row[:, k] = st["object_init_state"][ids, k] + c.reset_position_noise[k] * noise[:, k]
+        new_row[:, 3:7] = random_quat(rnd[ids, RND_OBJ_ROT:RND_OBJ_ROT + 3])
+        new_row[:, 7:13] = 0.0
+        st["root_state"][rows] = new_row
+        st["closest_fingertip_dist"][ids] = -1.0
+        st["furthest_hand_dist"][ids] = -1.0
+        hand_rows = st["allegro_hand_indices"][ids].to(torch.int32)
+        # force probability (:1265-1269)
+        pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
+        st["random_force_prob"][ids] = torch.exp((torch.log(pr[0]) - torch.log(pr[1])) * rnd[ids, RND_FORCE_PROB] + torch.log(pr[1]))
+        # DOF state (:1271-1290)
+        dflt = st["dof_default"]
+        dmax, dmin = hi - dflt, lo - dflt
+        coeff = torch.zeros_like(dflt)
+        coeff[0:A] = c.reset_dof_pos_noise_arm
+        coeff[A:D] = c.reset_dof_pos_noise_fingers
+        pos = dflt + coeff * (dmin + (dmax - dmin) * rnd[ids, RND_DOF_POS:RND_DOF_POS + D])
+        vel = c.reset_dof_vel_noise * (2.0 * rnd[ids, RND_DOF_POS + D:RND_DOF_POS + 2 * D] + (-1.0))
+        st["dof_state"][ids, :D, 0] = pos
+        st["dof_state"][ids, :D, 1] = vel
+        st["prev_targets"][ids, :D] = pos
+        st["cur_targets"][ids, :D] = pos
+        root_lists.append(st["object_indices"][ids])
+        # episode bookkeeping (:1323-1347)
+        st["progress_buf"][ids] = 0
+        st["reset_buf"][ids] = 0
+        st["prev_episode_successes"][ids] = st["successes"][ids]
+        st["successes"][ids] = 0.0
+        st["prev_episode_true_objective"][ids] = st["true_objective"][ids]
+        st["true_objective"][ids] = 0.0
+        st["lifted_object"][ids] = False
+        st["closest_keypoint_max_dist"][ids] = -1.0
+        st["closest_fingertip_dist"][ids] = -1.0
+        st["furthest_hand_dist"][ids] = -1.0
+        st["near_goal_steps"][ids] = 0
+        st["rewards_episode"][:, ids] = 0.0
+
+    root_rows = torch.unique(torch.cat(root_lists).to(torch.int32))       # (:1229-1244)
+
+    # action -> targets (:1377-1397)
+    cur = st["cur_targets"]
+    prev = st["prev_targets"]
+    hand = scale(actions[:, A:D], lo[A:D], hi[A:D])
+    hand = c.act_moving_average * hand + (1.0 - c.act_moving_average) * prev[:, A:D]
+    cur[:, A:D] = torch.max(torch.min(hand, hi[A:D]), lo[A:D])
+    arm = prev[:, :A] + c.hand_dof_speed_scale * c.dt * actions[:, :A]
+    cur[:, :A] = torch.max(torch.min(arm, hi[:A]), lo[:A])
+    prev[:, :] = cur
+
+    # random forces on the object body (:1401-1414)
+    if c.force_scale > 0.0:
+        st["rb_forces"] *= torch.pow(torch.tensor(c.force_decay, dtype=torch.float32), c.dt / c.force_decay_interval)
+        hit = (rnd[:, RND_FORCE_TEST] < st["random_force_prob"]).nonzero(as_tuple=False).squeeze(-1)
+        masses = torch.tensor([c.object_mass], dtype=torch.float32)
+        st["rb_forces"][hit, c.object_body, :] = rnd[hit, RND_FORCE_NORMAL:RND_FORCE_NORMAL + 3] * masses * c.force_scale
+    return {"root_rows": root_rows, "hand_rows": hand_rows}
+
+
+# ---------------------------------------------------------------------------------------------
+# post-physics step
+# ---------------------------------------------------------------------------------------------
+def _geometry(st: Dict[str, Tensor], c: KukaConsts) -> Dict[str, Tensor]:
+    """Gathers + keypoint / fingertip geometry of compute_observations (allegro_kuka_base.py:1002-1079)."""
+    N = st["reset_buf"].shape[0]
+    obj = st["root_state"][st["object_indices"]]
+    rb = st["rigid_body_state"].view(N, -1, 13)
+    palm = rb[:, c.palm_body]
+    tips = rb[:, list(c.tip_bodies)]
+    g: Dict[str, Tensor] = {"obj": obj, "palm": palm}
+    palm_off = torch.tensor(c.palm_offset, dtype=torch.float32).repeat(N, 1)
+    g["palm_center"] = palm[:, 0:3] + quat_rotate(palm[:, 3:7], palm_off)
+    tip_off = torch.tensor(np.asarray(c.tip_offsets, dtype=np.float32)).repeat(N, 1, 1)
+    tip_pos = torch.zeros(N, c.n_tips, 3)
+    for i in range(c.n_tips):
+        tip_pos[:, i] = tips[:, i, 0:3] + quat_rotate(tips[:, i, 3:7], tip_off[:, i])
+    g["tip_rel_obj"] = tip_pos - obj[:, None, 0:3]
+    g["tip_dist"] = torch.norm(g["tip_rel_obj"], dim=-1)
+    g["tip_rel_palm"] = tip_pos - g["palm_center"][:, None]
+    K = st["object_keypoint_offsets"].shape[1]
+    okp = torch.zeros(N, K, 3)
+    gkp = torch.zeros(N, K, 3)
+    goal = st["goal_states"]
+    for k in range(K):
+        okp[:, k] = obj[:, 0:3] + quat_rotate(obj[:, 3:7], st["object_keypoint_offsets"][:, k])
+        gkp[:, k] = goal[:, 0:3] + quat_rotate(goal[:, 3:7], st["object_keypoint_offsets"][:, k])
+    g["kp_rel_goal"] = okp - gkp
+    g["kp_rel_palm"] = okp - g["palm_center"][:, None]
+    g["kp_max"] = torch.norm(g["kp_rel_goal"], dim=-1).max(dim=-1).values
+    return g
+
+
+def _fill_obs(st: Dict[str, Tensor], c: KukaConsts, g: Dict[str, Tensor]) -> int:
+    """compute_full_state (allegro_kuka_base.py:1091-1172); returns the reward slot offset."""
+    N, D = st["reset_buf"].shape[0], c.n_dofs
+    dof = st["dof_state"].view(N, -1, 2)[:, :D]
+    parts = [
+        unscale(dof[..., 0], st["dof_lower"], st["dof_upper"]),
+        dof[..., 1],
+        g["palm_center"],
+        g["palm"][:, 3:13],
+        g["obj"][:, 3:13],
+        g["tip_rel_palm"].reshape(N, -1),
+        g["kp_rel_palm"].reshape(N, -1),
+        g["kp_rel_goal"].reshape(N, -1),
+        st["object_scales"],
+        st["closest_keypoint_max_dist"].unsqueeze(-1),
+        st["closest_fingertip_dist"],
+        st["lifted_object"].unsqueeze(-1).to(torch.float32),
+        torch.log(st["progress_buf"] / 10 + 1).unsqueeze(-1),
+        torch.log(st["successes"] + 1).unsqueeze(-1),
+    ]
+    body = torch.cat(parts, dim=-1)
+    ofs = body.shape[1]
+    st["obs_buf"][:, :ofs] = body
+    return ofs
+
+
+def observe(st: Dict[str, Tensor], c: KukaConsts) -> Dict[str, Tensor]:
+    """compute_observations (allegro_kuka_base.py:991-1089): geometry, lazy init of closest/furthest, obs row."""
+    g = _geometry(st, c)
+    st["closest_fingertip_dist"] = torch.where(st["closest_fingertip_dist"] < 0.0, g["tip_dist"], st["closest_fingertip_dist"])
+    st["furthest_hand_dist"] = torch.where(st["furthest_hand_dist"] < 0.0, g["tip_dist"][:, 0], st["furthest_hand_dist"])
+    st["closest_keypoint_max_dist"] = torch.where(st["closest_keypoint_max_dist"] < 0.0, g["kp_max"], st["closest_keypoint_max_dist"])
+    g["reward_ofs"] = _fill_obs(st, c, g)
+    return g
+
+
+def post_step(st: Dict[str, Tensor], c: KukaConsts) -> Dict[str, Tensor]:
+    """One ``post_physics_step`` plus the VecTask.step tail; mutates ``st``; returns extras-like scalars."""
+    st["progress_buf"] = st["progress_buf"] + 1
+    st["randomize_buf"] = st["randomize_buf"] + 1
+    g = observe(st, c)
+    obj_z = g["obj"][:, 2]
+    cur = g["tip_dist"]
+
+    # lifting (:788-812)
+    z_lift = 0.05 + obj_z - st["object_init_state"][:, 2]
+    lifting_rew = torch.clip(z_lift, 0, 0.5)
+    lifted_prev = st["lifted_object"]
+    lifted = (z_lift > c.lifting_bonus_threshold) | lifted_prev
+    lift_bonus_rew = c.lifting_bonus * (lifted & ~lifted_prev)
+    lifting_rew = lifting_rew * ~lifted
+    st["lifted_object"] = lifted
+
+    # fingertip / hand distance deltas (:759-786)
+    d_closest = st["closest_fingertip_dist"] - cur
+    st["closest_fingertip_dist"] = torch.minimum(st["closest_fingertip_dist"], cur)
+    d_furthest = st["furthest_hand_dist"] - cur[:, 0]
+    st["furthest_hand_dist"] = torch.maximum(st["furthest_hand_dist"], cur[:, 0])
+    ft = torch.sum(torch.clip(d_closest, 0, 10) * st["finger_rew_coeffs"], dim=-1)
+    ft = ft * ~lifted
+    hp = torch.clip(d_furthest, -10, 0)
+    hp = hp * ~lifted
+    hp = hp * c.n_tips
+
+    # keypoints (:814-828)
+    kp_delta = st["closest_keypoint_max_dist"] - g["kp_max"]
+    st["closest_keypoint_max_dist"] = torch.minimum(st["closest_keypoint_max_dist"], g["kp_max"])
+    kp_rew = torch.clip(kp_delta, 0, 100) * lifted
+
+    # success logic (:857-869)
+    near_goal = g["kp_max"] <= c.success_tolerance * c.keypoint_scale
+    st["near_goal_steps"] = st["near_goal_steps"] + near_goal
+    is_success = st["near_goal_steps"] >= c.success_steps
+    st["successes"] = st["successes"] + is_success
+    st["reset_goal_buf"][:] = is_success
+
+    acc = st["rewards_episode"]
+    acc[0] += ft
+    acc[1] += hp
+    acc[2] += lifting_rew
+    acc[3] += kp_rew
+    ft = ft * c.distance_delta_rew_scale
+    hp = hp * (c.distance_delta_rew_scale * 0)
+    lifting_rew = lifting_rew * c.lifting_rew_scale
+    kp_rew = kp_rew * c.keypoint_rew_scale
+    vel = st["dof_state"].view(cur.shape[0], -1, 2)[:, :c.n_dofs, 1]
+    kuka_pen = -1 * (torch.sum(torch.abs(vel[:, 0:c.n_arm_dofs]), dim=-1) * c.kuka_actions_penalty_scale)
+    allegro_pen = -1 * (torch.sum(torch.abs(vel[:, c.n_arm_dofs:c.n_dofs]), dim=-1) * c.allegro_actions_penalty_scale)
+    bonus_rew = near_goal * (c.reach_goal_bonus / c.success_steps)
+    reward = ft + hp + lifting_rew + lift_bonus_rew + kp_rew + kuka_pen + allegro_pen + bonus_rew
+    st["rew_buf"][:] = reward
+
+    # resets (:841-849, reorientation :97-102)
+    ones = torch.ones_like(st["reset_buf"])
+    resets = torch.where(obj_z < 0.1, ones, st["reset_buf"])
+    if c.max_consecutive_successes > 0:
+        st["progress_buf"] = torch.where(is_success, torch.zeros_like(st["progress_buf"]), st["progress_buf"])
+        resets = torch.where(st["successes"] >= c.max_consecutive_successes, ones, resets)
+    resets = torch.where(st["progress_buf"] >= c.max_episode_length - 1, ones, resets)
+    if c.extra_far_reset:
+        resets = torch.where(cur.max(dim=-1).values > 1.5, ones, resets)
+    st["reset_buf"][:] = resets
+
+    scale_, offset_ = true_objective_coeffs(c.success_tolerance, c.initial_tolerance, c.target_tolerance)
+    st["true_objective"] = (st["successes"] * scale_) + offset_ if scale_ != 1.0 else st["successes"] + offset_
+
+    step_terms = [ft, hp, lifting_rew, lift_bonus_rew, kp_rew, kuka_pen, allegro_pen, bonus_rew]
+    for name, val in zip(STEP_TERMS, step_terms):
+        acc[EPISODE_TERMS.index(name)] += val
+        st["episode_cumulative"][STEP_TERMS.index(name)] = val
+
+    # reward observation and clamp (:1437-1441)
+    st["obs_buf"][:, g["reward_ofs"]] = reward * 0.01
+    if c.clamp_abs_observations > 0:
+        st["obs_buf"].clamp_(-c.clamp_abs_observations, c.clamp_abs_observations)
+    # vec_task.py:424
+    st["timeout_buf"] = (st["progress_buf"] >= c.max_episode_length - 1) & (st["reset_buf"] != 0)
+    return {
+        "successes_mean": st["prev_episode_successes"].mean(),
+        "true_objective_mean": st["true_objective"].mean(),
+        "true_objective_min": st["true_objective"].min(),
+        "true_objective_max": st["true_objective"].max(),
+        "is_success": is_success,
+    }

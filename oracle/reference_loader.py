@@ -1,0 +1,266 @@
+"""ORACLE INFRASTRUCTURE (tests only) -- runs the UNMODIFIED reference classes from /root/reference.
+
+The reference's task modules import ``isaacgym`` (closed binary), ``gym``, ``hydra`` ... none of which
+exist here.  This loader installs stub modules and namespace-package shims so
+that ``isaacgymenvs/tasks/allegro_kuka/*.py`` import *from where they lie*, then builds task objects
+with ``object.__new__`` + attribute injection and a recording fake ``gym``.  The reference's own
+``pre_physics_step`` / ``post_physics_step`` then run on CPU torch on our synthetic state.
+
+Only usable where ``/root/reference`` exists (this container).  Nothing in the product imports it.
+"""
+from __future__ import annotations
+
+import contextlib
+import importlib
+import os
+import sys
+import types
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+REFERENCE_ROOT = os.environ.get("HANDARM_REFERENCE_ROOT", "/root/reference")
+
+
+def reference_available() -> bool:
+    return os.path.isdir(os.path.join(REFERENCE_ROOT, "isaacgymenvs", "tasks"))
+
+
+class _Any:
+    """Swallows any attribute access / call; refuses dunders (inspect needs that)."""
+
+    def __init__(self, *a, **k):
+        pass
+
+    def __call__(self, *a, **k):
+        return _Any()
+
+    def __getattr__(self, n):
+        if n.startswith("__"):
+            raise AttributeError(n)
+        return _Any()
+
+
+def _stub(name: str, **kw) -> types.ModuleType:
+    m = types.ModuleType(name)
+    m.__dict__.update(kw)
+    sys.modules[name] = m
+    return m
+
+
+_loaded: Dict[str, types.ModuleType] = {}
+
+
+def load_reference() -> Dict[str, types.ModuleType]:
+    """Import the reference's hot-path modules; returns {short name: module}."""
+    if _loaded:
+        return _loaded
+    if not reference_available():
+        raise RuntimeError(f"reference not found under {REFERENCE_ROOT}")
+
+    def lazy(n):
+        if n.startswith("__"):
+            raise AttributeError(n)
+        return _Any()
+
+    ig = _stub("isaacgym")
+    for sub in ("gymapi", "gymtorch", "gymutil", "torch_utils"):
+        m = _stub("isaacgym." + sub)
+        m.__getattr__ = lazy
+        setattr(ig, sub, m)
+    gt = sys.modules["isaacgym.gymtorch"]
+    gt.wrap_tensor = lambda t: t
+    gt.unwrap_tensor = lambda t: t
+    if "gym" not in sys.modules:
+        g = _stub("gym")
+        g.spaces = _stub("gym.spaces", Box=_Any, Dict=_Any)
+        g.Space = object
+    if "omegaconf" not in sys.modules:
+        _stub("omegaconf", DictConfig=dict, ListConfig=list, OmegaConf=_Any)
+    if "tkinter" not in sys.modules:
+        _stub("tkinter", W="w")
+    root = os.path.join(REFERENCE_ROOT, "isaacgymenvs")
+    for name, sub in [("isaacgymenvs", ""), ("isaacgymenvs.tasks", "/tasks"), ("isaacgymenvs.utils", "/utils"),
+                      ("isaacgymenvs.tasks.base", "/tasks/base"), ("isaacgymenvs.tasks.allegro_kuka", "/tasks/allegro_kuka"),
+                      ("isaacgymenvs.tasks.dextreme", "/tasks/dextreme")]:
+        _stub(name).__path__ = [root + sub]
+    if not hasattr(np, "Inf"):
+        np.Inf = np.inf
+    _loaded["tju"] = importlib.import_module("isaacgymenvs.utils.torch_jit_utils")
+    _loaded["akb"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_base")
+    _loaded["akr"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_reorientation")
+    _loaded["aku"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_utils")
+    _loaded["vt"] = importlib.import_module("isaacgymenvs.tasks.base.vec_task")
+    return _loaded
+
+
+class FakeGym:
+    """Records every call the task makes into the simulator and returns None."""
+
+    def __init__(self):
+        self.calls: List[tuple] = []
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+
+        def rec(*args, **kwargs):
+            self.calls.append((name, args))
+            return None
+
+        return rec
+
+
+KUKA_EPISODE_KEYS = ["raw_fingertip_delta_rew", "raw_hand_delta_penalty", "raw_lifting_rew", "raw_keypoint_rew", "fingertip_delta_rew",
+                     "hand_delta_penalty", "lifting_rew", "lift_bonus_rew", "keypoint_rew", "bonus_rew", "kuka_actions_penalty",
+                     "allegro_actions_penalty"]
+
+
+def make_reference_kuka(st: Dict[str, torch.Tensor], c) -> object:
+    """An ``AllegroKukaReorientation`` instance (reference class) aliasing the tensors of ``st``.
+
+    ``st`` is the dict layout of ``oracle/kuka_state.py``; ``c`` a ``KukaConsts``.  The instance owns
+    views of the same storage wherever the reference keeps views (``arm_hand_dof_pos`` ...).
+    """
+    mods = load_reference()
+    env = object.__new__(mods["akr"].AllegroKukaReorientation)
+    N = st["reset_buf"].shape[0]
+    K = st["object_keypoint_offsets"].shape[1]
+    e = env.__dict__
+    e.update(
+        gym=FakeGym(), sim=None, device="cpu", rl_device="cpu", num_environments=N, viewer=None, debug_viz=False, headless=True,
+        num_arm_dofs=c.n_arm_dofs, num_hand_dofs=c.n_dofs - c.n_arm_dofs, num_hand_arm_dofs=c.n_dofs, num_finger_dofs=4,
+        num_allegro_fingertips=c.n_tips, num_keypoints=K, obs_type="full_state", with_fingertip_force_sensors=False,
+        with_dof_force_sensors=False, num_observations=st["obs_buf"].shape[1], privileged_actions=False, use_relative_control=False,
+        randomize=False, should_load_initial_states=False, save_states=False, eval_stats=False,
+        dt=c.dt, act_moving_average=c.act_moving_average, hand_dof_speed_scale=c.hand_dof_speed_scale, force_scale=c.force_scale,
+        force_decay_interval=c.force_decay_interval, clamp_abs_observations=c.clamp_abs_observations,
+        max_episode_length=c.max_episode_length, max_consecutive_successes=c.max_consecutive_successes, success_steps=c.success_steps,
+        success_tolerance=c.success_tolerance, initial_tolerance=c.initial_tolerance, target_tolerance=c.target_tolerance,
+        tolerance_curriculum_increment=0.9, tolerance_curriculum_interval=10 ** 9, keypoint_scale=c.keypoint_scale,
+        lifting_bonus_threshold=c.lifting_bonus_threshold, lifting_bonus=c.lifting_bonus, lifting_rew_scale=c.lifting_rew_scale,
+        keypoint_rew_scale=c.keypoint_rew_scale, distance_delta_rew_scale=c.distance_delta_rew_scale, reach_goal_bonus=c.reach_goal_bonus,
+        kuka_actions_penalty_scale=c.kuka_actions_penalty_scale, allegro_actions_penalty_scale=c.allegro_actions_penalty_scale,
+        reset_position_noise_x=c.reset_position_noise[0], reset_position_noise_y=c.reset_position_noise[1],
+        reset_position_noise_z=c.reset_position_noise[2], reset_dof_pos_noise_arm=c.reset_dof_pos_noise_arm,
+        reset_dof_pos_noise_fingers=c.reset_dof_pos_noise_fingers, reset_dof_vel_noise=c.reset_dof_vel_noise,
+        frame_since_restart=0, last_curriculum_update=0, control_freq_inv=1, extras={}, total_successes=0, total_resets=0,
+        set_actor_root_state_object_indices=[], randomization_params={},
+    )
+    env.full_state_size = st["obs_buf"].shape[1]
+    env.force_decay = torch.tensor(c.force_decay, dtype=torch.float32)
+    env.force_prob_range = torch.tensor(c.force_prob_range, dtype=torch.float32)
+    env.palm_offset = np.array(c.palm_offset, dtype=np.float32)
+    env.fingertip_offsets = np.array(c.tip_offsets, dtype=np.float32)
+    env.target_volume_origin = torch.tensor(c.target_volume_origin, dtype=torch.float32)
+    env.target_volume_extent = torch.tensor(c.target_volume_extent, dtype=torch.float32)
+    env.allegro_palm_handle = c.palm_body
+    env.allegro_fingertip_handles = torch.tensor(list(c.tip_bodies), dtype=torch.long)
+    env.object_rb_handles = torch.tensor([c.object_body], dtype=torch.long)
+    env.object_rb_masses = torch.tensor([c.object_mass], dtype=torch.float32)
+    # simulator tensors and the reference's views of them (allegro_kuka_base.py:280-295)
+    env.root_state_tensor = st["root_state"]
+    env.rigid_body_states = st["rigid_body_state"].view(N, -1, 13)
+    env.dof_state = st["dof_state"].view(-1, 2)
+    env.arm_hand_dof_state = env.dof_state.view(N, -1, 2)[:, : c.n_dofs]
+    env.arm_hand_dof_pos = env.arm_hand_dof_state[..., 0]
+    env.arm_hand_dof_vel = env.arm_hand_dof_state[..., 1]
+    env.num_bodies = env.rigid_body_states.shape[1]
+    for name in ("object_indices", "goal_object_indices", "allegro_hand_indices", "goal_states", "object_init_state",
+                 "object_keypoint_offsets", "object_scales", "finger_rew_coeffs", "obs_buf", "rew_buf", "reset_buf", "reset_goal_buf",
+                 "progress_buf", "randomize_buf", "successes", "prev_episode_successes", "true_objective",
+                 "prev_episode_true_objective", "near_goal_steps", "lifted_object", "closest_keypoint_max_dist",
+                 "closest_fingertip_dist", "furthest_hand_dist", "prev_targets", "cur_targets", "rb_forces", "random_force_prob"):
+        setattr(env, name, st[name])
+    env.arm_hand_dof_lower_limits = st["dof_lower"]
+    env.arm_hand_dof_upper_limits = st["dof_upper"]
+    env.hand_arm_default_dof_pos = st["dof_default"]
+    env.obj_keypoint_pos = torch.zeros(N, K, 3)
+    env.goal_keypoint_pos = torch.zeros(N, K, 3)
+    env.action_torques = torch.zeros_like(st["rb_forces"])
+    env.rewards_episode = {k: st["rewards_episode"][i] for i, k in enumerate(KUKA_EPISODE_KEYS)}
+    env.timeout_buf = torch.zeros(N, dtype=torch.long)
+    return env
+
+
+@contextlib.contextmanager
+def scripted_randoms(queue: List[torch.Tensor]):
+    """Feed the reference pre-drawn raw numbers instead of torch's global generator.
+
+    ``queue`` holds, in the reference's consumption order, raw U(0,1) / N(0,1) tensors of exactly the
+    shape each call asks for.  ``torch_rand_float(lo, hi, shape)`` becomes ``(hi - lo) * raw + lo``.
+    """
+    mods = load_reference()
+    q = list(queue)
+
+    def pop(shape):
+        t = q.pop(0)
+        assert tuple(t.shape) == tuple(shape), f"scripted random shape {tuple(t.shape)} != requested {tuple(shape)}"
+        return t.clone()
+
+    def fake_rand_float(lower, upper, shape, device=None):
+        return (upper - lower) * pop(shape) + lower
+
+    def fake_rand(*shape, **kw):
+        shape = shape[0] if len(shape) == 1 and isinstance(shape[0], (tuple, list, torch.Size)) else shape
+        return pop(shape)
+
+    saved = {}
+    for key in ("akb", "akr"):
+        saved[key] = mods[key].torch_rand_float
+        mods[key].torch_rand_float = fake_rand_float
+    old_rand, old_randn = torch.rand, torch.randn
+    torch.rand, torch.randn = fake_rand, fake_rand
+    try:
+        yield q
+    finally:
+        torch.rand, torch.randn = old_rand, old_randn
+        for key in ("akb", "akr"):
+            mods[key].torch_rand_float = saved[key]
+
+
+def kuka_random_queue(st: Dict[str, torch.Tensor], c, rnd: torch.Tensor) -> List[torch.Tensor]:
+    """Order of draws of one reorientation ``pre_physics_step`` for table ``rnd``."""
+    from . import kuka_oracle as ko
+    D = c.n_dofs
+    goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
+    ids = st["reset_buf"].nonzero(as_tuple=False).squeeze(-1)
+    q = [rnd[goal_ids, ko.RND_GOAL_POS:ko.RND_GOAL_POS + 3], rnd[goal_ids, ko.RND_GOAL_ROT:ko.RND_GOAL_ROT + 3]]
+    prob = st["random_force_prob"].clone()
+    if len(ids) > 0:
+        q += [rnd[ids, ko.RND_RESET_GOAL_POS:ko.RND_RESET_GOAL_POS + 3], rnd[ids, ko.RND_RESET_GOAL_ROT:ko.RND_RESET_GOAL_ROT + 3],
+              rnd[ids, ko.RND_OBJ_POS:ko.RND_OBJ_POS + 3], rnd[ids, ko.RND_OBJ_ROT:ko.RND_OBJ_ROT + 3], rnd[ids, ko.RND_FORCE_PROB],
+              rnd[ids, ko.RND_DOF_POS:ko.RND_DOF_POS + D], rnd[ids, ko.RND_DOF_POS + D:ko.RND_DOF_POS + 2 * D]]
+        pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
+        prob[ids] = torch.exp((torch.log(pr[0]) - torch.log(pr[1])) * rnd[ids, ko.RND_FORCE_PROB] + torch.log(pr[1]))
+    if c.force_scale > 0.0:
+        q.append(rnd[:, ko.RND_FORCE_TEST])
+        hit = (rnd[:, ko.RND_FORCE_TEST] < prob).nonzero(as_tuple=False)
+        q.append(rnd[hit.squeeze(-1), ko.RND_FORCE_NORMAL:ko.RND_FORCE_NORMAL + 3].unsqueeze(1))
+    return q
+
+
+def reference_kuka_step(env, c, actions: torch.Tensor, rnd: torch.Tensor, st: Dict[str, torch.Tensor]) -> None:
+    """pre_physics_step + post_physics_step + the VecTask.step tail (vec_task.py:424) of the reference."""
+    with scripted_randoms(kuka_random_queue(st, c, rnd)) as q:
+        env.pre_physics_step(actions)
+        assert len(q) == 0, f"{len(q)} scripted random tensors were not consumed"
+    env.post_physics_step()
+    env.timeout_buf = (env.progress_buf >= env.max_episode_length - 1) & (env.reset_buf != 0)
+
+
+def harvest(env, st: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Copy the attributes the reference REBINDS (instead of mutating in place) back into a state dict."""
+    out = dict(st)
+    for name in ("progress_buf", "successes", "true_objective", "near_goal_steps", "lifted_object", "closest_keypoint_max_dist",
+                 "closest_fingertip_dist", "furthest_hand_dist", "timeout_buf", "reset_buf", "reset_goal_buf", "randomize_buf",
+                 "prev_episode_successes", "prev_episode_true_objective", "random_force_prob", "obs_buf", "rew_buf"):
+        out[name] = getattr(env, name)
+    out["actions"] = env.actions
+    out["rewards_episode"] = torch.stack([env.rewards_episode[k] for k in KUKA_EPISODE_KEYS])
+    cum = env.extras.get("episode_cumulative")
+    if cum is not None:
+        from .kuka_oracle import STEP_TERMS
+        out["episode_cumulative"] = torch.stack([cum[k] for k in STEP_TERMS])
+    return out

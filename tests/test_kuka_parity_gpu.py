@@ -1,0 +1,175 @@
+"""Parity of the fused CUDA kernels (through the VecTask surface -> C-ABI) against the CPU oracle.
+
+Tolerances (north star): flag / counter / index buffers bit-exact; observations and rewards within
+1e-5 relative in fp32 (an absolute floor of 2e-6 covers outputs that are differences of O(1)
+positions, where one ulp of the operands is the floor of any fp32 implementation, and the last-ulp
+freedom of log / sin / cos / exp).
+"""
+import pytest
+import torch
+
+from oracle import kuka_oracle as ko
+from oracle import kuka_state as ks
+from tests import kuka_harness as kh
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-5, 2e-6
+EXACT = ["reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf", "timeout_buf", "near_goal_steps", "lifted_object"]
+FLOAT = ["obs_buf", "rew_buf", "successes", "prev_episode_successes", "true_objective", "prev_episode_true_objective",
+         "closest_keypoint_max_dist", "closest_fingertip_dist", "furthest_hand_dist", "prev_targets", "cur_targets", "actions",
+         "rb_forces", "random_force_prob", "rewards_episode", "episode_cumulative", "goal_states", "root_state", "dof_state"]
+
+
+def assert_state_close(got, want, keys_exact=EXACT, keys_float=FLOAT, ctx=""):
+    for k in keys_exact:
+        assert torch.equal(got[k].long(), want[k].long()), f"{ctx}{k}: {(got[k].long() != want[k].long()).sum()} mismatches"
+    for k in keys_float:
+        g, w = got[k].float().reshape(-1), want[k].float().reshape(-1)
+        bad = ~torch.isclose(g, w, rtol=RTOL, atol=ATOL)
+        assert not bad.any(), f"{ctx}{k}: {int(bad.sum())} of {g.numel()} beyond tolerance, worst |d|={(g - w).abs().max():.3e}"
+
+
+def run_both(n, seed, fresh, steps=2, overrides=None, consts=None):
+    c = consts or ko.KukaConsts()
+    st = ks.make_state(n, seed=seed, c=c, fresh=fresh)
+    task = kh.make_task(n, overrides=overrides)
+    kh.load_state(task, st)
+    for step in range(steps):
+        act, rnd = ks.make_actions(n, seed + step), ks.make_rnd(n, seed + step)
+        lists = ko.pre_step(st, c, act, rnd)
+        task.ext_rand = rnd.cuda()
+        task.pre_physics_step(act.cuda())
+        got = kh.dump_state(task)
+        ctx = f"[n={n} seed={seed} fresh={fresh} step={step} pre] "
+        assert_state_close(got, st, keys_exact=["reset_buf", "reset_goal_buf", "progress_buf", "near_goal_steps", "lifted_object"],
+                           keys_float=[k for k in FLOAT if k not in ("obs_buf", "rew_buf", "episode_cumulative")], ctx=ctx)
+        assert torch.equal(torch.sort(got["root_rows"]).values, lists["root_rows"]), ctx + "root reset rows"
+        assert torch.equal(torch.sort(got["hand_rows"]).values, lists["hand_rows"]), ctx + "hand reset rows"
+        info = ko.post_step(st, c)
+        task.post_physics_step()
+        got = kh.dump_state(task)
+        ctx = f"[n={n} seed={seed} fresh={fresh} step={step} post] "
+        assert_state_close(got, st, ctx=ctx)
+        C = kh.AllegroKukaReorientation  # noqa: F841
+        from handarm_b200._lib import CONSTS as K
+        stats = got["stats"]
+        assert stats[K["HA_KUKA_STAT_N"]] == n
+        assert torch.isclose(stats[K["HA_KUKA_STAT_SUM_RESETS"]], st["reset_buf"].sum().float())
+        assert torch.isclose(stats[K["HA_KUKA_STAT_MEAN_TRUE_OBJECTIVE"]], info["true_objective_mean"], rtol=1e-5, atol=1e-6)
+        assert torch.isclose(stats[K["HA_KUKA_STAT_MIN_TRUE_OBJECTIVE"]], info["true_objective_min"])
+        assert torch.isclose(stats[K["HA_KUKA_STAT_MAX_TRUE_OBJECTIVE"]], info["true_objective_max"])
+        assert torch.isclose(stats[K["HA_KUKA_STAT_MEAN_PREV_EP_SUCCESSES"]], info["successes_mean"], rtol=1e-5, atol=1e-6)
+        assert torch.isclose(stats[K["HA_KUKA_STAT_MEAN_REWARD"]], st["rew_buf"].mean(), rtol=1e-4, atol=1e-4)
+        assert torch.isclose(stats[K["HA_KUKA_STAT_SUM_SUCCESS_EVENTS"]], info["is_success"].sum().float())
+    return task, st
+
+
+@pytest.mark.parametrize("n", [32, 1, 33, 1000, 4096])
+@pytest.mark.parametrize("fresh", [True, False])
+def test_kuka_step_matches_oracle(n, fresh):
+    run_both(n, seed=11 + n, fresh=fresh, steps=3)
+
+
+def test_kuka_success_steps_and_no_forces():
+    """regrasping-like scalars: successSteps 30, episodeLength 300, forces off."""
+    c = ko.KukaConsts(success_steps=30, max_episode_length=300, force_scale=0.0)
+    run_both(777, seed=5, fresh=False, steps=2, consts=c,
+             overrides={"env.successSteps": 30, "env.episodeLength": 300, "env.forceScale": 0.0})
+
+
+def test_kuka_all_reset_and_none_reset():
+    n = 257
+    for mode in ("all", "none"):
+        c = ko.KukaConsts()
+        st = ks.make_state(n, seed=2, c=c, fresh=False)
+        st["reset_buf"][:] = 1 if mode == "all" else 0
+        st["reset_goal_buf"][:] = 0
+        task = kh.make_task(n)
+        kh.load_state(task, st)
+        act, rnd = ks.make_actions(n, 1), ks.make_rnd(n, 1)
+        lists = ko.pre_step(st, c, act, rnd)
+        task.ext_rand = rnd.cuda()
+        task.pre_physics_step(act.cuda())
+        got = kh.dump_state(task)
+        assert got["hand_rows"].numel() == (n if mode == "all" else 0)
+        assert torch.equal(torch.sort(got["root_rows"]).values, lists["root_rows"])
+        ko.post_step(st, c)
+        task.post_physics_step()
+        assert_state_close(kh.dump_state(task), st, ctx=f"[{mode}] ")
+
+
+def test_kuka_boundaries():
+    """Exact threshold values: kp_max == tol (<=), z_lift == threshold (strict >), progress == max_len-2/-1, z == 0.1."""
+    n = 64
+    c = ko.KukaConsts()
+    st = ks.make_state(n, seed=9, c=c, fresh=False)
+    st["reset_buf"][:] = 0
+    st["reset_goal_buf"][:] = 0
+    st["progress_buf"][0:8] = torch.tensor([597, 598, 599, 600, 0, 1, 596, 598])
+    obj = st["root_state"].view(n, 4, 13)
+    obj[8, 1, 2] = 0.1            # not < 0.1 -> no fall reset
+    obj[9, 1, 2] = 0.09999999
+    obj[10, 1, 2] = st["object_init_state"][10, 2] + 0.1     # z_lift == 0.15 in exact arithmetic
+    obj[11, 1, 0:7] = st["goal_states"][11, 0:7]             # kp_max == 0 -> success
+    st["rigid_body_state"].view(n, 27, 13)[:, c.object_body] = obj[:, 1]
+    st["successes"][12] = 49.0
+    obj[12, 1, 0:7] = st["goal_states"][12, 0:7]             # 50th success -> reset
+    # antipodal quaternion (q and -q are the same rotation)
+    obj[13, 1, 3:7] = -obj[13, 1, 3:7]
+    task = kh.make_task(n)
+    kh.load_state(task, st)
+    act, rnd = ks.make_actions(n, 4), ks.make_rnd(n, 4)
+    ko.pre_step(st, c, act, rnd)
+    task.ext_rand = rnd.cuda()
+    task.pre_physics_step(act.cuda())
+    ko.post_step(st, c)
+    task.post_physics_step()
+    got = kh.dump_state(task)
+    assert_state_close(got, st)
+    assert got["reset_buf"][12] == 1 and got["reset_goal_buf"][11] == 1 and got["reset_buf"][8] == 0 and got["reset_buf"][9] == 1
+
+
+def test_kuka_observe_only_matches_oracle():
+    n = 500
+    c = ko.KukaConsts()
+    st = ks.make_state(n, seed=21, c=c, fresh=False)
+    task = kh.make_task(n)
+    kh.load_state(task, st)
+    ko.observe(st, c)
+    task.compute_observations()
+    got = kh.dump_state(task)
+    assert_state_close(got, st, keys_exact=["reset_buf", "progress_buf"],
+                       keys_float=["obs_buf", "closest_keypoint_max_dist", "closest_fingertip_dist", "furthest_hand_dist"])
+
+
+def test_kuka_fast_rng_statistics():
+    """In-kernel Philox mode: reset poses land in the documented ranges and are reproducible per seed."""
+    n = 8192
+    task = kh.make_task(n)
+    task.sim.fill_kuka(goal_states=None)
+    task.seed_rng(123)
+    act = torch.zeros(n, 23, device="cuda")
+    task.pre_physics_step(act)          # fresh task: every env resets
+    torch.cuda.synchronize()
+    goal = task.goal_states[:, 0:3].cpu()
+    lo = torch.tensor([-0.4, 0.0, 0.68])
+    hi = torch.tensor([0.4, 0.35, 1.05])
+    assert (goal >= lo - 1e-5).all() and (goal <= hi + 1e-5).all()
+    assert abs(goal[:, 0].mean()) < 0.02 and abs(goal[:, 0].std() - 0.8 / 12 ** 0.5) < 0.01
+    q = task.goal_states[:, 3:7].cpu()
+    assert torch.allclose(q.norm(dim=-1), torch.ones(n), atol=1e-5)
+    assert q.mean(dim=0).abs().max() < 0.03        # uniform on SO(3): zero-mean components
+    dof = task.sim.dof_state.view(n, 23, 2).cpu()
+    assert (dof[..., 1].abs() <= 0.5 + 1e-6).all() and abs(dof[..., 1].mean()) < 0.01
+    assert int(task.reset_counts[1]) == n and int(task.reset_counts[0]) == 2 * n
+    first = task.goal_states.clone()
+    task2 = kh.make_task(n)
+    task2.sim.fill_kuka(goal_states=None)
+    task2.seed_rng(123)
+    task2.pre_physics_step(act)
+    assert torch.equal(first, task2.goal_states)
+    task3 = kh.make_task(n)
+    task3.seed_rng(124)
+    task3.pre_physics_step(act)
+    assert not torch.equal(first, task3.goal_states)
