@@ -1,0 +1,38 @@
+"""Loads the reference-generated fixtures of ``tests/golden`` (made by ``oracle/make_golden.py``)."""
+from __future__ import annotations
+
+import glob
+import os
+from typing import Dict, List, Tuple
+
+import numpy as np
+import torch
+
+from oracle import kuka_oracle as ko
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+INT_CONSTS = {"success_steps", "max_episode_length", "max_consecutive_successes"}
+
+
+def fixture_names() -> List[str]:
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "kuka_*.npz")))
+
+
+def load_fixture(name: str):
+    """-> (consts, input state dict, [per-step dict(actions, rnd, pre={...}, post={...}, extras={...})])"""
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    over = {}
+    for k in z.files:
+        if k.startswith("consts/"):
+            key = k.split("/", 1)[1]
+            over[key] = int(z[k]) if key in INT_CONSTS else float(z[k])
+    c = ko.KukaConsts(**over)
+    st = {k.split("/", 1)[1]: torch.from_numpy(z[k].copy()) for k in z.files if k.startswith("in/")}
+    steps = []
+    for i in range(int(z["meta/steps"])):
+        d: Dict[str, object] = {"actions": torch.from_numpy(z[f"s{i}/actions"].copy()), "rnd": torch.from_numpy(z[f"s{i}/rnd"].copy())}
+        for phase in ("pre", "post", "extras"):
+            pre = f"s{i}/{phase}/"
+            d[phase] = {k[len(pre):]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith(pre)}
+        steps.append(d)
+    return c, st, steps
