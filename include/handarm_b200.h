@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define HA_ABI_VERSION 1
+#define HA_ABI_VERSION 2
 
 #define HA_OK 0
 #define HA_ERR_INVALID (-1)   /* bad argument / unsupported dimension */
@@ -111,7 +111,13 @@ typedef struct HaKukaParams {
   int32_t success_steps;
   int32_t use_fast_rng;     /* 0: consume ext_rand, 1: in-kernel Philox */
   int32_t force_enabled;    /* force_scale > 0 */
-  int32_t reserved_i[4];
+  /* root_regular != 0: the actor rows follow Isaac Gym's regular numbering
+   * row(env, slot) = env * actors_per_env + slot, so the gather needs no
+   * dependent index load; the host verifies this against the index tables */
+  int32_t root_regular;
+  int32_t actors_per_env;
+  int32_t object_slot;
+  int32_t goal_slot;
 
   float palm_offset[3];
   float tip_offset[HA_MAX_TIPS][3];
@@ -149,7 +155,7 @@ typedef struct HaKukaDynamic {
   float true_objective_offset;
   float pad0;
   uint64_t rng_seed;
-  uint64_t rng_step;                 /* advanced by ha_kuka_pre_step when use_fast_rng */
+  uint64_t rng_step;                 /* one tick per ha_kuka_post_step / ha_kuka_reset_idx (fast RNG mode) */
 } HaKukaDynamic;
 
 typedef struct HaKukaBuffers {
@@ -198,7 +204,8 @@ typedef struct HaKukaBuffers {
   int32_t* reset_counts;        /* [4]: n_root, n_hand, n_reset_envs, n_goal_resets */
   /* ---- reductions ---- */
   float* stats;                 /* [HA_STATS_LEN], see HA_KUKA_STAT_* */
-  float* scratch;               /* [ha_kuka_scratch_floats(n_envs)] */
+  int64_t* stat_accum;          /* [HA_STATS_LEN] fixed-point accumulators; initialise once with ha_kuka_stat_accum_init(i):
+                                   0 for sums, INT32_MIN for the two MAX slots (the kernel re-arms them itself) */
   uint32_t* tickets;            /* [8], zero-initialised once by the caller */
   /* ---- dynamic scalars ---- */
   HaKukaDynamic* dynamic;       /* device */
@@ -237,7 +244,8 @@ int ha_kuka_obs_dim(int n_arms, int n_keypoints);
 size_t ha_kuka_bytes_per_env_step(const HaKukaParams* p);
 size_t ha_kuka_post_bytes_per_env_step(const HaKukaParams* p);
 size_t ha_kuka_pre_bytes_per_env_step(const HaKukaParams* p);
-size_t ha_kuka_scratch_floats(int n_envs);
+/* initial value of stat_accum[i] (host writes these once before the first post step) */
+int64_t ha_kuka_stat_accum_init(int i);
 
 /* pre_physics_step: consume reset / reset_goal masks, reset scatter and
  * re-randomisation, action -> DOF targets, random forces.

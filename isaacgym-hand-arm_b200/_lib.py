@@ -129,8 +129,10 @@ def load():
     lib = ctypes.CDLL(LIB_PATH)
     lib.ha_last_error.restype = ctypes.c_char_p
     for fn in ("ha_sizeof_kuka_params", "ha_sizeof_kuka_buffers", "ha_sizeof_kuka_dynamic", "ha_kuka_bytes_per_env_step",
-               "ha_kuka_post_bytes_per_env_step", "ha_kuka_pre_bytes_per_env_step", "ha_kuka_scratch_floats"):
+               "ha_kuka_post_bytes_per_env_step", "ha_kuka_pre_bytes_per_env_step"):
         getattr(lib, fn).restype = ctypes.c_size_t
+    lib.ha_kuka_stat_accum_init.restype = ctypes.c_int64
+    lib.ha_kuka_stat_accum_init.argtypes = [ctypes.c_int]
     if lib.ha_abi_version() != CONSTS["HA_ABI_VERSION"]:
         raise HandArmLibraryError(f"ABI mismatch: library {lib.ha_abi_version()} vs header {CONSTS['HA_ABI_VERSION']}")
     for cls, fn in ((HaKukaParams, lib.ha_sizeof_kuka_params), (HaKukaBuffers, lib.ha_sizeof_kuka_buffers),
@@ -140,7 +142,7 @@ def load():
     lib.ha_kuka_pre_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_post_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_observe.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
-    lib.ha_kuka_scratch_floats.argtypes = [ctypes.c_int]
+    lib.ha_kuka_reset_idx.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_obs_dim.argtypes = [ctypes.c_int, ctypes.c_int]
     for fn in ("ha_kuka_bytes_per_env_step", "ha_kuka_post_bytes_per_env_step", "ha_kuka_pre_bytes_per_env_step"):
         getattr(lib, fn).argtypes = [ctypes.c_void_p]

@@ -30,13 +30,19 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
                         b->prev_episode_successes, b->true_objective, b->prev_episode_true_objective, b->near_goal_steps,
                         b->lifted_object, b->closest_keypoint_max_dist, b->closest_fingertip_dist, b->furthest_hand_dist,
                         b->rewards_episode, b->episode_cumulative, b->prev_targets, b->cur_targets, b->actions, b->rb_forces,
-                        b->random_force_prob, b->root_reset_indices, b->hand_reset_indices, b->reset_counts, b->stats, b->scratch,
+                        b->random_force_prob, b->root_reset_indices, b->hand_reset_indices, b->reset_counts, b->stats, b->stat_accum,
                         b->tickets, b->dynamic};
   for (size_t i = 0; i < sizeof(need) / sizeof(need[0]); ++i) HA_REQUIRE(need[i] != nullptr, "HaKukaBuffers field #%zu is null", i);
   HA_REQUIRE_ALIGNED16(b->dof_state);
   HA_REQUIRE_ALIGNED16(b->obs_buf);
   HA_REQUIRE_ALIGNED16(b->closest_fingertip_dist);
   HA_REQUIRE_ALIGNED16(b->finger_rew_coeffs);
+  HA_REQUIRE_ALIGNED16(b->prev_targets);
+  HA_REQUIRE_ALIGNED16(b->cur_targets);
+  HA_REQUIRE_ALIGNED16(b->actions);
+  if (p->root_regular)
+    HA_REQUIRE(p->actors_per_env > 0 && p->object_slot >= 0 && p->object_slot < p->actors_per_env && p->goal_slot < p->actors_per_env,
+               "root_regular needs 0 <= object_slot, goal_slot < actors_per_env");
   return HA_OK;
 }
 
@@ -90,15 +96,13 @@ size_t ha_kuka_bytes_per_env_step(const HaKukaParams* p) {
   return ha_kuka_post_bytes_per_env_step(p) + ha_kuka_pre_bytes_per_env_step(p);
 }
 
-size_t ha_kuka_scratch_floats(int n_envs) {
-  const size_t ctas = ((size_t)n_envs + HA_ENVS_PER_CTA - 1) / HA_ENVS_PER_CTA;
-  return ctas * HA_STATS_LEN;
-}
+int64_t ha_kuka_stat_accum_init(int i) { return ha::stat_is_max(i) ? (int64_t)ha::kStatMaxInit : 0; }
 
 int ha_kuka_pre_step(const HaKukaParams* p, const HaKukaBuffers* b, const float* actions, const float* ext_rand, ha_stream_t stream) {
   int rc = validate_kuka(p, b);
   if (rc) return rc;
   HA_REQUIRE(actions != nullptr, "actions is null");
+  HA_REQUIRE(ha::aligned16(actions), "actions must be 16-byte aligned");
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
   ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, actions, ext_rand, ha::kPreFull);
@@ -111,6 +115,7 @@ int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
   ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);
+  if (p->use_fast_rng) ha::kuka_rng_tick_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(b->dynamic);
   return ha::check_cuda(cudaGetLastError(), "kuka_pre_kernel(reset_only) launch");
 }
 

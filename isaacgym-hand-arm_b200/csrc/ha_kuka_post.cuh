@@ -4,15 +4,23 @@
 // + _compute_resets (:841-849) + clamp_obs (:1174-1176), plus the VecTask.step
 // tail (vec_task.py:424-432: timeout_buf, obs clip).
 //
-// Mapping: one CTA = a tile of 32 consecutive envs, 128 threads.
-//   phase L  all threads gather the tile's inputs with coalesced loads
-//            (contiguous spans for DOF / keypoint tables, 28..52-byte row
-//            granules for the AoS rigid-body / root rows) into padded smem;
-//   phase C  warp w, lane e: fingertip w and keypoint w of env e (+ one of the
-//            per-env odd jobs); results go to the smem obs tile;
-//   phase R  warp 0, lane e: reward / success / reset logic of env e;
-//   phase S  all threads: episode accumulators (SoA, coalesced) and the obs
-//            tile as one contiguous run of 128-bit stores.
+// Mapping (memory-bound design, no CTA barrier on the data path):
+//   one WARP owns a tile of 8 consecutive envs and runs it start to finish;
+//   lane = part * 8 + e  (e = env in tile, part = fingertip / keypoint index),
+//   i.e. 4 lanes per env so that 32768 envs give 4096 independent warps.
+//   phase L  the warp gathers the tile: contiguous spans (DOF state, keypoint
+//            table, scales) as wide loads, AoS rows (13-float rigid-body /
+//            root rows, 52-byte stride, only 4-byte aligned) with 16 or 8
+//            lanes per row so one request touches 2..4 rows; everything is
+//            issued before anything is consumed;
+//   phase C  lane (part, e): fingertip `part` and keypoint `part` of env e;
+//            the 4 lanes of an env exchange distances with shuffles and all
+//            run the (identical) reward / reset logic;
+//   phase S  per-env outputs are split over the 4 parts (coalesced 32..64-byte
+//            runs); the 8 x obs_dim tile leaves as one contiguous run of
+//            128-bit stores.
+// Episode statistics: warp shuffle -> CTA -> 64-bit fixed-point atomics, so
+// sums are order-independent (bit-reproducible); the last CTA converts them.
 #pragma once
 #include "ha_device.cuh"
 #include "../../include/handarm_b200.h"
@@ -23,8 +31,8 @@ struct KukaLayout {            // obs slot offsets, allegro_kuka_base.py:1091-11
   int dof_pos, dof_vel, palm_pos, palm_rot_vel, obj_rot_vel, tip_rel_palm, kp_rel_palm, kp_rel_goal,
       scales, closest_kp, closest_tip, lifted, progress, successes, reward, dim;
 };
-__host__ __device__ inline KukaLayout kuka_layout(int n_dofs, int n_tips, int K) {
-  KukaLayout l;
+__host__ __device__ constexpr KukaLayout kuka_layout(int n_dofs, int n_tips, int K) {
+  KukaLayout l{};
   int o = 0;
   l.dof_pos = o; o += n_dofs;
   l.dof_vel = o; o += n_dofs;
@@ -48,242 +56,250 @@ __host__ __device__ inline KukaLayout kuka_layout(int n_dofs, int n_tips, int K)
 enum { kPostFull = 0, kPostObserveOnly = 1 };
 
 constexpr int kD1 = 23;              // single arm DOFs
-constexpr int kT1 = 4;               // fingertips
-constexpr int kRbW = 13 + 7 * kT1;   // palm row + (pos,quat) of 4 tips = 41 (odd: conflict-free)
-constexpr int kRedW = 13;            // per-env reduction scratch row (odd)
+constexpr int kT1 = 4;               // fingertips == lanes per env
+constexpr int kTile = 8;             // envs per warp
+constexpr int kWarps = kThreads / 32;
 constexpr int kNPart = HA_KUKA_N_PARTIAL_STATS;
+
+// fixed-point scales of the 64-bit statistic accumulators
+__host__ __device__ constexpr float stat_scale(int i) {
+  return (i == HA_KUKA_STAT_SUM_REWARD) ? 65536.0f : (i == HA_KUKA_STAT_SUM_TRUE_OBJECTIVE) ? 1048576.0f : 1.0f;
+}
+__host__ __device__ constexpr bool stat_is_max(int i) {
+  return i == HA_KUKA_STAT_MAX_TRUE_OBJECTIVE || i == HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE;
+}
+// order-preserving float <-> int64 key (for atomicMax on signed integers)
+__device__ __forceinline__ long long float_key(float f) {
+  const int b = __float_as_int(f);
+  return (long long)(b >= 0 ? b : (b ^ 0x7fffffff));
+}
+__device__ __forceinline__ float key_float(long long k) {
+  const int b = (int)k;
+  return __int_as_float(b >= 0 ? b : (b ^ 0x7fffffff));
+}
+constexpr long long kStatMaxInit = -0x7fffffffLL - 1;   // below every float key
+
+template <int K>
+struct KukaPostWarpSmem {
+  static constexpr int kObs = kuka_layout(kD1, kT1, K).dim;
+  float obs[kTile * kObs];          // row-major tile, leaves as one contiguous run
+  float palm[kTile * 13];
+  float tip[kTile * kT1 * 7];       // [(e * 4 + t) * 7 + c]: pos3 quat4
+  float obj[kTile * 13];
+  float goal[kTile * 7];
+  float kp[kTile * 3 * K];
+  float lo[kD1 + 1], hi[kD1 + 1];   // per-DOF limits (no divergent constant-bank reads in the loops)
+};
 
 template <int K>
 struct KukaPostSmem {
-  static constexpr int kObs = 2 * kD1 + 3 + 10 + 10 + 3 * kT1 + 6 * K + 3 + 1 + kT1 + 1 + 1 + 1 + 1;
-  float obs[kEnvsPerCta * kObs];     // flat row-major tile, stored contiguously
-  float rb[kEnvsPerCta * kRbW];
-  float obj[kEnvsPerCta * 13];
-  float goal[kEnvsPerCta * 7];
-  float kp[kEnvsPerCta * (3 * K | 1)];
-  float red[kEnvsPerCta * kRedW];    // [0:4] tip dist, [4:8] kp dist, [8] sum|v arm|, [9] sum|v hand|
-  float terms[HA_KUKA_N_EPISODE_TERMS * kEnvsPerCta];
-  float part[4 * 16];
+  KukaPostWarpSmem<K> w[kWarps];
+  float part[kWarps][kNPart];
   int last_flag;
 };
 
 template <int K>
-__global__ void __launch_bounds__(kThreads, 8)
+__global__ void __launch_bounds__(kThreads, 7)
 kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b, const int mode) {
   using Smem = KukaPostSmem<K>;
-  constexpr int OBS = Smem::kObs;
-  constexpr int KPW = (3 * K) | 1;
+  using WS = KukaPostWarpSmem<K>;
+  constexpr int OBS = WS::kObs;
+  constexpr KukaLayout L = kuka_layout(kD1, kT1, K);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  Smem& s = *reinterpret_cast<Smem*>(smem_raw);
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int env0 = blockIdx.x * kEnvsPerCta;
+  WS& s = sm.w[warp];
   const int n = p.n_envs;
-  const int nvalid = min(kEnvsPerCta, n - env0);
-  const KukaLayout L = kuka_layout(kD1, kT1, K);
-  const int env = env0 + lane;
-  const bool valid = lane < nvalid;
+  const int env0 = (blockIdx.x * kWarps + warp) * kTile;
+  const int nvalid = min(kTile, n - env0);          // <= 0: this warp has no tile
+  const int part = lane >> 3, el = lane & 7;        // compute mapping: 4 lanes per env
+  const bool valid = el < nvalid;
+  const unsigned FULL = 0xffffffffu;
 
-  // ------------------------------ phase L ---------------------------------
-  // per-env scalars of the reward phase go straight to registers of warp 0;
-  // issue them first so they are in flight during the tile gather.
-  long long r_progress = 0, r_reset = 0;
-  float r_succ = 0.f, r_ckp = 0.f, r_furthest = 0.f, r_initz = 0.f, r_prev_ep = 0.f, r_old_rew_obs = 0.f;
-  int r_near = 0;
-  unsigned char r_lifted = 0;
-  float4 r_ctip = make_float4(0.f, 0.f, 0.f, 0.f), r_coef = make_float4(1.f, 1.f, 1.f, 1.f);
-  if (warp == 0 && valid) {
-    r_progress = b.progress_buf[env];
-    r_reset = b.reset_buf[env];
-    r_succ = b.successes[env];
-    r_ckp = b.closest_keypoint_max_dist[env];
-    r_furthest = b.furthest_hand_dist[env];
-    r_near = b.near_goal_steps[env];
-    r_lifted = b.lifted_object[env];
-    r_initz = ldg(b.object_init_state + (size_t)env * 13 + 2);
-    r_prev_ep = b.prev_episode_successes[env];
-    r_ctip = *reinterpret_cast<const float4*>(b.closest_fingertip_dist + (size_t)env * 4);
-    r_coef = __ldg(reinterpret_cast<const float4*>(b.finger_rew_coeffs + (size_t)env * 4));
-    if (mode == kPostObserveOnly) r_old_rew_obs = b.obs_buf[(size_t)env * OBS + L.reward];
-  }
-  // episode accumulators: warp w owns terms w, w+4, w+8
-  float r_acc[3] = {0.f, 0.f, 0.f};
-  if (mode == kPostFull && valid) {
-#pragma unroll
-    for (int j = 0; j < 3; ++j) r_acc[j] = b.rewards_episode[(size_t)(warp + 4 * j) * n + env];
-  }
+  // per-env results that feed the statistics (stay 0 / -inf for idle lanes)
+  float st_reward = 0.f, st_resets = 0.f, st_success = 0.f, st_prev_ep = 0.f, st_tobj = 0.f, st_timeout = 0.f, st_lifted = 0.f;
+  bool st_valid = false;
 
-  // DOF tile: [nvalid, 23, 2] contiguous, base 16-byte aligned when env0 % 2 == 0
-  {
-    const float* src = b.dof_state + (size_t)env0 * (2 * kD1);
-    const int total = nvalid * 2 * kD1;
-    constexpr int kVecIters = (kEnvsPerCta * 2 * kD1 / 4 + kThreads - 1) / kThreads;  // 3
-    float4 v[kVecIters];
-    const int nvec = total >> 2;
+  if (nvalid > 0) {
+    const int last = nvalid - 1;
+    const int env = env0 + min(el, last);           // clamped: idle lanes re-read a valid env, stores are predicated
+    // ------------------------------ phase L ---------------------------------
+    if (lane < kD1) { s.lo[lane] = p.dof_lower[lane]; s.hi[lane] = p.dof_upper[lane]; }
+
+    // AoS rows.  16 lanes per 13-float row (2 rows / request), 8 lanes per 7-float row (4 rows / request).
+    const int h16 = lane >> 4, c16 = lane & 15;
+    const int r8 = lane >> 3, c8 = lane & 7;
+    const size_t rb_env_stride = (size_t)p.n_bodies * 13;
+    const float* rb0 = b.rigid_body_state + (size_t)env0 * rb_env_stride;
+    float palm_v[4], obj_v[4], tip_v[8], goal_v[2];
+    {
+      const float* src = rb0 + (size_t)p.palm_body[0] * 13 + min(c16, 12);
 #pragma unroll
-    for (int i = 0; i < kVecIters; ++i) {
-      const int q = tid + i * kThreads;
-      if (q < nvec) v[i] = __ldg(reinterpret_cast<const float4*>(src) + q);
+      for (int i = 0; i < 4; ++i) palm_v[i] = ldg(src + (size_t)min(2 * i + h16, last) * rb_env_stride);
     }
-    // rigid-body rows: palm (13 floats) + 4 tips (7 floats each) per env
-    constexpr int kRbIters = (kEnvsPerCta * kRbW + kThreads - 1) / kThreads;  // 11
-    float rbv[kRbIters];
-    const float* rb = b.rigid_body_state + (size_t)env0 * p.n_bodies * 13;
+    {
 #pragma unroll
-    for (int i = 0; i < kRbIters; ++i) {
-      const int idx = tid + i * kThreads;
-      const int e = idx / kRbW, j = idx - e * kRbW;
-      int body, c;
-      if (j < 13) { body = p.palm_body[0]; c = j; }
-      else { const int t = (j - 13) / 7; c = (j - 13) - 7 * t; body = p.tip_body[t]; }
-      rbv[i] = (e < nvalid) ? ldg(rb + ((size_t)e * p.n_bodies + body) * 13 + c) : 0.f;
-    }
-    // object root row (13) and goal pose (7)
-    constexpr int kObjIters = (kEnvsPerCta * 13 + kThreads - 1) / kThreads;  // 4
-    float ov[kObjIters];
-#pragma unroll
-    for (int i = 0; i < kObjIters; ++i) {
-      const int idx = tid + i * kThreads;
-      const int e = idx / 13, c = idx - e * 13;
-      ov[i] = 0.f;
-      if (e < nvalid) {
-        const int row = __ldg(b.object_actor + env0 + e);
-        ov[i] = b.root_state[(size_t)row * 13 + c];
+      for (int i = 0; i < 4; ++i) {
+        const int e = env0 + min(2 * i + h16, last);
+        const int row = p.root_regular ? e * p.actors_per_env + p.object_slot : __ldg(b.object_actor + e);
+        obj_v[i] = b.root_state[(size_t)row * 13 + min(c16, 12)];
       }
     }
-    constexpr int kGoalIters = (kEnvsPerCta * 7 + kThreads - 1) / kThreads;  // 2
-    float gv[kGoalIters];
+    {
+      const float* src = rb0 + (size_t)p.tip_body[r8] * 13 + min(c8, 6);
 #pragma unroll
-    for (int i = 0; i < kGoalIters; ++i) {
-      const int idx = tid + i * kThreads;
-      const int e = idx / 7, c = idx - e * 7;
-      gv[i] = (e < nvalid) ? b.goal_states[(size_t)(env0 + e) * 13 + c] : 0.f;
+      for (int i = 0; i < 8; ++i) tip_v[i] = ldg(src + (size_t)min(i, last) * rb_env_stride);
     }
-    constexpr int kKpIters = (kEnvsPerCta * 3 * K + kThreads - 1) / kThreads;
-    float kv[kKpIters];
+    {
+#pragma unroll
+      for (int i = 0; i < 2; ++i) goal_v[i] = b.goal_states[(size_t)(env0 + min(4 * i + r8, last)) * 13 + min(c8, 6)];
+    }
+    // contiguous spans: DOF state [nvalid, 23, 2], keypoint table [nvalid, K, 3], scales [nvalid, 3]
+    const float* dof_src = b.dof_state + (size_t)env0 * (2 * kD1);
+    const int dof_total = nvalid * 2 * kD1, dof_nvec = dof_total >> 2;
+    float4 dof_v[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int q = lane + 32 * i;
+      dof_v[i] = (q < dof_nvec) ? __ldg(reinterpret_cast<const float4*>(dof_src) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float dof_tail = 0.f;                             // odd nvalid leaves 2 floats after the last float4
+    if ((dof_nvec << 2) + lane < dof_total) dof_tail = ldg(dof_src + (dof_nvec << 2) + lane);
+    constexpr int kKpIters = (kTile * 3 * K + 31) / 32;
+    float kp_v[kKpIters];
 #pragma unroll
     for (int i = 0; i < kKpIters; ++i) {
-      const int idx = tid + i * kThreads;
-      kv[i] = (idx < nvalid * 3 * K) ? ldg(b.object_keypoint_offsets + (size_t)env0 * 3 * K + idx) : 0.f;
+      const int idx = lane + 32 * i;
+      kp_v[i] = (idx < nvalid * 3 * K) ? ldg(b.object_keypoint_offsets + (size_t)env0 * 3 * K + idx) : 0.f;
     }
+    const float scale_v = (lane < nvalid * 3) ? ldg(b.object_scales + (size_t)env0 * 3 + lane) : 0.f;
 
-    // ---- all loads issued; now scatter into smem ----
+    // per-env scalars (all 4 lanes of an env read the same words: one sector per request)
+    const long long r_progress = b.progress_buf[env];
+    const long long r_reset = b.reset_buf[env];
+    const float r_succ = b.successes[env];
+    const float r_ckp = b.closest_keypoint_max_dist[env];
+    const float r_furthest = b.furthest_hand_dist[env];
+    const int r_near = b.near_goal_steps[env];
+    const unsigned char r_lifted = b.lifted_object[env];
+    const float r_initz = ldg(b.object_init_state + (size_t)env * 13 + 2);
+    const float r_prev_ep = b.prev_episode_successes[env];
+    const float4 r_ctip = *reinterpret_cast<const float4*>(b.closest_fingertip_dist + (size_t)env * 4);
+    const float4 r_coef = __ldg(reinterpret_cast<const float4*>(b.finger_rew_coeffs + (size_t)env * 4));
+    float r_old_rew_obs = 0.f;
+    if (mode == kPostObserveOnly) r_old_rew_obs = b.obs_buf[(size_t)env * OBS + L.reward];
+    float r_acc[3] = {0.f, 0.f, 0.f};                  // episode accumulators: part p owns terms p, p+4, p+8
+    long long r_randomize = 0;
+    if (mode == kPostFull) {
 #pragma unroll
-    for (int i = 0; i < kVecIters; ++i) {
-      const int q = tid + i * kThreads;
-      if (q < nvec) {
-        const float vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+      for (int j = 0; j < 3; ++j) r_acc[j] = b.rewards_episode[(size_t)(part + 4 * j) * n + env];
+      if (b.randomize_buf && part == 1) r_randomize = b.randomize_buf[env];
+    }
+    const float keypoint_tol = b.dynamic->keypoint_success_tolerance;
+    const float tobj_scale = b.dynamic->true_objective_scale, tobj_offset = b.dynamic->true_objective_offset;
+
+    // ---- all loads issued; scatter into the warp's smem ----
+    __syncwarp();                                     // lo / hi visible
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const int f = 4 * q + c;
-          const int e = f / (2 * kD1), r = f - e * (2 * kD1);
-          const int d = r >> 1;
-          // dof_pos -> unscale (allegro_kuka_base.py:1095-1100); dof_vel raw (:1104)
-          s.obs[e * OBS + ((r & 1) ? L.dof_vel + d : L.dof_pos + d)] =
-              (r & 1) ? vv[c] : unscale_from(vv[c], p.dof_lower[d], p.dof_upper[d]);
+    for (int i = 0; i < 4; ++i) {
+      const int e = 2 * i + h16;
+      if (c16 < 13) {
+        s.palm[e * 13 + c16] = palm_v[i];
+        s.obj[e * 13 + c16] = obj_v[i];
+        if (c16 >= 3) {                               // palm rot + vel (:1112-1117), object rot + vel (:1120)
+          s.obs[e * OBS + L.palm_rot_vel + c16 - 3] = palm_v[i];
+          s.obs[e * OBS + L.obj_rot_vel + c16 - 3] = obj_v[i];
         }
       }
     }
-    for (int f = (nvec << 2) + tid; f < total; f += kThreads) {  // tail of a ragged last tile
-      const int e = f / (2 * kD1), r = f - e * (2 * kD1), d = r >> 1;
-      const float x = src[f];
-      s.obs[e * OBS + ((r & 1) ? L.dof_vel + d : L.dof_pos + d)] = (r & 1) ? x : unscale_from(x, p.dof_lower[d], p.dof_upper[d]);
-    }
 #pragma unroll
-    for (int i = 0; i < kRbIters; ++i) {
-      const int idx = tid + i * kThreads;
-      if (idx < kEnvsPerCta * kRbW) s.rb[idx] = rbv[i];
-    }
+    for (int i = 0; i < 8; ++i)
+      if (c8 < 7) s.tip[(i * kT1 + r8) * 7 + c8] = tip_v[i];
 #pragma unroll
-    for (int i = 0; i < kObjIters; ++i) {
-      const int idx = tid + i * kThreads;
-      if (idx < kEnvsPerCta * 13) s.obj[idx] = ov[i];
-    }
-#pragma unroll
-    for (int i = 0; i < kGoalIters; ++i) {
-      const int idx = tid + i * kThreads;
-      if (idx < kEnvsPerCta * 7) s.goal[idx] = gv[i];
-    }
+    for (int i = 0; i < 2; ++i)
+      if (c8 < 7) s.goal[(4 * i + r8) * 7 + c8] = goal_v[i];
 #pragma unroll
     for (int i = 0; i < kKpIters; ++i) {
-      const int idx = tid + i * kThreads;
-      if (idx < kEnvsPerCta * 3 * K) { const int e = idx / (3 * K); s.kp[e * KPW + (idx - e * 3 * K)] = kv[i]; }
+      const int idx = lane + 32 * i;
+      if (idx < kTile * 3 * K) s.kp[idx] = kp_v[i];
     }
-  }
-  __syncthreads();
+    if (lane < kTile * 3) { const int e = lane / 3; s.obs[e * OBS + L.scales + (lane - 3 * e)] = scale_v; }   // (:1143)
+    // DOF part of the obs row: unscale(dof_pos) (:1095-1100), raw dof_vel (:1104)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int q = lane + 32 * i;
+      if (q < dof_nvec) {
+        const int g0 = 2 * q;                         // (env, dof) pair index; a float4 holds pairs g0 and g0 + 1
+        const int e0 = g0 / kD1, d0 = g0 - e0 * kD1;
+        const int e1 = (d0 == kD1 - 1) ? e0 + 1 : e0, d1 = (d0 == kD1 - 1) ? 0 : d0 + 1;
+        s.obs[e0 * OBS + L.dof_pos + d0] = unscale_from(dof_v[i].x, s.lo[d0], s.hi[d0]);
+        s.obs[e0 * OBS + L.dof_vel + d0] = dof_v[i].y;
+        s.obs[e1 * OBS + L.dof_pos + d1] = unscale_from(dof_v[i].z, s.lo[d1], s.hi[d1]);
+        s.obs[e1 * OBS + L.dof_vel + d1] = dof_v[i].w;
+      }
+    }
+    if ((dof_nvec << 2) + lane < dof_total) {         // the last (pos, vel) pair of an odd tile
+      const int f = (dof_nvec << 2) + lane;
+      const int e = f / (2 * kD1), r = f - e * (2 * kD1), d = r >> 1;
+      s.obs[e * OBS + ((r & 1) ? L.dof_vel + d : L.dof_pos + d)] = (r & 1) ? dof_tail : unscale_from(dof_tail, s.lo[d], s.hi[d]);
+    }
+    __syncwarp();
 
-  // ------------------------------ phase C ---------------------------------
-  {
-    const float* rb = s.rb + lane * kRbW;
-    const float* ob = s.obj + lane * 13;
-    float* o = s.obs + lane * OBS;
-    const f3 palm_pos = {rb[0], rb[1], rb[2]};
-    const f4 palm_rot = {rb[3], rb[4], rb[5], rb[6]};
+    // ------------------------------ phase C ---------------------------------
+    float* o = s.obs + el * OBS;
+    const float* pr = s.palm + el * 13;
+    const float* ob = s.obj + el * 13;
     // palm_center_pos = palm_pos + quat_rotate(palm_rot, palm_offset)   (:1013-1017)
-    const f3 pc = palm_pos + quat_rotate(palm_rot, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
+    const f3 pc = f3{pr[0], pr[1], pr[2]} + quat_rotate(f4{pr[3], pr[4], pr[5], pr[6]}, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
     const f3 obj_pos = {ob[0], ob[1], ob[2]};
-    // fingertip `warp` (:1033-1052)
-    {
-      const int t = warp;
-      const float* tr = rb + 13 + 7 * t;
-      const f3 tp = {tr[0], tr[1], tr[2]};
-      const f4 tq = {tr[3], tr[4], tr[5], tr[6]};
-      const f3 to = tp + quat_rotate(tq, f3{p.tip_offset[t][0], p.tip_offset[t][1], p.tip_offset[t][2]});
-      const f3 rel_obj = to - obj_pos;
-      const f3 rel_palm = to - pc;
-      s.red[lane * kRedW + t] = norm3(rel_obj);
-      o[L.tip_rel_palm + 3 * t + 0] = rel_palm.x;
-      o[L.tip_rel_palm + 3 * t + 1] = rel_palm.y;
-      o[L.tip_rel_palm + 3 * t + 2] = rel_palm.z;
+    const float obj_z = ob[2];
+    float my_tip_dist;
+    {   // fingertip `part` (:1033-1052)
+      const float* tr = s.tip + (el * kT1 + part) * 7;
+      const f3 to = f3{tr[0], tr[1], tr[2]} +
+                    quat_rotate(f4{tr[3], tr[4], tr[5], tr[6]}, f3{p.tip_offset[part][0], p.tip_offset[part][1], p.tip_offset[part][2]});
+      const f3 rel_obj = to - obj_pos, rel_palm = to - pc;
+      my_tip_dist = norm3(rel_obj);
+      o[L.tip_rel_palm + 3 * part + 0] = rel_palm.x;
+      o[L.tip_rel_palm + 3 * part + 1] = rel_palm.y;
+      o[L.tip_rel_palm + 3 * part + 2] = rel_palm.z;
     }
-    // keypoint `warp` (:1057-1073)
-    if (warp < K) {
-      const int k = warp;
-      const float* kp = s.kp + lane * KPW + 3 * k;
-      const float* gl = s.goal + lane * 7;
+    float my_kp_dist = 0.0f;                          // distances are >= 0, so 0 is neutral for the max
+    if (part < K) {                                   // keypoint `part` (:1057-1073)
+      const float* kp = s.kp + el * 3 * K + 3 * part;
+      const float* gl = s.goal + el * 7;
       const f3 off = {kp[0], kp[1], kp[2]};
-      const f4 obj_rot = {ob[3], ob[4], ob[5], ob[6]};
-      const f3 okp = obj_pos + quat_rotate(obj_rot, off);
+      const f3 okp = obj_pos + quat_rotate(f4{ob[3], ob[4], ob[5], ob[6]}, off);
       const f3 gkp = f3{gl[0], gl[1], gl[2]} + quat_rotate(f4{gl[3], gl[4], gl[5], gl[6]}, off);
-      const f3 rel_goal = okp - gkp;
-      const f3 rel_palm = okp - pc;
-      s.red[lane * kRedW + 4 + k] = norm3(rel_goal);
-      o[L.kp_rel_palm + 3 * k + 0] = rel_palm.x;
-      o[L.kp_rel_palm + 3 * k + 1] = rel_palm.y;
-      o[L.kp_rel_palm + 3 * k + 2] = rel_palm.z;
-      o[L.kp_rel_goal + 3 * k + 0] = rel_goal.x;
-      o[L.kp_rel_goal + 3 * k + 1] = rel_goal.y;
-      o[L.kp_rel_goal + 3 * k + 2] = rel_goal.z;
+      const f3 rel_goal = okp - gkp, rel_palm = okp - pc;
+      my_kp_dist = norm3(rel_goal);
+      o[L.kp_rel_palm + 3 * part + 0] = rel_palm.x;
+      o[L.kp_rel_palm + 3 * part + 1] = rel_palm.y;
+      o[L.kp_rel_palm + 3 * part + 2] = rel_palm.z;
+      o[L.kp_rel_goal + 3 * part + 0] = rel_goal.x;
+      o[L.kp_rel_goal + 3 * part + 1] = rel_goal.y;
+      o[L.kp_rel_goal + 3 * part + 2] = rel_goal.z;
     }
-    if (warp == 0) {          // palm pos, palm rot + vel (:1112-1117)
-      o[L.palm_pos + 0] = pc.x; o[L.palm_pos + 1] = pc.y; o[L.palm_pos + 2] = pc.z;
+    // _action_penalties sums (:830-839): each part adds its share, then a 4-lane butterfly
+    float sa = 0.f, sh = 0.f;
+    {
+      const float* v = o + L.dof_vel;
+      sa = fabsf(v[part]);
+      if (part < 3) sa += fabsf(v[part + 4]);
 #pragma unroll
-      for (int c = 0; c < 10; ++c) o[L.palm_rot_vel + c] = rb[3 + c];
-    } else if (warp == 1) {   // object rot + vel (:1120), object scales (:1143)
-#pragma unroll
-      for (int c = 0; c < 10; ++c) o[L.obj_rot_vel + c] = ob[3 + c];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) o[L.scales + c] = valid ? ldg(b.object_scales + (size_t)env * 3 + c) : 0.f;
-    } else if (warp == 2) {   // _action_penalties sums (:830-839)
-      float sa = 0.f, sh = 0.f;
-#pragma unroll
-      for (int d = 0; d < 7; ++d) sa += fabsf(o[L.dof_vel + d]);
-#pragma unroll
-      for (int d = 7; d < kD1; ++d) sh += fabsf(o[L.dof_vel + d]);
-      s.red[lane * kRedW + 8] = sa;
-      s.red[lane * kRedW + 9] = sh;
+      for (int j = 0; j < 4; ++j) sh += fabsf(v[7 + part + 4 * j]);
     }
-  }
-  __syncthreads();
+    sa += __shfl_xor_sync(FULL, sa, 8);  sh += __shfl_xor_sync(FULL, sh, 8);
+    sa += __shfl_xor_sync(FULL, sa, 16); sh += __shfl_xor_sync(FULL, sh, 16);
+    float cur[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) cur[j] = __shfl_sync(FULL, my_tip_dist, j * 8 + el);
+    float kp_max = fmaxf(my_kp_dist, __shfl_xor_sync(FULL, my_kp_dist, 8));
+    kp_max = fmaxf(kp_max, __shfl_xor_sync(FULL, kp_max, 16));
 
-  // ------------------------------ phase R ---------------------------------
-  if (warp == 0) {
-    float* o = s.obs + lane * OBS;
-    const float* rd = s.red + lane * kRedW;
-    const float cur[4] = {rd[0], rd[1], rd[2], rd[3]};
-    float kp_max = rd[4];
-#pragma unroll
-    for (int k = 1; k < K; ++k) kp_max = fmaxf(kp_max, rd[4 + k]);
+    // ------------------------ reward / reset logic ---------------------------
+    // (identical in the 4 lanes of an env; each part stores its share of the results)
     float ctip[4] = {r_ctip.x, r_ctip.y, r_ctip.z, r_ctip.w};
     const float coef[4] = {r_coef.x, r_coef.y, r_coef.z, r_coef.w};
     // lazy initialisation of the per-episode closest / furthest distances (:1044-1049, :1077-1079)
@@ -291,25 +307,26 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     for (int i = 0; i < 4; ++i) ctip[i] = (ctip[i] < 0.0f) ? cur[i] : ctip[i];
     float furthest = (r_furthest < 0.0f) ? cur[0] : r_furthest;
     float ckp = (r_ckp < 0.0f) ? kp_max : r_ckp;
-
     const long long progress = r_progress + (mode == kPostFull ? 1 : 0);   // progress_buf += 1 (:1429)
-    // observation slots that see pre-update state (SURVEY 8a ordering notes)
-    o[L.closest_kp] = ckp;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) o[L.closest_tip + i] = ctip[i];
-    o[L.lifted] = r_lifted ? 1.0f : 0.0f;
-    o[L.progress] = logf((float)progress / 10.0f + 1.0f);
-    o[L.successes] = logf(r_succ + 1.0f);
+    // observation slots that see pre-update state (ordering: SURVEY 8a)
+    if (part == 0) {
+      o[L.palm_pos + 0] = pc.x; o[L.palm_pos + 1] = pc.y; o[L.palm_pos + 2] = pc.z;
+      o[L.closest_kp] = ckp;
+      o[L.lifted] = r_lifted ? 1.0f : 0.0f;
+    }
+    o[L.closest_tip + part] = (part == 0) ? ctip[0] : (part == 1) ? ctip[1] : (part == 2) ? ctip[2] : ctip[3];
+    const float log_prog = logf((float)progress / 10.0f + 1.0f);
+    const float log_succ = logf(r_succ + 1.0f);
+    if (part == 1) { o[L.progress] = log_prog; o[L.successes] = log_succ; }
 
     if (mode == kPostObserveOnly) {
-      o[L.reward] = r_old_rew_obs;
-      if (valid) {
+      if (part == 1) o[L.reward] = r_old_rew_obs;
+      if (valid && part == 3) {
         b.closest_keypoint_max_dist[env] = ckp;
         b.furthest_hand_dist[env] = furthest;
         *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(ctip[0], ctip[1], ctip[2], ctip[3]);
       }
     } else {
-      const float obj_z = s.obj[lane * 13 + 2];
       // _lifting_reward (:788-812)
       const float z_lift = 0.05f + obj_z - r_initz;
       float lifting_rew = clipf(z_lift, 0.0f, 0.5f);
@@ -337,19 +354,22 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       ckp = fminf(ckp, kp_max);
       kp_rew *= lifted ? 1.0f : 0.0f;
       // compute_kuka_reward (:854-930)
-      const bool near_goal = kp_max <= b.dynamic->keypoint_success_tolerance;
+      const bool near_goal = kp_max <= keypoint_tol;
       const int near_steps = r_near + (near_goal ? 1 : 0);
       const bool is_success = near_steps >= p.success_steps;
       const float succ = r_succ + (is_success ? 1.0f : 0.0f);
-      const float raw_ft = ft, raw_hp = hp, raw_lift = lifting_rew, raw_kp = kp_rew;
+      float t[HA_KUKA_N_EPISODE_TERMS];
+      t[HA_KUKA_RAW_FINGERTIP_DELTA] = ft; t[HA_KUKA_RAW_HAND_DELTA] = hp; t[HA_KUKA_RAW_LIFTING] = lifting_rew; t[HA_KUKA_RAW_KEYPOINT] = kp_rew;
       ft *= p.distance_delta_rew_scale;
       hp *= p.hand_delta_rew_scale;
       lifting_rew *= p.lifting_rew_scale;
       kp_rew *= p.keypoint_rew_scale;
-      const float kuka_pen = -1.0f * (rd[8] * p.kuka_actions_penalty_scale);
-      const float allegro_pen = -1.0f * (rd[9] * p.allegro_actions_penalty_scale);
+      const float kuka_pen = -1.0f * (sa * p.kuka_actions_penalty_scale);
+      const float allegro_pen = -1.0f * (sh * p.allegro_actions_penalty_scale);
       const float bonus_rew = (near_goal ? 1.0f : 0.0f) * p.bonus_per_step;
       const float reward = ft + hp + lifting_rew + lift_bonus_rew + kp_rew + kuka_pen + allegro_pen + bonus_rew;
+      t[HA_KUKA_FINGERTIP_DELTA] = ft; t[HA_KUKA_HAND_DELTA] = hp; t[HA_KUKA_LIFTING] = lifting_rew; t[HA_KUKA_LIFT_BONUS] = lift_bonus_rew;
+      t[HA_KUKA_KEYPOINT] = kp_rew; t[HA_KUKA_BONUS] = bonus_rew; t[HA_KUKA_KUKA_PENALTY] = kuka_pen; t[HA_KUKA_ALLEGRO_PENALTY] = allegro_pen;
       // _compute_resets (:841-849) + reorientation _extra_reset_rules (allegro_kuka_reorientation.py:97-102)
       long long resets = (obj_z < p.fall_z) ? 1 : r_reset;
       long long prog = progress;
@@ -363,138 +383,156 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
         const float far = fmaxf(fmaxf(cur[0], cur[1]), fmaxf(cur[2], cur[3]));
         resets = (far > p.far_tip_dist) ? 1 : resets;
       }
-      const float true_obj = succ * b.dynamic->true_objective_scale + b.dynamic->true_objective_offset;
-      const float rew_obs = reward * 0.01f;                          // (:1437-1439)
-      o[L.reward] = rew_obs;
-
-      float* tm = s.terms;
-      tm[HA_KUKA_RAW_FINGERTIP_DELTA * kEnvsPerCta + lane] = raw_ft;
-      tm[HA_KUKA_RAW_HAND_DELTA * kEnvsPerCta + lane] = raw_hp;
-      tm[HA_KUKA_RAW_LIFTING * kEnvsPerCta + lane] = raw_lift;
-      tm[HA_KUKA_RAW_KEYPOINT * kEnvsPerCta + lane] = raw_kp;
-      tm[HA_KUKA_FINGERTIP_DELTA * kEnvsPerCta + lane] = ft;
-      tm[HA_KUKA_HAND_DELTA * kEnvsPerCta + lane] = hp;
-      tm[HA_KUKA_LIFTING * kEnvsPerCta + lane] = lifting_rew;
-      tm[HA_KUKA_LIFT_BONUS * kEnvsPerCta + lane] = lift_bonus_rew;
-      tm[HA_KUKA_KEYPOINT * kEnvsPerCta + lane] = kp_rew;
-      tm[HA_KUKA_BONUS * kEnvsPerCta + lane] = bonus_rew;
-      tm[HA_KUKA_KUKA_PENALTY * kEnvsPerCta + lane] = kuka_pen;
-      tm[HA_KUKA_ALLEGRO_PENALTY * kEnvsPerCta + lane] = allegro_pen;
-
+      const float true_obj = succ * tobj_scale + tobj_offset;
       const bool timeout_flag = timed_out && (resets != 0);          // vec_task.py:424
+      if (part == 1) o[L.reward] = reward * 0.01f;                   // (:1437-1439)
+
+      // ------------------------------ phase S ---------------------------------
+      // per-env outputs, split over the 4 parts of an env
       if (valid) {
-        b.rew_buf[env] = reward;
-        b.reset_buf[env] = resets;
-        b.reset_goal_buf[env] = is_success ? 1 : 0;
-        b.progress_buf[env] = prog;
-        if (b.randomize_buf) b.randomize_buf[env] += 1;              // (:1430)
-        b.timeout_buf[env] = timeout_flag ? 1 : 0;
-        b.successes[env] = succ;
-        b.true_objective[env] = true_obj;
-        b.near_goal_steps[env] = near_steps;
-        b.lifted_object[env] = lifted ? 1 : 0;
-        b.closest_keypoint_max_dist[env] = ckp;
-        b.furthest_hand_dist[env] = furthest;
-        *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(ctip[0], ctip[1], ctip[2], ctip[3]);
-      }
-      // per-CTA partial statistics, fixed order
-      float st[kNPart];
-      st[HA_KUKA_STAT_N] = valid ? 1.f : 0.f;
-      st[HA_KUKA_STAT_SUM_REWARD] = valid ? reward : 0.f;
-      st[HA_KUKA_STAT_SUM_RESETS] = valid ? (float)resets : 0.f;
-      st[HA_KUKA_STAT_SUM_SUCCESS_EVENTS] = (valid && is_success) ? 1.f : 0.f;
-      st[HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES] = valid ? r_prev_ep : 0.f;
-      st[HA_KUKA_STAT_SUM_TRUE_OBJECTIVE] = valid ? true_obj : 0.f;
-      st[HA_KUKA_STAT_MAX_TRUE_OBJECTIVE] = valid ? true_obj : -3.0e38f;
-      st[HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE] = valid ? -true_obj : -3.0e38f;
-      st[HA_KUKA_STAT_SUM_TIMEOUTS] = (valid && timeout_flag) ? 1.f : 0.f;
-      st[HA_KUKA_STAT_SUM_LIFTED] = (valid && lifted) ? 1.f : 0.f;
+        if (part == 0) {
+          b.rew_buf[env] = reward;
+          b.reset_buf[env] = resets;
+          b.progress_buf[env] = prog;
+        } else if (part == 1) {
+          b.reset_goal_buf[env] = is_success ? 1 : 0;
+          if (b.randomize_buf) b.randomize_buf[env] = r_randomize + 1;   // (:1430)
+          b.timeout_buf[env] = timeout_flag ? 1 : 0;
+        } else if (part == 2) {
+          b.successes[env] = succ;
+          b.true_objective[env] = true_obj;
+          b.near_goal_steps[env] = near_steps;
+          b.lifted_object[env] = lifted ? 1 : 0;
+        } else {
+          b.closest_keypoint_max_dist[env] = ckp;
+          b.furthest_hand_dist[env] = furthest;
+          *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(ctip[0], ctip[1], ctip[2], ctip[3]);
+        }
+        // rewards_episode[k] += term (:871-874, :923-926): part p owns k = p, p + 4, p + 8
 #pragma unroll
-      for (int i = 0; i < kNPart; ++i) {
-        const bool is_max = (i == HA_KUKA_STAT_MAX_TRUE_OBJECTIVE || i == HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE);
-        const float r = is_max ? warp_max(st[i]) : warp_sum(st[i]);
-        if (lane == 0) b.scratch[(size_t)i * gridDim.x + blockIdx.x] = r;   // [stat][cta]
+        for (int j = 0; j < 3; ++j) {
+          const float tk = (part == 0) ? t[4 * j] : (part == 1) ? t[4 * j + 1] : (part == 2) ? t[4 * j + 2] : t[4 * j + 3];
+          b.rewards_episode[(size_t)(part + 4 * j) * n + env] = r_acc[j] + tk;
+        }
+        // episode_cumulative[k] = term, the reference's list order (:912-921): part p owns k = p, p + 4
+        {
+          const float c0 = (part == 0) ? t[HA_KUKA_FINGERTIP_DELTA] : (part == 1) ? t[HA_KUKA_HAND_DELTA]
+                         : (part == 2) ? t[HA_KUKA_LIFTING] : t[HA_KUKA_LIFT_BONUS];
+          const float c1 = (part == 0) ? t[HA_KUKA_KEYPOINT] : (part == 1) ? t[HA_KUKA_KUKA_PENALTY]
+                         : (part == 2) ? t[HA_KUKA_ALLEGRO_PENALTY] : t[HA_KUKA_BONUS];
+          b.episode_cumulative[(size_t)part * n + env] = c0;
+          b.episode_cumulative[(size_t)(part + 4) * n + env] = c1;
+        }
+      }
+      if (valid) {
+        st_valid = true;
+        st_reward = reward; st_resets = (float)resets; st_success = is_success ? 1.f : 0.f; st_prev_ep = r_prev_ep;
+        st_tobj = true_obj; st_timeout = timeout_flag ? 1.f : 0.f; st_lifted = lifted ? 1.f : 0.f;
+      }
+    }
+    __syncwarp();
+    {
+      // obs tile: clamp (:1174-1176 clamp_obs, vec_task.py:432 clip) and store as one contiguous run
+      const float c = p.clamp_abs_obs;
+      const bool do_clamp = c > 0.0f;
+      float* dst = b.obs_buf + (size_t)env0 * OBS;
+      const int total = nvalid * OBS;
+      const int nvec = total >> 2;                    // tile base is 16-byte aligned (env0 % 8 == 0, obs_buf aligned)
+      constexpr int kObsIters = (kTile * OBS / 4 + 31) / 32;
+#pragma unroll
+      for (int i = 0; i < kObsIters; ++i) {
+        const int q = lane + 32 * i;
+        if (q < nvec) {
+          float4 v = *reinterpret_cast<const float4*>(s.obs + 4 * q);
+          if (do_clamp) {
+            v.x = fminf(fmaxf(v.x, -c), c); v.y = fminf(fmaxf(v.y, -c), c);
+            v.z = fminf(fmaxf(v.z, -c), c); v.w = fminf(fmaxf(v.w, -c), c);
+          }
+          *reinterpret_cast<float4*>(dst + 4 * q) = v;
+        }
+      }
+      const int f = (nvec << 2) + lane;               // ragged last tile: up to 3 trailing floats
+      if (f < total) {
+        float v = s.obs[f];
+        if (do_clamp) v = fminf(fmaxf(v, -c), c);
+        dst[f] = v;
       }
     }
   }
-  __syncthreads();
-
-  // ------------------------------ phase S ---------------------------------
-  if (mode == kPostFull && valid) {
-    // rewards_episode[k] += term (:871-874, :923-926); episode_cumulative[k] = term (:925)
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      const int k = warp + 4 * j;
-      const float t = s.terms[k * kEnvsPerCta + lane];
-      b.rewards_episode[(size_t)k * n + env] = r_acc[j] + t;
-    }
-    // step terms in the reference's list order (:912-921)
-    const int cum_src[HA_KUKA_N_STEP_TERMS] = {HA_KUKA_FINGERTIP_DELTA, HA_KUKA_HAND_DELTA, HA_KUKA_LIFTING, HA_KUKA_LIFT_BONUS,
-                                               HA_KUKA_KEYPOINT, HA_KUKA_KUKA_PENALTY, HA_KUKA_ALLEGRO_PENALTY, HA_KUKA_BONUS};
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int k = warp + 4 * j;
-      b.episode_cumulative[(size_t)k * n + env] = s.terms[cum_src[k] * kEnvsPerCta + lane];
-    }
-  }
-  {
-    // obs tile: clamp (:1174-1176 clamp_obs, vec_task.py:432 clip) and store contiguously
-    const float c = p.clamp_abs_obs;
-    float* dst = b.obs_buf + (size_t)env0 * OBS;
-    const int total = nvalid * OBS;
-    const int nvec = ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) ? (total >> 2) : 0;
-    for (int q = tid; q < nvec; q += kThreads) {
-      float4 v = *reinterpret_cast<const float4*>(s.obs + 4 * q);
-      if (c > 0.0f) {
-        v.x = fminf(fmaxf(v.x, -c), c); v.y = fminf(fmaxf(v.y, -c), c);
-        v.z = fminf(fmaxf(v.z, -c), c); v.w = fminf(fmaxf(v.w, -c), c);
-      }
-      *reinterpret_cast<float4*>(dst + 4 * q) = v;
-    }
-    for (int f = (nvec << 2) + tid; f < total; f += kThreads) {
-      float v = s.obs[f];
-      if (c > 0.0f) v = fminf(fmaxf(v, -c), c);
-      dst[f] = v;
-    }
-  }
-
-  // ---------------------- last CTA: final statistics ----------------------
   if (mode != kPostFull) return;
-  __threadfence();
-  if (tid == 0) {
-    const unsigned t = atomicAdd(b.tickets + 0, 1u);
-    s.last_flag = (t == gridDim.x - 1);
+
+  // --------------------------- episode statistics ---------------------------
+  // warp: only part-0 lanes contribute (one lane per env); butterfly over the 8 envs
+  {
+    const bool c = st_valid && part == 0;
+    float v[kNPart];
+    v[HA_KUKA_STAT_N] = c ? 1.f : 0.f;
+    v[HA_KUKA_STAT_SUM_REWARD] = c ? st_reward : 0.f;
+    v[HA_KUKA_STAT_SUM_RESETS] = c ? st_resets : 0.f;
+    v[HA_KUKA_STAT_SUM_SUCCESS_EVENTS] = c ? st_success : 0.f;
+    v[HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES] = c ? st_prev_ep : 0.f;
+    v[HA_KUKA_STAT_SUM_TRUE_OBJECTIVE] = c ? st_tobj : 0.f;
+    v[HA_KUKA_STAT_MAX_TRUE_OBJECTIVE] = c ? st_tobj : -3.0e38f;
+    v[HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE] = c ? -st_tobj : -3.0e38f;
+    v[HA_KUKA_STAT_SUM_TIMEOUTS] = c ? st_timeout : 0.f;
+    v[HA_KUKA_STAT_SUM_LIFTED] = c ? st_lifted : 0.f;
+#pragma unroll
+    for (int i = 0; i < kNPart; ++i) {
+#pragma unroll
+      for (int ofs = 4; ofs > 0; ofs >>= 1) {
+        const float other = __shfl_xor_sync(FULL, v[i], ofs);
+        v[i] = stat_is_max(i) ? fmaxf(v[i], other) : v[i] + other;
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < kNPart; ++i) sm.part[warp][i] = v[i];
+    }
   }
   __syncthreads();
-  if (!s.last_flag) return;
-  __threadfence();
-  {
-    // 128 threads: stat = tid / 8 (16 slots), 8 lanes per stat stride over the CTAs
-    const int stat = tid >> 3, sub = tid & 7;
-    const bool is_max = (stat == HA_KUKA_STAT_MAX_TRUE_OBJECTIVE || stat == HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE);
-    float acc = is_max ? -3.0e38f : 0.f;
-    if (stat < kNPart) {
-      const volatile float* src = b.scratch + (size_t)stat * gridDim.x;
-      for (int i = sub; i < (int)gridDim.x; i += 8) acc = is_max ? fmaxf(acc, src[i]) : acc + src[i];
-    }
+  if (tid < kNPart) {
+    float acc = sm.part[0][tid];
 #pragma unroll
-    for (int o = 4; o > 0; o >>= 1) {
-      const float other = __shfl_xor_sync(0xffffffffu, acc, o);
-      acc = is_max ? fmaxf(acc, other) : acc + other;
+    for (int w = 1; w < kWarps; ++w) acc = stat_is_max(tid) ? fmaxf(acc, sm.part[w][tid]) : acc + sm.part[w][tid];
+    if (stat_is_max(tid)) {
+      atomicMax(reinterpret_cast<long long*>(b.stat_accum + tid), float_key(acc));
+    } else {
+      const float sc = (tid == HA_KUKA_STAT_SUM_REWARD) ? 65536.0f : (tid == HA_KUKA_STAT_SUM_TRUE_OBJECTIVE) ? 1048576.0f : 1.0f;
+      atomicAdd(reinterpret_cast<unsigned long long*>(b.stat_accum + tid), (unsigned long long)__float2ll_rn(acc * sc));
     }
-    if (sub == 0 && stat < kNPart) { b.stats[stat] = acc; s.part[stat] = acc; }
-    __syncthreads();
-    if (tid == 0) {
-      // means / min for extras (allegro_kuka_base.py:903-910), so the host needs no extra launches
-      const float inv_n = 1.0f / s.part[HA_KUKA_STAT_N];
-      b.stats[HA_KUKA_STAT_MEAN_REWARD] = s.part[HA_KUKA_STAT_SUM_REWARD] * inv_n;
-      b.stats[HA_KUKA_STAT_MEAN_PREV_EP_SUCCESSES] = s.part[HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES] * inv_n;
-      b.stats[HA_KUKA_STAT_MEAN_TRUE_OBJECTIVE] = s.part[HA_KUKA_STAT_SUM_TRUE_OBJECTIVE] * inv_n;
-      b.stats[HA_KUKA_STAT_MIN_TRUE_OBJECTIVE] = -s.part[HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE];
-      b.tickets[0] = 0;                    // re-arm for the next launch (graph replay safe)
-      // the reset/index counters of the pre-step are consumed by now: clear for the next pre-step
-      b.reset_counts[0] = 0; b.reset_counts[1] = 0; b.reset_counts[2] = 0; b.reset_counts[3] = 0;
-    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    const unsigned tk = atomicAdd(b.tickets + 0, 1u);
+    sm.last_flag = (tk == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!sm.last_flag) return;
+  // ---------------------- last CTA: final statistics ----------------------
+  if (tid == 0) __threadfence();
+  if (tid < kNPart) {
+    const bool is_max = stat_is_max(tid);
+    const long long raw = (long long)atomicExch(reinterpret_cast<unsigned long long*>(b.stat_accum + tid),
+                                                (unsigned long long)(is_max ? kStatMaxInit : 0LL));
+    const float sc = (tid == HA_KUKA_STAT_SUM_REWARD) ? 65536.0f : (tid == HA_KUKA_STAT_SUM_TRUE_OBJECTIVE) ? 1048576.0f : 1.0f;
+    const float val = is_max ? key_float(raw) : (float)((double)raw / (double)sc);
+    b.stats[tid] = val;
+    sm.part[0][tid] = val;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    // means / min for extras (allegro_kuka_base.py:903-910), so the host needs no extra launches
+    const float inv_n = 1.0f / sm.part[0][HA_KUKA_STAT_N];
+    b.stats[HA_KUKA_STAT_MEAN_REWARD] = sm.part[0][HA_KUKA_STAT_SUM_REWARD] * inv_n;
+    b.stats[HA_KUKA_STAT_MEAN_PREV_EP_SUCCESSES] = sm.part[0][HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES] * inv_n;
+    b.stats[HA_KUKA_STAT_MEAN_TRUE_OBJECTIVE] = sm.part[0][HA_KUKA_STAT_SUM_TRUE_OBJECTIVE] * inv_n;
+    b.stats[HA_KUKA_STAT_MIN_TRUE_OBJECTIVE] = -sm.part[0][HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE];
+    b.tickets[0] = 0;                    // re-arm for the next launch (graph replay safe)
+    // the reset/index counters of the pre-step are consumed by now: clear for the next pre-step
+    b.reset_counts[0] = 0; b.reset_counts[1] = 0; b.reset_counts[2] = 0; b.reset_counts[3] = 0;
+    // fast-mode RNG: one counter tick per step
+    b.dynamic->rng_step = b.dynamic->rng_step + 1;
   }
 }
 

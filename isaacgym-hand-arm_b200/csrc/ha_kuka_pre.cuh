@@ -8,11 +8,13 @@
 // (:1401-1414).  No nonzero()/unique()/len(): masks are consumed in place.
 //
 // Mapping: CTA = tile of 32 envs, 128 threads.
-//   all threads : (env, dof) elementwise pass over the contiguous [32, 23]
-//                 tiles of actions / prev_targets / cur_targets / dof_state;
-//   warp 0      : per-env scalar reset work (goal pose, object pose, episode
-//                 state, actor index lists);
-//   warp 1      : random force on the object body row;
+//   all threads : the contiguous [32, 23] tiles of actions / prev_targets /
+//                 cur_targets as 128-bit vectors (one float4 = 4 consecutive
+//                 (env, dof) elements); loads are issued before the masks are
+//                 known, the masks arrive as two 32-bit ballots;
+//   warp 0      : per-env scalar reset work, only for tiles that have a reset
+//                 (out-of-line: the common path stays a few hundred instructions);
+//   warp 1      : random force on the object body rows, 3 coalesced requests;
 //   warps 2,3   : zero the 12 per-episode accumulators of reset envs.
 #pragma once
 #include "ha_device.cuh"
@@ -26,10 +28,10 @@ struct KukaRand {
   const float* ext;   // [n_envs, stride] or nullptr
   int stride;
   Rng rng;
-  __device__ __forceinline__ float u(int env, int slot) const {
+  __device__ __noinline__ float u(int env, int slot) const {
     return ext ? __ldg(ext + (size_t)env * stride + slot) : rng.uniform(env, slot);
   }
-  __device__ __forceinline__ float nrm(int env, int slot, int j) const {
+  __device__ __noinline__ float nrm(int env, int slot, int j) const {
     return ext ? __ldg(ext + (size_t)env * stride + slot + j) : rng.normal(env, j);
   }
 };
@@ -39,12 +41,106 @@ __device__ __forceinline__ float force_prob_from(const HaKukaParams& p, float u)
   return expf(p.force_log_c0 * u + p.force_log_c1);
 }
 
+struct KukaPreSmem {
+  float lo[24], hi[24], dflt[24], noise[24];
+};
+
+// reset_idx DOF re-randomisation of one (env, dof) element (:1271-1290); returns the new position
+__device__ __noinline__ float kuka_reset_dof(const HaKukaBuffers& b, const KukaRand& R, const KukaPreSmem& s, float vel_noise,
+                                             int env, int d) {
+  constexpr int D = 23;
+  const float lo = s.lo[d], hi = s.hi[d], dflt = s.dflt[d];
+  const float delta_max = hi - dflt, delta_min = lo - dflt;
+  const float u_pos = R.u(env, HA_KUKA_RND_DOF_POS + d);
+  const float rand_delta = delta_min + (delta_max - delta_min) * u_pos;
+  const float pos = dflt + s.noise[d] * rand_delta;
+  const float u_vel = R.u(env, HA_KUKA_RND_DOF_POS + D + d);
+  const float vel = vel_noise * (2.0f * u_vel + -1.0f);
+  *reinterpret_cast<float2*>(b.dof_state + 2 * ((size_t)env * D + d)) = make_float2(pos, vel);
+  return pos;   // prev_targets = cur_targets = allegro_pos (:1289-1290)
+}
+
+// goal / object / episode-state reset of one env (lane = env), and the actor-row lists of the tile
+__device__ __noinline__ void kuka_reset_env_scalars(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env, int lane,
+                                                   bool rst, bool grst) {
+  const bool any_goal = rst || grst;
+  if (any_goal) {
+    // _reset_target; an env that is in both sets is drawn twice by the
+    // reference and the reset_idx draw wins
+    const int sp = rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS;
+    const int sr = rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT;
+    float g[7];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) g[c] = p.target_min[c] + R.u(env, sp + c) * p.target_size[c];
+    const f4 q = random_quat(R.u(env, sr + 0), R.u(env, sr + 1), R.u(env, sr + 2));
+    g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
+    float* gs = b.goal_states + (size_t)env * 13;
+    float* rr = b.root_state + (size_t)b.goal_actor[env] * 13;
+#pragma unroll
+    for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr[c] = g[c]; }
+#pragma unroll
+    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
+    b.reset_goal_buf[env] = 0;                       // reset_target_pose (:1194-1196)
+    b.near_goal_steps[env] = 0;
+    b.closest_keypoint_max_dist[env] = -1.0f;
+  }
+  if (rst) {
+    // reset_object_pose (:1198-1224)
+    const float* init = b.object_init_state + (size_t)env * 13;
+    float* rr = b.root_state + (size_t)b.object_actor[env] * 13;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float r = 2.0f * R.u(env, HA_KUKA_RND_OBJ_POS + c) + -1.0f;     // torch_rand_float(-1, 1)
+      rr[c] = __ldg(init + c) + p.reset_pos_noise[c] * r;
+    }
+    const f4 q = random_quat(R.u(env, HA_KUKA_RND_OBJ_ROT + 0), R.u(env, HA_KUKA_RND_OBJ_ROT + 1), R.u(env, HA_KUKA_RND_OBJ_ROT + 2));
+    rr[3] = q.x; rr[4] = q.y; rr[5] = q.z; rr[6] = q.w;
+#pragma unroll
+    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
+    *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
+    b.furthest_hand_dist[env] = -1.0f;
+    b.random_force_prob[env] = force_prob_from(p, R.u(env, HA_KUKA_RND_FORCE_PROB));
+    // episode bookkeeping (:1323-1347)
+    b.progress_buf[env] = 0;
+    b.reset_buf[env] = 0;
+    b.prev_episode_successes[env] = b.successes[env];
+    b.successes[env] = 0.0f;
+    b.prev_episode_true_objective[env] = b.true_objective[env];
+    b.true_objective[env] = 0.0f;
+    b.lifted_object[env] = 0;
+  }
+  // actor rows for set_actor_root_state_tensor_indexed / set_dof_*_indexed:
+  // warp-aggregated append, rows of one env stay adjacent and ascending
+  const unsigned m_any = __ballot_sync(0xffffffffu, any_goal);
+  const unsigned m_rst = __ballot_sync(0xffffffffu, rst);
+  const unsigned m_goal_only = m_any & ~m_rst;
+  const int n_root = 2 * __popc(m_rst) + __popc(m_goal_only);
+  const int n_hand = __popc(m_rst);
+  int root_base = 0, hand_base = 0;
+  if (lane == 0 && n_root) {
+    root_base = atomicAdd(b.reset_counts + 0, n_root);
+    if (n_hand) hand_base = atomicAdd(b.reset_counts + 1, n_hand);
+    if (n_hand) atomicAdd(b.reset_counts + 2, n_hand);
+    atomicAdd(b.reset_counts + 3, __popc(m_any));
+  }
+  root_base = __shfl_sync(0xffffffffu, root_base, 0);
+  hand_base = __shfl_sync(0xffffffffu, hand_base, 0);
+  const unsigned below = (1u << lane) - 1u;
+  if (any_goal) {
+    int k = root_base + 2 * __popc(m_rst & below) + __popc(m_goal_only & below);
+    if (rst) b.root_reset_indices[k++] = b.object_actor[env];
+    b.root_reset_indices[k] = b.goal_actor[env];
+  }
+  if (rst) b.hand_reset_indices[hand_base + __popc(m_rst & below)] = b.hand_actor[env];
+}
+
 __global__ void __launch_bounds__(kThreads, 8)
 kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b,
                 const float* __restrict__ actions, const float* __restrict__ ext_rand, const int mode) {
   constexpr int D = 23;
-  __shared__ unsigned char s_reset[kEnvsPerCta];
-  __shared__ int s_last;
+  constexpr int kVecPerTile = kEnvsPerCta * D / 4;     // 184 float4 per full tile
+  constexpr int kIters = (kVecPerTile + kThreads - 1) / kThreads;   // 2
+  __shared__ KukaPreSmem s;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int env0 = blockIdx.x * kEnvsPerCta;
@@ -52,6 +148,45 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   const int nvalid = min(kEnvsPerCta, n - env0);
   const int env = env0 + lane;
   const bool valid = lane < nvalid;
+  const bool reset_only = (mode == kPreResetOnly);   // VecTask.reset_idx / reset_done outside of a step
+
+  // ---- issue the tile's vector loads first: they do not depend on the masks ----
+  const size_t base = (size_t)env0 * D;
+  const int total = nvalid * D, nvec = total >> 2;     // tile base is 16-byte aligned (env0 % 32 == 0)
+  float4 a[kIters], prev[kIters];
+#pragma unroll
+  for (int i = 0; i < kIters; ++i) {
+    const int q = tid + i * kThreads;
+    a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    prev[i] = a[i];
+    if (q < nvec) {
+      if (!reset_only) a[i] = __ldg(reinterpret_cast<const float4*>(actions + base) + q);
+      prev[i] = *(reinterpret_cast<const float4*>(b.prev_targets + base) + q);
+    }
+  }
+  // every warp reads the tile's masks (coalesced int64) -> identical ballots in all warps
+  const bool rst = valid && (b.reset_buf[env] != 0);
+  const bool grst = valid && !reset_only && (b.reset_goal_buf[env] != 0);
+  const unsigned m_rst = __ballot_sync(0xffffffffu, rst);
+  const unsigned m_goal = __ballot_sync(0xffffffffu, grst);
+  // force inputs of warp 1 (issued early as well)
+  const bool do_force = (warp == 1) && p.force_enabled && !reset_only;
+  float f_prob = 0.f, f_v[3] = {0.f, 0.f, 0.f};
+  const size_t frow = ((size_t)env0 * p.n_bodies + p.object_body) * 3;
+  const int fstride = p.n_bodies * 3;
+  if (do_force) {
+    if (valid) f_prob = b.random_force_prob[env];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int idx = lane + 32 * i, e = idx / 3, c = idx - 3 * e;
+      if (e < nvalid) f_v[i] = b.rb_forces[frow + (size_t)e * fstride + c];
+    }
+  }
+  if (tid < D) {
+    s.lo[tid] = p.dof_lower[tid]; s.hi[tid] = p.dof_upper[tid];
+    s.dflt[tid] = p.dof_default[tid]; s.noise[tid] = p.dof_reset_noise[tid];
+  }
+  __syncthreads();
 
   KukaRand R;
   R.ext = p.use_fast_rng ? nullptr : ext_rand;
@@ -59,154 +194,92 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   R.rng.seed = b.dynamic->rng_seed;
   R.rng.step = b.dynamic->rng_step;
 
-  // every warp reads the tile's masks (coalesced int64)
-  const bool rst = valid && (b.reset_buf[env] != 0);
-  const bool reset_only = (mode == kPreResetOnly);   // VecTask.reset_idx / reset_done outside of a step
-  const bool grst = valid && !reset_only && (b.reset_goal_buf[env] != 0);
-  if (warp == 0) s_reset[lane] = rst ? 1 : 0;
-  __syncthreads();
-
-  // ---------------- all threads: DOF targets, elementwise -----------------
-  {
-    const size_t base = (size_t)env0 * D;
-    const int total = nvalid * D;
-    constexpr int kIters = (kEnvsPerCta * D + kThreads - 1) / kThreads;  // 6
-    float a[kIters], prev[kIters];
+  // ---------------- all threads: DOF targets, 4 consecutive elements per float4 ----------------
+  if (!(reset_only && m_rst == 0u)) {
+    const float ema = p.act_moving_average, one_m_ema = p.one_minus_act_moving_average, gain = p.arm_action_gain;
+    const bool copy_actions = !reset_only && (actions != b.actions);
 #pragma unroll
     for (int i = 0; i < kIters; ++i) {
-      const int f = tid + i * kThreads;
-      if (f < total) { a[i] = reset_only ? 0.f : __ldg(actions + base + f); prev[i] = b.prev_targets[base + f]; }
+      const int q = tid + i * kThreads;
+      if (q >= nvec) continue;
+      const int f0 = 4 * q;
+      int e = f0 / D, d = f0 - e * D;
+      const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w};
+      const float pvv[4] = {prev[i].x, prev[i].y, prev[i].z, prev[i].w};
+      float cur[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float lo = s.lo[d], hi = s.hi[d];
+        float pv = pvv[c];
+        const bool er = (m_rst >> e) & 1u;
+        if (er) pv = kuka_reset_dof(b, R, s, p.reset_dof_vel_noise, env0 + e, d);
+        float x;
+        if (reset_only) {
+          x = pv;
+        } else if (d >= 7) {   // absolute control of the hand DOFs (:1377-1390)
+          x = scale_to(av[c], lo, hi);
+          x = ema * x + one_m_ema * pv;
+          x = clamp_to(x, lo, hi);
+        } else {               // relative control of the arm DOFs (:1392-1395)
+          x = clamp_to(pv + gain * av[c], lo, hi);
+        }
+        cur[c] = x;
+        if (reset_only && er) { b.cur_targets[base + f0 + c] = x; b.prev_targets[base + f0 + c] = x; }   // only the reset envs' rows
+        if (++d == D) { d = 0; ++e; }
+      }
+      if (!reset_only) {
+        const float4 o = make_float4(cur[0], cur[1], cur[2], cur[3]);
+        *(reinterpret_cast<float4*>(b.cur_targets + base) + q) = o;
+        *(reinterpret_cast<float4*>(b.prev_targets + base) + q) = o;     // (:1397)
+      }
+      if (copy_actions) *(reinterpret_cast<float4*>(b.actions + base) + q) = a[i];   // self.actions = actions.clone() (:1357)
     }
-#pragma unroll
-    for (int i = 0; i < kIters; ++i) {
-      const int f = tid + i * kThreads;
-      if (f >= total) continue;
+    // ragged last tile: up to 3 trailing elements
+    const int f = (nvec << 2) + tid;
+    if (f < total) {
       const int e = f / D, d = f - e * D;
-      if (reset_only && !s_reset[e]) continue;
-      const float lo = p.dof_lower[d], hi = p.dof_upper[d];
-      float pv = prev[i];
-      if (s_reset[e]) {
-        // reset_idx DOF re-randomisation (:1271-1290)
-        const int ge = env0 + e;
-        const float dflt = p.dof_default[d];
-        const float delta_max = hi - dflt, delta_min = lo - dflt;
-        const float u_pos = R.u(ge, HA_KUKA_RND_DOF_POS + d);
-        const float rand_delta = delta_min + (delta_max - delta_min) * u_pos;
-        const float pos = dflt + p.dof_reset_noise[d] * rand_delta;
-        const float u_vel = R.u(ge, HA_KUKA_RND_DOF_POS + D + d);
-        const float vel = p.reset_dof_vel_noise * (2.0f * u_vel + -1.0f);
-        *reinterpret_cast<float2*>(b.dof_state + 2 * (base + f)) = make_float2(pos, vel);
-        pv = pos;   // prev_targets = cur_targets = allegro_pos (:1289-1290)
-      }
-      float cur;
-      if (reset_only) {
-        cur = pv;
-      } else if (d >= 7) {   // absolute control of the hand DOFs (:1377-1390)
-        cur = scale_to(a[i], lo, hi);
-        cur = p.act_moving_average * cur + p.one_minus_act_moving_average * pv;
-        cur = clamp_to(cur, lo, hi);
-      } else {        // relative control of the arm DOFs (:1392-1395)
-        cur = clamp_to(pv + p.arm_action_gain * a[i], lo, hi);
-      }
-      b.cur_targets[base + f] = cur;
-      b.prev_targets[base + f] = cur;     // (:1397)
-      if (!reset_only) b.actions[base + f] = a[i];   // self.actions = actions.clone() (:1357)
+      const float lo = s.lo[d], hi = s.hi[d];
+      const float av = reset_only ? 0.f : __ldg(actions + base + f);
+      float pv = b.prev_targets[base + f];
+      const bool er = (m_rst >> e) & 1u;
+      if (er) pv = kuka_reset_dof(b, R, s, p.reset_dof_vel_noise, env0 + e, d);
+      float x;
+      if (reset_only) x = pv;
+      else if (d >= 7) { x = scale_to(av, lo, hi); x = ema * x + one_m_ema * pv; x = clamp_to(x, lo, hi); }
+      else x = clamp_to(pv + gain * av, lo, hi);
+      if (!reset_only || er) { b.cur_targets[base + f] = x; b.prev_targets[base + f] = x; }
+      if (copy_actions) b.actions[base + f] = av;
     }
   }
 
-  // ---------------- warp 0: per-env scalar reset work ---------------------
-  if (warp == 0) {
-    const bool any_goal = rst || grst;
-    if (any_goal) {
-      // _reset_target; an env that is in both sets is drawn twice by the
-      // reference and the reset_idx draw wins
-      const int sp = rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS;
-      const int sr = rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT;
-      float g[7];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) g[c] = p.target_min[c] + R.u(env, sp + c) * p.target_size[c];
-      const f4 q = random_quat(R.u(env, sr + 0), R.u(env, sr + 1), R.u(env, sr + 2));
-      g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
-      float* gs = b.goal_states + (size_t)env * 13;
-      const int grow = b.goal_actor[env];
-      float* rr = b.root_state + (size_t)grow * 13;
-#pragma unroll
-      for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr[c] = g[c]; }
-#pragma unroll
-      for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
-      b.reset_goal_buf[env] = 0;                       // reset_target_pose (:1194-1196)
-      b.near_goal_steps[env] = 0;
-      b.closest_keypoint_max_dist[env] = -1.0f;
-    }
-    if (rst) {
-      // reset_object_pose (:1198-1224)
-      const float* init = b.object_init_state + (size_t)env * 13;
-      const int orow = b.object_actor[env];
-      float* rr = b.root_state + (size_t)orow * 13;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const float r = 2.0f * R.u(env, HA_KUKA_RND_OBJ_POS + c) + -1.0f;     // torch_rand_float(-1, 1)
-        rr[c] = __ldg(init + c) + p.reset_pos_noise[c] * r;
-      }
-      const f4 q = random_quat(R.u(env, HA_KUKA_RND_OBJ_ROT + 0), R.u(env, HA_KUKA_RND_OBJ_ROT + 1), R.u(env, HA_KUKA_RND_OBJ_ROT + 2));
-      rr[3] = q.x; rr[4] = q.y; rr[5] = q.z; rr[6] = q.w;
-#pragma unroll
-      for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
-      *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
-      b.furthest_hand_dist[env] = -1.0f;
-      b.random_force_prob[env] = force_prob_from(p, R.u(env, HA_KUKA_RND_FORCE_PROB));
-      // episode bookkeeping (:1323-1347)
-      b.progress_buf[env] = 0;
-      b.reset_buf[env] = 0;
-      b.prev_episode_successes[env] = b.successes[env];
-      b.successes[env] = 0.0f;
-      b.prev_episode_true_objective[env] = b.true_objective[env];
-      b.true_objective[env] = 0.0f;
-      b.lifted_object[env] = 0;
-    }
-    // actor rows for set_actor_root_state_tensor_indexed / set_dof_*_indexed:
-    // warp-aggregated append, rows of one env stay adjacent and ascending
-    const unsigned m_any = __ballot_sync(0xffffffffu, any_goal);
-    const unsigned m_rst = __ballot_sync(0xffffffffu, rst);
-    const unsigned m_goal_only = m_any & ~m_rst;
-    const int n_root = 2 * __popc(m_rst) + __popc(m_goal_only);
-    const int n_hand = __popc(m_rst);
-    int root_base = 0, hand_base = 0;
-    if (lane == 0 && n_root) {
-      root_base = atomicAdd(b.reset_counts + 0, n_root);
-      if (n_hand) hand_base = atomicAdd(b.reset_counts + 1, n_hand);
-      if (n_hand) atomicAdd(b.reset_counts + 2, n_hand);
-      atomicAdd(b.reset_counts + 3, __popc(m_any));
-    }
-    root_base = __shfl_sync(0xffffffffu, root_base, 0);
-    hand_base = __shfl_sync(0xffffffffu, hand_base, 0);
-    const unsigned below = (1u << lane) - 1u;
-    if (any_goal) {
-      const int pos = root_base + 2 * __popc(m_rst & below) + __popc(m_goal_only & below);
-      int k = pos;
-      if (rst) b.root_reset_indices[k++] = b.object_actor[env];
-      b.root_reset_indices[k] = b.goal_actor[env];
-    }
-    if (rst) b.hand_reset_indices[hand_base + __popc(m_rst & below)] = b.hand_actor[env];
-  }
+  // ---------------- warp 0: per-env scalar reset work (tiles with a reset only) ----------------
+  if (warp == 0 && (m_rst | m_goal) != 0u) kuka_reset_env_scalars(p, b, R, env, lane, rst, grst);
 
-  // ---------------- warp 1: random forces on the object body ---------------
-  if (warp == 1 && p.force_enabled && valid && !reset_only) {
-    float* f = b.rb_forces + ((size_t)env * p.n_bodies + p.object_body) * 3;
-    float fx = f[0], fy = f[1], fz = f[2];
-    if (rst) { fx = 0.f; fy = 0.f; fz = 0.f; }          // rb_forces[env_ids] = 0 (:1255)
-    fx *= p.force_decay_pow; fy *= p.force_decay_pow; fz *= p.force_decay_pow;   // (:1402)
-    const float prob = rst ? force_prob_from(p, R.u(env, HA_KUKA_RND_FORCE_PROB)) : b.random_force_prob[env];
-    if (R.u(env, HA_KUKA_RND_FORCE_TEST) < prob) {      // (:1405-1410)
-      fx = R.nrm(env, HA_KUKA_RND_FORCE_NORMAL, 0) * p.force_gain[0] * p.force_gain[1];
-      fy = R.nrm(env, HA_KUKA_RND_FORCE_NORMAL, 1) * p.force_gain[0] * p.force_gain[1];
-      fz = R.nrm(env, HA_KUKA_RND_FORCE_NORMAL, 2) * p.force_gain[0] * p.force_gain[1];
+  // ---------------- warp 1: random forces on the object body ----------------
+  if (warp == 1) {
+    if (do_force) {
+      // Bernoulli test per env (lane = env), then (env, component) lanes apply it (:1401-1414)
+      bool hit = false;
+      if (valid) {
+        const float prob = rst ? force_prob_from(p, R.u(env, HA_KUKA_RND_FORCE_PROB)) : f_prob;
+        hit = R.u(env, HA_KUKA_RND_FORCE_TEST) < prob;
+      }
+      const unsigned m_hit = __ballot_sync(0xffffffffu, hit);
+      const float decay = p.force_decay_pow, g0 = p.force_gain[0], g1 = p.force_gain[1];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const int idx = lane + 32 * i, e = idx / 3, c = idx - 3 * e;
+        if (e < nvalid) {
+          float v = ((m_rst >> e) & 1u) ? 0.f : f_v[i];          // rb_forces[env_ids] = 0 (:1255)
+          v *= decay;                                            // (:1402)
+          if ((m_hit >> e) & 1u) v = R.nrm(env0 + e, HA_KUKA_RND_FORCE_NORMAL, c) * g0 * g1;   // (:1405-1410)
+          b.rb_forces[frow + (size_t)e * fstride + c] = v;
+        }
+      }
+    } else if (rst) {
+      float* f = b.rb_forces + frow + (size_t)lane * fstride;
+      f[0] = 0.f; f[1] = 0.f; f[2] = 0.f;
     }
-    f[0] = fx; f[1] = fy; f[2] = fz;
-  }
-  if (warp == 1 && (!p.force_enabled || reset_only) && rst) {
-    float* f = b.rb_forces + ((size_t)env * p.n_bodies + p.object_body) * 3;
-    f[0] = 0.f; f[1] = 0.f; f[2] = 0.f;
   }
 
   // ---------------- warps 2,3: zero per-episode accumulators ---------------
@@ -214,16 +287,9 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
 #pragma unroll
     for (int k = warp - 2; k < HA_KUKA_N_EPISODE_TERMS; k += 2) b.rewards_episode[(size_t)k * n + env] = 0.0f;   // (:1341-1342)
   }
-
-  // ---------------- last CTA: advance the fast-mode RNG counter ------------
-  if (p.use_fast_rng) {
-    __threadfence();
-    if (tid == 0) {
-      const unsigned t = atomicAdd(b.tickets + 1, 1u);
-      s_last = (t == gridDim.x - 1);
-      if (s_last) { b.tickets[1] = 0; b.dynamic->rng_step = R.rng.step + 1; }
-    }
-  }
 }
+
+// advances the fast-mode RNG counter after an out-of-step reset (inside a step ha_kuka_post_step does it)
+__global__ void kuka_rng_tick_kernel(HaKukaDynamic* dyn) { dyn->rng_step = dyn->rng_step + 1; }
 
 }  // namespace ha

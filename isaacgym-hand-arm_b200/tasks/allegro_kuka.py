@@ -283,10 +283,15 @@ class AllegroKukaBase(VecTask):
         p.reset_pos_noise[0], p.reset_pos_noise[1], p.reset_pos_noise[2] = (self.reset_position_noise_x, self.reset_position_noise_y,
                                                                           self.reset_position_noise_z)
         p.reset_dof_vel_noise = self.reset_dof_vel_noise
+        # regular Isaac Gym actor numbering (row = env * actors_per_env + slot) lets the gather skip the index tables
+        ar = torch.arange(self.num_envs, dtype=torch.long, device=self.device) * L.actors_per_env
+        regular = bool(torch.equal(self.object_indices, ar + L.object_actor)) and bool(torch.equal(self.goal_object_indices, ar + L.goal_actor))
+        p.root_regular, p.actors_per_env, p.object_slot, p.goal_slot = int(regular), L.actors_per_env, L.object_actor, L.goal_actor
         self._params = p
         self._observe_params = _lib.HaKukaParams.from_buffer_copy(p)
         self._observe_params.clamp_abs_obs = 0.0    # VecTask.reset() clips on the host side copy only
-        self._scratch = torch.zeros(int(self._lib.ha_kuka_scratch_floats(self.num_envs)), dtype=torch.float, device=self.device)
+        self._stat_accum = torch.tensor([int(self._lib.ha_kuka_stat_accum_init(i)) for i in range(C["HA_STATS_LEN"])],
+                                        dtype=torch.int64, device=self.device)
         self._buffers = _lib.HaKukaBuffers()
         self._bind_buffers()
         self._write_dynamic()
@@ -308,7 +313,7 @@ class AllegroKukaBase(VecTask):
             rewards_episode=self._rewards_episode, episode_cumulative=self._episode_cumulative, prev_targets=self.prev_targets,
             cur_targets=self.cur_targets, actions=self.actions, rb_forces=self.rb_forces, random_force_prob=self.random_force_prob,
             root_reset_indices=self.root_reset_indices, hand_reset_indices=self.hand_reset_indices, reset_counts=self.reset_counts,
-            stats=self.stats, scratch=self._scratch, tickets=self._tickets, dynamic=self._dynamic)
+            stats=self.stats, stat_accum=self._stat_accum, tickets=self._tickets, dynamic=self._dynamic)
         for name, t in self._bound.items():
             assert t.is_contiguous(), name
             setattr(b, name, t.data_ptr())
