@@ -98,32 +98,27 @@ struct KukaPostSmem {
   int last_flag;
 };
 
-template <int K>
-__global__ void __launch_bounds__(kThreads, 7)
-kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b, const int mode) {
-  using Smem = KukaPostSmem<K>;
+struct KukaPostEnvStats {   // per-env results that feed the statistics (idle lanes: valid == false)
+  float reward = 0.f, resets = 0.f, success = 0.f, prev_ep = 0.f, tobj = 0.f, timeout = 0.f, lifted = 0.f;
+  bool valid = false;
+};
+
+// One warp, one tile of up to 8 envs.  kFull: all 8 envs exist (no index clamps; every warp but the last one).
+template <int K, bool kFull>
+__device__ __forceinline__ void kuka_post_tile(const HaKukaParams& p, const HaKukaBuffers& b, KukaPostWarpSmem<K>& s, const int mode,
+                                               const int env0, const int nvalid_rt, const int lane, KukaPostEnvStats& st) {
   using WS = KukaPostWarpSmem<K>;
   constexpr int OBS = WS::kObs;
   constexpr KukaLayout L = kuka_layout(kD1, kT1, K);
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  WS& s = sm.w[warp];
   const int n = p.n_envs;
-  const int env0 = (blockIdx.x * kWarps + warp) * kTile;
-  const int nvalid = min(kTile, n - env0);          // <= 0: this warp has no tile
+  const int nvalid = kFull ? kTile : nvalid_rt;
   const int part = lane >> 3, el = lane & 7;        // compute mapping: 4 lanes per env
-  const bool valid = el < nvalid;
+  const bool valid = kFull ? true : (el < nvalid);
   const unsigned FULL = 0xffffffffu;
-
-  // per-env results that feed the statistics (stay 0 / -inf for idle lanes)
-  float st_reward = 0.f, st_resets = 0.f, st_success = 0.f, st_prev_ep = 0.f, st_tobj = 0.f, st_timeout = 0.f, st_lifted = 0.f;
-  bool st_valid = false;
-
-  if (nvalid > 0) {
-    const int last = nvalid - 1;
-    const int env = env0 + min(el, last);           // clamped: idle lanes re-read a valid env, stores are predicated
+  const int last = nvalid - 1;
+  auto cl = [&](int e) { return kFull ? e : min(e, last); };   // idle lanes of a ragged tile re-read a valid env
+  {
+    const int env = env0 + cl(el);                  // stores are predicated on `valid`
     // ------------------------------ phase L ---------------------------------
     if (lane < kD1) { s.lo[lane] = p.dof_lower[lane]; s.hi[lane] = p.dof_upper[lane]; }
 
@@ -136,12 +131,12 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     {
       const float* src = rb0 + (size_t)p.palm_body[0] * 13 + min(c16, 12);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) palm_v[i] = ldg(src + (size_t)min(2 * i + h16, last) * rb_env_stride);
+      for (int i = 0; i < 4; ++i) palm_v[i] = ldg(src + (size_t)cl(2 * i + h16) * rb_env_stride);
     }
     {
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const int e = env0 + min(2 * i + h16, last);
+        const int e = env0 + cl(2 * i + h16);
         const int row = p.root_regular ? e * p.actors_per_env + p.object_slot : __ldg(b.object_actor + e);
         obj_v[i] = b.root_state[(size_t)row * 13 + min(c16, 12)];
       }
@@ -149,11 +144,11 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     {
       const float* src = rb0 + (size_t)p.tip_body[r8] * 13 + min(c8, 6);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) tip_v[i] = ldg(src + (size_t)min(i, last) * rb_env_stride);
+      for (int i = 0; i < 8; ++i) tip_v[i] = ldg(src + (size_t)cl(i) * rb_env_stride);
     }
     {
 #pragma unroll
-      for (int i = 0; i < 2; ++i) goal_v[i] = b.goal_states[(size_t)(env0 + min(4 * i + r8, last)) * 13 + min(c8, 6)];
+      for (int i = 0; i < 2; ++i) goal_v[i] = b.goal_states[(size_t)(env0 + cl(4 * i + r8)) * 13 + min(c8, 6)];
     }
     // contiguous spans: DOF state [nvalid, 23, 2], keypoint table [nvalid, K, 3], scales [nvalid, 3]
     const float* dof_src = b.dof_state + (size_t)env0 * (2 * kD1);
@@ -315,9 +310,10 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       o[L.lifted] = r_lifted ? 1.0f : 0.0f;
     }
     o[L.closest_tip + part] = (part == 0) ? ctip[0] : (part == 1) ? ctip[1] : (part == 2) ? ctip[2] : ctip[3];
-    const float log_prog = logf((float)progress / 10.0f + 1.0f);
-    const float log_succ = logf(r_succ + 1.0f);
-    if (part == 1) { o[L.progress] = log_prog; o[L.successes] = log_succ; }
+    {   // log(progress / 10 + 1) (:1162) by part 0, log(successes + 1) (:1164) by part 1: one logf per lane
+      const float lg = logf((part == 0) ? ((float)progress / 10.0f + 1.0f) : (r_succ + 1.0f));
+      if (part < 2) o[(part == 0) ? L.progress : L.successes] = lg;
+    }
 
     if (mode == kPostObserveOnly) {
       if (part == 1) o[L.reward] = r_old_rew_obs;
@@ -425,9 +421,9 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
         }
       }
       if (valid) {
-        st_valid = true;
-        st_reward = reward; st_resets = (float)resets; st_success = is_success ? 1.f : 0.f; st_prev_ep = r_prev_ep;
-        st_tobj = true_obj; st_timeout = timeout_flag ? 1.f : 0.f; st_lifted = lifted ? 1.f : 0.f;
+        st.valid = true;
+        st.reward = reward; st.resets = (float)resets; st.success = is_success ? 1.f : 0.f; st.prev_ep = r_prev_ep;
+        st.tobj = true_obj; st.timeout = timeout_flag ? 1.f : 0.f; st.lifted = lifted ? 1.f : 0.f;
       }
     }
     __syncwarp();
@@ -459,34 +455,53 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       }
     }
   }
+}
+
+template <int K>
+__global__ void __launch_bounds__(kThreads, 7)
+kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b, const int mode) {
+  using Smem = KukaPostSmem<K>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int env0 = (blockIdx.x * kWarps + warp) * kTile;
+  const int nvalid = min(kTile, p.n_envs - env0);          // <= 0: this warp has no tile
+  const int part = lane >> 3;
+  const unsigned FULL = 0xffffffffu;
+  KukaPostEnvStats st;
+  if (nvalid == kTile) kuka_post_tile<K, true>(p, b, sm.w[warp], mode, env0, nvalid, lane, st);
+  else if (nvalid > 0) kuka_post_tile<K, false>(p, b, sm.w[warp], mode, env0, nvalid, lane, st);
   if (mode != kPostFull) return;
 
   // --------------------------- episode statistics ---------------------------
-  // warp: only part-0 lanes contribute (one lane per env); butterfly over the 8 envs
+  // warp: one lane per env contributes (part 0); 0/1 flags by ballot, the rest by an 8-lane butterfly
   {
-    const bool c = st_valid && part == 0;
-    float v[kNPart];
-    v[HA_KUKA_STAT_N] = c ? 1.f : 0.f;
-    v[HA_KUKA_STAT_SUM_REWARD] = c ? st_reward : 0.f;
-    v[HA_KUKA_STAT_SUM_RESETS] = c ? st_resets : 0.f;
-    v[HA_KUKA_STAT_SUM_SUCCESS_EVENTS] = c ? st_success : 0.f;
-    v[HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES] = c ? st_prev_ep : 0.f;
-    v[HA_KUKA_STAT_SUM_TRUE_OBJECTIVE] = c ? st_tobj : 0.f;
-    v[HA_KUKA_STAT_MAX_TRUE_OBJECTIVE] = c ? st_tobj : -3.0e38f;
-    v[HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE] = c ? -st_tobj : -3.0e38f;
-    v[HA_KUKA_STAT_SUM_TIMEOUTS] = c ? st_timeout : 0.f;
-    v[HA_KUKA_STAT_SUM_LIFTED] = c ? st_lifted : 0.f;
+    const bool c = st.valid && part == 0;
+    const unsigned m_n = __ballot_sync(FULL, c), m_rs = __ballot_sync(FULL, c && st.resets != 0.f);
+    const unsigned m_su = __ballot_sync(FULL, c && st.success != 0.f), m_to = __ballot_sync(FULL, c && st.timeout != 0.f);
+    const unsigned m_li = __ballot_sync(FULL, c && st.lifted != 0.f);
+    float v_rew = c ? st.reward : 0.f, v_pe = c ? st.prev_ep : 0.f, v_to = c ? st.tobj : 0.f;
+    float v_mx = c ? st.tobj : -3.0e38f, v_mn = c ? -st.tobj : -3.0e38f;
 #pragma unroll
-    for (int i = 0; i < kNPart; ++i) {
-#pragma unroll
-      for (int ofs = 4; ofs > 0; ofs >>= 1) {
-        const float other = __shfl_xor_sync(FULL, v[i], ofs);
-        v[i] = stat_is_max(i) ? fmaxf(v[i], other) : v[i] + other;
-      }
+    for (int ofs = 4; ofs > 0; ofs >>= 1) {
+      v_rew += __shfl_xor_sync(FULL, v_rew, ofs);
+      v_pe += __shfl_xor_sync(FULL, v_pe, ofs);
+      v_to += __shfl_xor_sync(FULL, v_to, ofs);
+      v_mx = fmaxf(v_mx, __shfl_xor_sync(FULL, v_mx, ofs));
+      v_mn = fmaxf(v_mn, __shfl_xor_sync(FULL, v_mn, ofs));
     }
     if (lane == 0) {
-#pragma unroll
-      for (int i = 0; i < kNPart; ++i) sm.part[warp][i] = v[i];
+      float* o = sm.part[warp];
+      o[HA_KUKA_STAT_N] = (float)__popc(m_n);
+      o[HA_KUKA_STAT_SUM_REWARD] = v_rew;
+      o[HA_KUKA_STAT_SUM_RESETS] = (float)__popc(m_rs);
+      o[HA_KUKA_STAT_SUM_SUCCESS_EVENTS] = (float)__popc(m_su);
+      o[HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES] = v_pe;
+      o[HA_KUKA_STAT_SUM_TRUE_OBJECTIVE] = v_to;
+      o[HA_KUKA_STAT_MAX_TRUE_OBJECTIVE] = v_mx;
+      o[HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE] = v_mn;
+      o[HA_KUKA_STAT_SUM_TIMEOUTS] = (float)__popc(m_to);
+      o[HA_KUKA_STAT_SUM_LIFTED] = (float)__popc(m_li);
     }
   }
   __syncthreads();

@@ -45,19 +45,30 @@ struct KukaPreSmem {
   float lo[24], hi[24], dflt[24], noise[24];
 };
 
-// reset_idx DOF re-randomisation of one (env, dof) element (:1271-1290); returns the new position
-__device__ __noinline__ float kuka_reset_dof(const HaKukaBuffers& b, const KukaRand& R, const KukaPreSmem& s, float vel_noise,
-                                             int env, int d) {
+// reset_idx DOF re-randomisation of one env by one warp, lane = dof (:1271-1290).
+// Writes dof_state and prev_targets = cur_targets = allegro_pos (:1289-1290).
+__device__ __noinline__ void kuka_reset_dofs_warp(const HaKukaBuffers& b, const KukaRand& R, const KukaPreSmem& s, float vel_noise,
+                                                  int env, int lane) {
   constexpr int D = 23;
+  if (lane >= D) return;
+  const int d = lane;
+  float u_pos, u_vel;
+  if (R.ext) {
+    u_pos = __ldg(R.ext + (size_t)env * R.stride + HA_KUKA_RND_DOF_POS + d);
+    u_vel = __ldg(R.ext + (size_t)env * R.stride + HA_KUKA_RND_DOF_POS + D + d);
+  } else {
+    const float2 u = R.rng.uniform2(env, 64 + d);     // one Philox block per DOF: (.x, .y) = (pos, vel) draws
+    u_pos = u.x; u_vel = u.y;
+  }
   const float lo = s.lo[d], hi = s.hi[d], dflt = s.dflt[d];
   const float delta_max = hi - dflt, delta_min = lo - dflt;
-  const float u_pos = R.u(env, HA_KUKA_RND_DOF_POS + d);
   const float rand_delta = delta_min + (delta_max - delta_min) * u_pos;
   const float pos = dflt + s.noise[d] * rand_delta;
-  const float u_vel = R.u(env, HA_KUKA_RND_DOF_POS + D + d);
   const float vel = vel_noise * (2.0f * u_vel + -1.0f);
-  *reinterpret_cast<float2*>(b.dof_state + 2 * ((size_t)env * D + d)) = make_float2(pos, vel);
-  return pos;   // prev_targets = cur_targets = allegro_pos (:1289-1290)
+  const size_t idx = (size_t)env * D + d;
+  *reinterpret_cast<float2*>(b.dof_state + 2 * idx) = make_float2(pos, vel);
+  b.prev_targets[idx] = pos;
+  b.cur_targets[idx] = pos;
 }
 
 // goal / object / episode-state reset of one env (lane = env), and the actor-row lists of the tile
@@ -159,8 +170,8 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     const int q = tid + i * kThreads;
     a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     prev[i] = a[i];
-    if (q < nvec) {
-      if (!reset_only) a[i] = __ldg(reinterpret_cast<const float4*>(actions + base) + q);
+    if (q < nvec && !reset_only) {
+      a[i] = __ldg(reinterpret_cast<const float4*>(actions + base) + q);
       prev[i] = *(reinterpret_cast<const float4*>(b.prev_targets + base) + q);
     }
   }
@@ -186,18 +197,28 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     s.lo[tid] = p.dof_lower[tid]; s.hi[tid] = p.dof_upper[tid];
     s.dflt[tid] = p.dof_default[tid]; s.noise[tid] = p.dof_reset_noise[tid];
   }
-  __syncthreads();
-
   KukaRand R;
   R.ext = p.use_fast_rng ? nullptr : ext_rand;
   R.stride = HA_KUKA_RND_STRIDE(D);
   R.rng.seed = b.dynamic->rng_seed;
   R.rng.step = b.dynamic->rng_step;
+  __syncthreads();
+  if (m_rst != 0u) {                                   // uniform over the CTA; rare per tile
+    // DOF re-randomisation of the tile's reset envs, one warp per env (round robin), lane = dof
+    unsigned m = m_rst;
+    int rank = 0;
+    while (m) {
+      const int e = __ffs(m) - 1;
+      m &= m - 1;
+      if ((rank++ & (kThreads / 32 - 1)) == warp) kuka_reset_dofs_warp(b, R, s, p.reset_dof_vel_noise, env0 + e, lane);
+    }
+    __syncthreads();                                   // new prev_targets visible to the element pass below
+  }
 
   // ---------------- all threads: DOF targets, 4 consecutive elements per float4 ----------------
-  if (!(reset_only && m_rst == 0u)) {
+  if (!reset_only) {
     const float ema = p.act_moving_average, one_m_ema = p.one_minus_act_moving_average, gain = p.arm_action_gain;
-    const bool copy_actions = !reset_only && (actions != b.actions);
+    const bool copy_actions = (actions != b.actions);
 #pragma unroll
     for (int i = 0; i < kIters; ++i) {
       const int q = tid + i * kThreads;
@@ -212,11 +233,9 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
         const float lo = s.lo[d], hi = s.hi[d];
         float pv = pvv[c];
         const bool er = (m_rst >> e) & 1u;
-        if (er) pv = kuka_reset_dof(b, R, s, p.reset_dof_vel_noise, env0 + e, d);
+        if (er) pv = __ldcg(b.prev_targets + base + f0 + c);     // re-randomised just above by another warp
         float x;
-        if (reset_only) {
-          x = pv;
-        } else if (d >= 7) {   // absolute control of the hand DOFs (:1377-1390)
+        if (d >= 7) {          // absolute control of the hand DOFs (:1377-1390)
           x = scale_to(av[c], lo, hi);
           x = ema * x + one_m_ema * pv;
           x = clamp_to(x, lo, hi);
@@ -224,14 +243,11 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
           x = clamp_to(pv + gain * av[c], lo, hi);
         }
         cur[c] = x;
-        if (reset_only && er) { b.cur_targets[base + f0 + c] = x; b.prev_targets[base + f0 + c] = x; }   // only the reset envs' rows
         if (++d == D) { d = 0; ++e; }
       }
-      if (!reset_only) {
-        const float4 o = make_float4(cur[0], cur[1], cur[2], cur[3]);
-        *(reinterpret_cast<float4*>(b.cur_targets + base) + q) = o;
-        *(reinterpret_cast<float4*>(b.prev_targets + base) + q) = o;     // (:1397)
-      }
+      const float4 o = make_float4(cur[0], cur[1], cur[2], cur[3]);
+      *(reinterpret_cast<float4*>(b.cur_targets + base) + q) = o;
+      *(reinterpret_cast<float4*>(b.prev_targets + base) + q) = o;       // (:1397)
       if (copy_actions) *(reinterpret_cast<float4*>(b.actions + base) + q) = a[i];   // self.actions = actions.clone() (:1357)
     }
     // ragged last tile: up to 3 trailing elements
@@ -239,15 +255,13 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     if (f < total) {
       const int e = f / D, d = f - e * D;
       const float lo = s.lo[d], hi = s.hi[d];
-      const float av = reset_only ? 0.f : __ldg(actions + base + f);
-      float pv = b.prev_targets[base + f];
-      const bool er = (m_rst >> e) & 1u;
-      if (er) pv = kuka_reset_dof(b, R, s, p.reset_dof_vel_noise, env0 + e, d);
+      const float av = __ldg(actions + base + f);
+      const float pv = __ldcg(b.prev_targets + base + f);
       float x;
-      if (reset_only) x = pv;
-      else if (d >= 7) { x = scale_to(av, lo, hi); x = ema * x + one_m_ema * pv; x = clamp_to(x, lo, hi); }
+      if (d >= 7) { x = scale_to(av, lo, hi); x = ema * x + one_m_ema * pv; x = clamp_to(x, lo, hi); }
       else x = clamp_to(pv + gain * av, lo, hi);
-      if (!reset_only || er) { b.cur_targets[base + f] = x; b.prev_targets[base + f] = x; }
+      b.cur_targets[base + f] = x;
+      b.prev_targets[base + f] = x;
       if (copy_actions) b.actions[base + f] = av;
     }
   }
