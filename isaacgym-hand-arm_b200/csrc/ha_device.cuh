@@ -99,6 +99,12 @@ struct Rng {
     const int c = slot & 3;
     return u32_to_unit(c == 0 ? r.x : c == 1 ? r.y : c == 2 ? r.z : r.w);
   }
+  // all four uniforms of one counter block
+  __device__ __forceinline__ float4 uniform4(int env, int block) const {
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)env, (uint32_t)block, (uint32_t)step, (uint32_t)(step >> 32)),
+                                  make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    return make_float4(u32_to_unit(r.x), u32_to_unit(r.y), u32_to_unit(r.z), u32_to_unit(r.w));
+  }
   // two uniforms of one counter block (used with block >= 64: disjoint from the slot blocks above)
   __device__ __forceinline__ float2 uniform2(int env, int block) const {
     const uint4 r = philox4x32_10(make_uint4((uint32_t)env, (uint32_t)block, (uint32_t)step, (uint32_t)(step >> 32)),

@@ -56,8 +56,8 @@ int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStr
     if (rc) return rc;
     configured = true;
   }
-  const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
-  ha::kuka_post_kernel<K><<<grid, ha::kThreads, sizeof(S), st>>>(*p, *b, mode);
+  const int grid = (p->n_envs + ha::kTile - 1) / ha::kTile;
+  ha::kuka_post_kernel<K><<<grid, ha::kPostThreads, sizeof(S), st>>>(*p, *b, mode);
   return ha::check_cuda(cudaGetLastError(), "kuka_post_kernel launch");
 }
 

@@ -31,6 +31,14 @@ struct KukaRand {
   __device__ __noinline__ float u(int env, int slot) const {
     return ext ? __ldg(ext + (size_t)env * stride + slot) : rng.uniform(env, slot);
   }
+  // the four draws slot .. slot+3 (parity table: 4 loads; fast mode: ONE Philox block, id = slot)
+  __device__ __noinline__ float4 u4(int env, int slot) const {
+    if (ext) {
+      const float* r = ext + (size_t)env * stride + slot;
+      return make_float4(__ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3));
+    }
+    return rng.uniform4(env, 32 + slot);
+  }
   __device__ __noinline__ float nrm(int env, int slot, int j) const {
     return ext ? __ldg(ext + (size_t)env * stride + slot + j) : rng.normal(env, j);
   }
@@ -71,22 +79,44 @@ __device__ __noinline__ void kuka_reset_dofs_warp(const HaKukaBuffers& b, const 
   b.cur_targets[idx] = pos;
 }
 
-// goal / object / episode-state reset of one env (lane = env), and the actor-row lists of the tile
+// goal / object / episode-state reset of one env (lane = env), and the actor-row lists of the tile.
+// Executed by a whole warp for a tile that has at least one reset: every load and every random draw
+// is issued up front (one memory round trip on the critical path), stores follow.
 __device__ __noinline__ void kuka_reset_env_scalars(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env, int lane,
                                                    bool rst, bool grst) {
   const bool any_goal = rst || grst;
+  // _reset_target; an env that is in both sets is drawn twice by the
+  // reference and the reset_idx draw wins
+  const int sp = rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS;
+  const int sr = rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT;
+  float4 u_gp = make_float4(0.f, 0.f, 0.f, 0.f), u_gr = u_gp, u_op = u_gp, u_or = u_gp;
+  float u_fp = 0.f, succ = 0.f, tobj = 0.f, init0 = 0.f, init1 = 0.f, init2 = 0.f;
+  int goal_row = 0, obj_row = 0, hand_row = 0;
   if (any_goal) {
-    // _reset_target; an env that is in both sets is drawn twice by the
-    // reference and the reset_idx draw wins
-    const int sp = rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS;
-    const int sr = rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT;
+    u_gp = R.u4(env, sp);
+    u_gr = R.u4(env, sr);
+    goal_row = p.root_regular ? env * p.actors_per_env + p.goal_slot : b.goal_actor[env];
+  }
+  if (rst) {
+    u_op = R.u4(env, HA_KUKA_RND_OBJ_POS);
+    u_or = R.u4(env, HA_KUKA_RND_OBJ_ROT);
+    u_fp = R.u4(env, HA_KUKA_RND_FORCE_PROB).x;
+    obj_row = p.root_regular ? env * p.actors_per_env + p.object_slot : b.object_actor[env];
+    hand_row = b.hand_actor[env];
+    succ = b.successes[env];
+    tobj = b.true_objective[env];
+    const float* init = b.object_init_state + (size_t)env * 13;
+    init0 = __ldg(init + 0); init1 = __ldg(init + 1); init2 = __ldg(init + 2);
+  }
+  if (any_goal) {
     float g[7];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) g[c] = p.target_min[c] + R.u(env, sp + c) * p.target_size[c];
-    const f4 q = random_quat(R.u(env, sr + 0), R.u(env, sr + 1), R.u(env, sr + 2));
+    g[0] = p.target_min[0] + u_gp.x * p.target_size[0];
+    g[1] = p.target_min[1] + u_gp.y * p.target_size[1];
+    g[2] = p.target_min[2] + u_gp.z * p.target_size[2];
+    const f4 q = random_quat(u_gr.x, u_gr.y, u_gr.z);
     g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
     float* gs = b.goal_states + (size_t)env * 13;
-    float* rr = b.root_state + (size_t)b.goal_actor[env] * 13;
+    float* rr = b.root_state + (size_t)goal_row * 13;
 #pragma unroll
     for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr[c] = g[c]; }
 #pragma unroll
@@ -96,27 +126,24 @@ __device__ __noinline__ void kuka_reset_env_scalars(const HaKukaParams& p, const
     b.closest_keypoint_max_dist[env] = -1.0f;
   }
   if (rst) {
-    // reset_object_pose (:1198-1224)
-    const float* init = b.object_init_state + (size_t)env * 13;
-    float* rr = b.root_state + (size_t)b.object_actor[env] * 13;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const float r = 2.0f * R.u(env, HA_KUKA_RND_OBJ_POS + c) + -1.0f;     // torch_rand_float(-1, 1)
-      rr[c] = __ldg(init + c) + p.reset_pos_noise[c] * r;
-    }
-    const f4 q = random_quat(R.u(env, HA_KUKA_RND_OBJ_ROT + 0), R.u(env, HA_KUKA_RND_OBJ_ROT + 1), R.u(env, HA_KUKA_RND_OBJ_ROT + 2));
+    // reset_object_pose (:1198-1224); torch_rand_float(-1, 1) = 2 u - 1
+    float* rr = b.root_state + (size_t)obj_row * 13;
+    rr[0] = init0 + p.reset_pos_noise[0] * (2.0f * u_op.x + -1.0f);
+    rr[1] = init1 + p.reset_pos_noise[1] * (2.0f * u_op.y + -1.0f);
+    rr[2] = init2 + p.reset_pos_noise[2] * (2.0f * u_op.z + -1.0f);
+    const f4 q = random_quat(u_or.x, u_or.y, u_or.z);
     rr[3] = q.x; rr[4] = q.y; rr[5] = q.z; rr[6] = q.w;
 #pragma unroll
     for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
     *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
     b.furthest_hand_dist[env] = -1.0f;
-    b.random_force_prob[env] = force_prob_from(p, R.u(env, HA_KUKA_RND_FORCE_PROB));
+    b.random_force_prob[env] = force_prob_from(p, u_fp);
     // episode bookkeeping (:1323-1347)
     b.progress_buf[env] = 0;
     b.reset_buf[env] = 0;
-    b.prev_episode_successes[env] = b.successes[env];
+    b.prev_episode_successes[env] = succ;
     b.successes[env] = 0.0f;
-    b.prev_episode_true_objective[env] = b.true_objective[env];
+    b.prev_episode_true_objective[env] = tobj;
     b.true_objective[env] = 0.0f;
     b.lifted_object[env] = 0;
   }
@@ -139,10 +166,10 @@ __device__ __noinline__ void kuka_reset_env_scalars(const HaKukaParams& p, const
   const unsigned below = (1u << lane) - 1u;
   if (any_goal) {
     int k = root_base + 2 * __popc(m_rst & below) + __popc(m_goal_only & below);
-    if (rst) b.root_reset_indices[k++] = b.object_actor[env];
-    b.root_reset_indices[k] = b.goal_actor[env];
+    if (rst) b.root_reset_indices[k++] = obj_row;
+    b.root_reset_indices[k] = goal_row;
   }
-  if (rst) b.hand_reset_indices[hand_base + __popc(m_rst & below)] = b.hand_actor[env];
+  if (rst) b.hand_reset_indices[hand_base + __popc(m_rst & below)] = hand_row;
 }
 
 __global__ void __launch_bounds__(kThreads, 8)
@@ -275,7 +302,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       // Bernoulli test per env (lane = env), then (env, component) lanes apply it (:1401-1414)
       bool hit = false;
       if (valid) {
-        const float prob = rst ? force_prob_from(p, R.u(env, HA_KUKA_RND_FORCE_PROB)) : f_prob;
+        const float prob = rst ? force_prob_from(p, R.u4(env, HA_KUKA_RND_FORCE_PROB).x) : f_prob;
         hit = R.u(env, HA_KUKA_RND_FORCE_TEST) < prob;
       }
       const unsigned m_hit = __ballot_sync(0xffffffffu, hit);
