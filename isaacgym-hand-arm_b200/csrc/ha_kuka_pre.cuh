@@ -12,8 +12,9 @@
 //                 cur_targets as 128-bit vectors (one float4 = 4 consecutive
 //                 (env, dof) elements); loads are issued before the masks are
 //                 known, the masks arrive as two 32-bit ballots;
-//   warp 0      : per-env scalar reset work, only for tiles that have a reset
-//                 (out-of-line: the common path stays a few hundred instructions);
+//   warp 0      : per-env scalar reset work, only for tiles that have a reset; its loads,
+//                 random draws and list-slot atomics are issued as soon as the masks are
+//                 known, so a tile with a reset pays ONE extra memory round trip;
 //   warp 1      : random force on the object body rows, 3 coalesced requests;
 //   warps 2,3   : zero the 12 per-episode accumulators of reset envs.
 #pragma once
@@ -51,12 +52,14 @@ __device__ __forceinline__ float force_prob_from(const HaKukaParams& p, float u)
 
 struct KukaPreSmem {
   float lo[24], hi[24], dflt[24], noise[24];
+  float pos[kEnvsPerCta][24];      // re-randomised DOF positions of the tile's reset envs (row = env in tile)
 };
 
 // reset_idx DOF re-randomisation of one env by one warp, lane = dof (:1271-1290).
-// Writes dof_state and prev_targets = cur_targets = allegro_pos (:1289-1290).
-__device__ __noinline__ void kuka_reset_dofs_warp(const HaKukaBuffers& b, const KukaRand& R, const KukaPreSmem& s, float vel_noise,
-                                                  int env, int lane) {
+// Writes dof_state; the new position goes to smem for the element pass (prev_targets = cur_targets = pos, :1289-1290),
+// and straight to global memory when there is no element pass (reset outside of a step).
+__device__ __noinline__ void kuka_reset_dofs_warp(const HaKukaBuffers& b, const KukaRand& R, KukaPreSmem& s, float vel_noise,
+                                                  int env, int e_local, int lane, bool write_targets) {
   constexpr int D = 23;
   if (lane >= D) return;
   const int d = lane;
@@ -75,78 +78,29 @@ __device__ __noinline__ void kuka_reset_dofs_warp(const HaKukaBuffers& b, const 
   const float vel = vel_noise * (2.0f * u_vel + -1.0f);
   const size_t idx = (size_t)env * D + d;
   *reinterpret_cast<float2*>(b.dof_state + 2 * idx) = make_float2(pos, vel);
-  b.prev_targets[idx] = pos;
-  b.cur_targets[idx] = pos;
+  s.pos[e_local][d] = pos;
+  if (write_targets) { b.prev_targets[idx] = pos; b.cur_targets[idx] = pos; }
 }
 
-// goal / object / episode-state reset of one env (lane = env), and the actor-row lists of the tile.
-// Executed by a whole warp for a tile that has at least one reset: every load and every random draw
-// is issued up front (one memory round trip on the critical path), stores follow.
-__device__ __noinline__ void kuka_reset_env_scalars(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env, int lane,
-                                                   bool rst, bool grst) {
+// Everything the scalar reset of one env needs, fetched / drawn up front (lane = env).
+struct KukaResetPrefetch {
+  float4 u_gp, u_gr, u_op, u_or;   // goal position / rotation, object position / rotation draws
+  float u_fp, succ, tobj, init0, init1, init2;
+  int goal_row, obj_row, hand_row, root_pos, hand_pos, root_base, hand_base;
+};
+
+__device__ __forceinline__ float4 kuka_draw4(const KukaRand& R, int env, int slot) {   // inlined: independent Philox chains overlap
+  if (R.ext) {
+    const float* r = R.ext + (size_t)env * R.stride + slot;
+    return make_float4(__ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3));
+  }
+  return R.rng.uniform4(env, 32 + slot);
+}
+
+// Issue phase: loads, random draws and the list-slot atomics of a tile that has a goal / full reset.
+__device__ __forceinline__ void kuka_reset_prefetch(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env, int lane,
+                                                bool rst, bool grst, KukaResetPrefetch& f) {
   const bool any_goal = rst || grst;
-  // _reset_target; an env that is in both sets is drawn twice by the
-  // reference and the reset_idx draw wins (SURVEY appendix B)
-  const int sp = rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS;
-  const int sr = rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT;
-  float4 u_gp = make_float4(0.f, 0.f, 0.f, 0.f), u_gr = u_gp, u_op = u_gp, u_or = u_gp;
-  float u_fp = 0.f, succ = 0.f, tobj = 0.f, init0 = 0.f, init1 = 0.f, init2 = 0.f;
-  int goal_row = 0, obj_row = 0, hand_row = 0;
-  if (any_goal) {
-    u_gp = R.u4(env, sp);
-    u_gr = R.u4(env, sr);
-    goal_row = p.root_regular ? env * p.actors_per_env + p.goal_slot : b.goal_actor[env];
-  }
-  if (rst) {
-    u_op = R.u4(env, HA_KUKA_RND_OBJ_POS);
-    u_or = R.u4(env, HA_KUKA_RND_OBJ_ROT);
-    u_fp = R.u4(env, HA_KUKA_RND_FORCE_PROB).x;
-    obj_row = p.root_regular ? env * p.actors_per_env + p.object_slot : b.object_actor[env];
-    hand_row = b.hand_actor[env];
-    succ = b.successes[env];
-    tobj = b.true_objective[env];
-    const float* init = b.object_init_state + (size_t)env * 13;
-    init0 = __ldg(init + 0); init1 = __ldg(init + 1); init2 = __ldg(init + 2);
-  }
-  if (any_goal) {
-    float g[7];
-    g[0] = p.target_min[0] + u_gp.x * p.target_size[0];
-    g[1] = p.target_min[1] + u_gp.y * p.target_size[1];
-    g[2] = p.target_min[2] + u_gp.z * p.target_size[2];
-    const f4 q = random_quat(u_gr.x, u_gr.y, u_gr.z);
-    g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
-    float* gs = b.goal_states + (size_t)env * 13;
-    float* rr = b.root_state + (size_t)goal_row * 13;
-#pragma unroll
-    for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr[c] = g[c]; }
-#pragma unroll
-    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
-    b.reset_goal_buf[env] = 0;                       // reset_target_pose (:1194-1196)
-    b.near_goal_steps[env] = 0;
-    b.closest_keypoint_max_dist[env] = -1.0f;
-  }
-  if (rst) {
-    // reset_object_pose (:1198-1224); torch_rand_float(-1, 1) = 2 u - 1
-    float* rr = b.root_state + (size_t)obj_row * 13;
-    rr[0] = init0 + p.reset_pos_noise[0] * (2.0f * u_op.x + -1.0f);
-    rr[1] = init1 + p.reset_pos_noise[1] * (2.0f * u_op.y + -1.0f);
-    rr[2] = init2 + p.reset_pos_noise[2] * (2.0f * u_op.z + -1.0f);
-    const f4 q = random_quat(u_or.x, u_or.y, u_or.z);
-    rr[3] = q.x; rr[4] = q.y; rr[5] = q.z; rr[6] = q.w;
-#pragma unroll
-    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
-    *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
-    b.furthest_hand_dist[env] = -1.0f;
-    b.random_force_prob[env] = force_prob_from(p, u_fp);
-    // episode bookkeeping (:1323-1347)
-    b.progress_buf[env] = 0;
-    b.reset_buf[env] = 0;
-    b.prev_episode_successes[env] = succ;
-    b.successes[env] = 0.0f;
-    b.prev_episode_true_objective[env] = tobj;
-    b.true_objective[env] = 0.0f;
-    b.lifted_object[env] = 0;
-  }
   // actor rows for set_actor_root_state_tensor_indexed / set_dof_*_indexed:
   // warp-aggregated append, rows of one env stay adjacent and ascending
   const unsigned m_any = __ballot_sync(0xffffffffu, any_goal);
@@ -161,18 +115,88 @@ __device__ __noinline__ void kuka_reset_env_scalars(const HaKukaParams& p, const
     if (n_hand) atomicAdd(b.reset_counts + 2, n_hand);
     atomicAdd(b.reset_counts + 3, __popc(m_any));
   }
-  root_base = __shfl_sync(0xffffffffu, root_base, 0);
-  hand_base = __shfl_sync(0xffffffffu, hand_base, 0);
-  const unsigned below = (1u << lane) - 1u;
-  if (any_goal) {
-    int k = root_base + 2 * __popc(m_rst & below) + __popc(m_goal_only & below);
-    if (rst) b.root_reset_indices[k++] = obj_row;
-    b.root_reset_indices[k] = goal_row;
+  // _reset_target; an env that is in both sets is drawn twice by the
+  // reference and the reset_idx draw wins (SURVEY appendix B)
+  const int sp = rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS;
+  const int sr = rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT;
+  f.succ = 0.f; f.tobj = 0.f; f.init0 = 0.f; f.init1 = 0.f; f.init2 = 0.f;
+  f.goal_row = 0; f.obj_row = 0; f.hand_row = 0;
+  if (any_goal) f.goal_row = p.root_regular ? env * p.actors_per_env + p.goal_slot : b.goal_actor[env];
+  if (rst) {
+    f.obj_row = p.root_regular ? env * p.actors_per_env + p.object_slot : b.object_actor[env];
+    f.hand_row = b.hand_actor[env];
+    f.succ = b.successes[env];
+    f.tobj = b.true_objective[env];
+    const float* init = b.object_init_state + (size_t)env * 13;
+    f.init0 = __ldg(init + 0); f.init1 = __ldg(init + 1); f.init2 = __ldg(init + 2);
   }
-  if (rst) b.hand_reset_indices[hand_base + __popc(m_rst & below)] = hand_row;
+  const int ec = any_goal ? env : 0;                  // idle lanes draw for env 0 (cheap, keeps the warp converged)
+  f.u_gp = kuka_draw4(R, ec, sp);
+  f.u_gr = kuka_draw4(R, ec, sr);
+  f.u_op = kuka_draw4(R, ec, HA_KUKA_RND_OBJ_POS);
+  f.u_or = kuka_draw4(R, ec, HA_KUKA_RND_OBJ_ROT);
+  f.u_fp = kuka_draw4(R, ec, HA_KUKA_RND_FORCE_PROB).x;
+  const unsigned below = (1u << lane) - 1u;
+  f.root_pos = 2 * __popc(m_rst & below) + __popc(m_goal_only & below);   // offsets inside the warp's list segments;
+  f.hand_pos = __popc(m_rst & below);                                     // the bases (lane 0's atomics) are added on use
+  f.root_base = root_base;
+  f.hand_base = hand_base;
 }
 
-__global__ void __launch_bounds__(kThreads, 8)
+// Apply phase: goal / object / episode-state reset of one env (lane = env) from the prefetched values.
+__device__ __forceinline__ void kuka_reset_apply(const HaKukaParams& p, const HaKukaBuffers& b, const KukaResetPrefetch& f, int env,
+                                                 bool rst, bool grst) {
+  const bool any_goal = rst || grst;
+  if (any_goal) {
+    float g[7];
+    g[0] = p.target_min[0] + f.u_gp.x * p.target_size[0];
+    g[1] = p.target_min[1] + f.u_gp.y * p.target_size[1];
+    g[2] = p.target_min[2] + f.u_gp.z * p.target_size[2];
+    const f4 q = random_quat(f.u_gr.x, f.u_gr.y, f.u_gr.z);
+    g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
+    float* gs = b.goal_states + (size_t)env * 13;
+    float* rr = b.root_state + (size_t)f.goal_row * 13;
+#pragma unroll
+    for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr[c] = g[c]; }
+#pragma unroll
+    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
+    b.reset_goal_buf[env] = 0;                       // reset_target_pose (:1194-1196)
+    b.near_goal_steps[env] = 0;
+    b.closest_keypoint_max_dist[env] = -1.0f;
+  }
+  if (rst) {
+    // reset_object_pose (:1198-1224); torch_rand_float(-1, 1) = 2 u - 1
+    float* rr = b.root_state + (size_t)f.obj_row * 13;
+    rr[0] = f.init0 + p.reset_pos_noise[0] * (2.0f * f.u_op.x + -1.0f);
+    rr[1] = f.init1 + p.reset_pos_noise[1] * (2.0f * f.u_op.y + -1.0f);
+    rr[2] = f.init2 + p.reset_pos_noise[2] * (2.0f * f.u_op.z + -1.0f);
+    const f4 q = random_quat(f.u_or.x, f.u_or.y, f.u_or.z);
+    rr[3] = q.x; rr[4] = q.y; rr[5] = q.z; rr[6] = q.w;
+#pragma unroll
+    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
+    *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
+    b.furthest_hand_dist[env] = -1.0f;
+    b.random_force_prob[env] = force_prob_from(p, f.u_fp);
+    // episode bookkeeping (:1323-1347)
+    b.progress_buf[env] = 0;
+    b.reset_buf[env] = 0;
+    b.prev_episode_successes[env] = f.succ;
+    b.successes[env] = 0.0f;
+    b.prev_episode_true_objective[env] = f.tobj;
+    b.true_objective[env] = 0.0f;
+    b.lifted_object[env] = 0;
+  }
+  const int root_base = __shfl_sync(0xffffffffu, f.root_base, 0);
+  const int hand_base = __shfl_sync(0xffffffffu, f.hand_base, 0);
+  if (any_goal) {
+    int k = root_base + f.root_pos;
+    if (rst) b.root_reset_indices[k++] = f.obj_row;
+    b.root_reset_indices[k] = f.goal_row;
+  }
+  if (rst) b.hand_reset_indices[hand_base + f.hand_pos] = f.hand_row;
+}
+
+__global__ void __launch_bounds__(kThreads, 7)
 kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b,
                 const float* __restrict__ actions, const float* __restrict__ ext_rand, const int mode) {
   constexpr int D = 23;
@@ -203,10 +227,8 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     }
   }
   // every warp reads the tile's masks (coalesced int64) -> identical ballots in all warps
-  const bool rst = valid && (b.reset_buf[env] != 0);
-  const bool grst = valid && !reset_only && (b.reset_goal_buf[env] != 0);
-  const unsigned m_rst = __ballot_sync(0xffffffffu, rst);
-  const unsigned m_goal = __ballot_sync(0xffffffffu, grst);
+  const long long raw_rst = valid ? b.reset_buf[env] : 0;
+  const long long raw_goal = (valid && !reset_only) ? b.reset_goal_buf[env] : 0;
   // force inputs of warp 1 (issued early as well)
   const bool do_force = (warp == 1) && p.force_enabled && !reset_only;
   float f_prob = 0.f, f_v[3] = {0.f, 0.f, 0.f};
@@ -220,26 +242,33 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       if (e < nvalid) f_v[i] = b.rb_forces[frow + (size_t)e * fstride + c];
     }
   }
-  if (tid < D) {
-    s.lo[tid] = p.dof_lower[tid]; s.hi[tid] = p.dof_upper[tid];
-    s.dflt[tid] = p.dof_default[tid]; s.noise[tid] = p.dof_reset_noise[tid];
-  }
   KukaRand R;
   R.ext = p.use_fast_rng ? nullptr : ext_rand;
   R.stride = HA_KUKA_RND_STRIDE(D);
   R.rng.seed = b.dynamic->rng_seed;
   R.rng.step = b.dynamic->rng_step;
+  if (tid < D) {
+    s.lo[tid] = p.dof_lower[tid]; s.hi[tid] = p.dof_upper[tid];
+    s.dflt[tid] = p.dof_default[tid]; s.noise[tid] = p.dof_reset_noise[tid];
+  }
+  const bool rst = raw_rst != 0, grst = raw_goal != 0;
+  const unsigned m_rst = __ballot_sync(0xffffffffu, rst);
+  const unsigned m_goal = __ballot_sync(0xffffffffu, grst);
+  const bool tile_resets = (m_rst | m_goal) != 0u;     // uniform over the CTA; about a third of the tiles per step
+  // warp 0: everything the scalar reset needs goes in flight now and is consumed at the very end
+  KukaResetPrefetch pf;
+  if (warp == 0 && tile_resets) kuka_reset_prefetch(p, b, R, env, lane, rst, grst, pf);
   __syncthreads();
-  if (m_rst != 0u) {                                   // uniform over the CTA; rare per tile
+  if (m_rst != 0u) {
     // DOF re-randomisation of the tile's reset envs, one warp per env (round robin), lane = dof
     unsigned m = m_rst;
     int rank = 0;
     while (m) {
       const int e = __ffs(m) - 1;
       m &= m - 1;
-      if ((rank++ & (kThreads / 32 - 1)) == warp) kuka_reset_dofs_warp(b, R, s, p.reset_dof_vel_noise, env0 + e, lane);
+      if ((rank++ & (kThreads / 32 - 1)) == warp) kuka_reset_dofs_warp(b, R, s, p.reset_dof_vel_noise, env0 + e, e, lane, reset_only);
     }
-    __syncthreads();                                   // new prev_targets visible to the element pass below
+    __syncthreads();                                   // s.pos visible to the element pass below
   }
 
   // ---------------- all threads: DOF targets, 4 consecutive elements per float4 ----------------
@@ -259,8 +288,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       for (int c = 0; c < 4; ++c) {
         const float lo = s.lo[d], hi = s.hi[d];
         float pv = pvv[c];
-        const bool er = (m_rst >> e) & 1u;
-        if (er) pv = __ldcg(b.prev_targets + base + f0 + c);     // re-randomised just above by another warp
+        if ((m_rst >> e) & 1u) pv = s.pos[e][d];       // re-randomised just above
         float x;
         if (d >= 7) {          // absolute control of the hand DOFs (:1377-1390)
           x = scale_to(av[c], lo, hi);
@@ -283,7 +311,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       const int e = f / D, d = f - e * D;
       const float lo = s.lo[d], hi = s.hi[d];
       const float av = __ldg(actions + base + f);
-      const float pv = __ldcg(b.prev_targets + base + f);
+      const float pv = ((m_rst >> e) & 1u) ? s.pos[e][d] : b.prev_targets[base + f];
       float x;
       if (d >= 7) { x = scale_to(av, lo, hi); x = ema * x + one_m_ema * pv; x = clamp_to(x, lo, hi); }
       else x = clamp_to(pv + gain * av, lo, hi);
@@ -292,9 +320,6 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       if (copy_actions) b.actions[base + f] = av;
     }
   }
-
-  // ---------------- warp 0: per-env scalar reset work (tiles with a reset only) ----------------
-  if (warp == 0 && (m_rst | m_goal) != 0u) kuka_reset_env_scalars(p, b, R, env, lane, rst, grst);
 
   // ---------------- warp 1: random forces on the object body ----------------
   if (warp == 1) {
@@ -328,6 +353,9 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
 #pragma unroll
     for (int k = warp - 2; k < HA_KUKA_N_EPISODE_TERMS; k += 2) b.rewards_episode[(size_t)k * n + env] = 0.0f;   // (:1341-1342)
   }
+
+  // ---------------- warp 0: per-env scalar reset work (tiles with a reset only) ----------------
+  if (warp == 0 && tile_resets) kuka_reset_apply(p, b, pf, env, rst, grst);
 }
 
 // advances the fast-mode RNG counter after an out-of-step reset (inside a step ha_kuka_post_step does it)
