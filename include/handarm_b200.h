@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define HA_ABI_VERSION 2
+#define HA_ABI_VERSION 3
 
 #define HA_OK 0
 #define HA_ERR_INVALID (-1)   /* bad argument / unsupported dimension */
@@ -125,6 +125,7 @@ typedef struct HaKukaParams {
   float dof_upper[HA_MAX_DOFS];
   float dof_default[HA_MAX_DOFS];
   float dof_reset_noise[HA_MAX_DOFS];   /* 0.1 arm / 0.1 fingers coefficients */
+  float dof_range_rcp[HA_MAX_DOFS];     /* fp32(1 / (dof_upper - dof_lower)), see ha_kuka_fill_derived() */
   float clamp_abs_obs;      /* <=0: no clamp; VecTask clip_obs already folded in (min) */
   /* reward */
   float lifting_bonus_threshold, lifting_bonus, lifting_rew_scale;
@@ -244,6 +245,9 @@ int ha_kuka_obs_dim(int n_arms, int n_keypoints);
 size_t ha_kuka_bytes_per_env_step(const HaKukaParams* p);
 size_t ha_kuka_post_bytes_per_env_step(const HaKukaParams* p);
 size_t ha_kuka_pre_bytes_per_env_step(const HaKukaParams* p);
+/* fills the derived fields of HaKukaParams (dof_range_rcp) from the primary ones; call once after
+ * dof_lower / dof_upper are set */
+void ha_kuka_fill_derived(HaKukaParams* p);
 /* initial value of stat_accum[i] (host writes these once before the first post step) */
 int64_t ha_kuka_stat_accum_init(int i);
 

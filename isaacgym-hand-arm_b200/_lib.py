@@ -144,6 +144,8 @@ def load():
     lib.ha_kuka_observe.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_reset_idx.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_obs_dim.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.ha_kuka_fill_derived.argtypes = [ctypes.c_void_p]
+    lib.ha_kuka_fill_derived.restype = None
     for fn in ("ha_kuka_bytes_per_env_step", "ha_kuka_post_bytes_per_env_step", "ha_kuka_pre_bytes_per_env_step"):
         getattr(lib, fn).argtypes = [ctypes.c_void_p]
     _lib = lib

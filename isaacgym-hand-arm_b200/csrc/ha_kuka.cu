@@ -1,5 +1,6 @@
 // C-ABI entry points of the AllegroKuka family (see include/handarm_b200.h).
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include "../../include/handarm_b200.h"
 #include "ha_host.h"
@@ -37,6 +38,8 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   HA_REQUIRE_ALIGNED16(b->obs_buf);
   HA_REQUIRE_ALIGNED16(b->closest_fingertip_dist);
   HA_REQUIRE_ALIGNED16(b->finger_rew_coeffs);
+  HA_REQUIRE_ALIGNED16(b->object_keypoint_offsets);
+  HA_REQUIRE_ALIGNED16(b->object_scales);
   HA_REQUIRE_ALIGNED16(b->prev_targets);
   HA_REQUIRE_ALIGNED16(b->cur_targets);
   HA_REQUIRE_ALIGNED16(b->actions);
@@ -46,17 +49,37 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   return HA_OK;
 }
 
+int post_grid_limit(int blocks_per_sm) {
+  static int sm_count = 0;
+  static int override_grid = -1;
+  if (sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+    const char* e = getenv("HA_POST_GRID");      // tuning hook: force the persistent grid size
+    override_grid = e ? atoi(e) : 0;
+  }
+  return override_grid > 0 ? override_grid : sm_count * blocks_per_sm;
+}
+
 template <int K>
 int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {
   using S = ha::KukaPostSmem<K>;
-  static bool configured = false;
-  if (!configured) {
+  static int blocks_per_sm = 0;
+  if (blocks_per_sm == 0) {
     int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka_post_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
                             "cudaFuncSetAttribute(kuka_post_kernel)");
     if (rc) return rc;
-    configured = true;
+    int nb = 0;
+    rc = ha::check_cuda(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ha::kuka_post_kernel<K>, ha::kPostThreads, sizeof(S)),
+                        "cudaOccupancyMaxActiveBlocksPerMultiprocessor(kuka_post_kernel)");
+    if (rc) return rc;
+    blocks_per_sm = nb > 0 ? nb : 1;
   }
-  const int grid = (p->n_envs + ha::kTile - 1) / ha::kTile;
+  // persistent CTAs: one wave of resident CTAs walks the 32-env tiles
+  const int n_tiles = (p->n_envs + ha::kTile - 1) / ha::kTile;
+  const int limit = post_grid_limit(blocks_per_sm);
+  const int grid = n_tiles < limit ? n_tiles : limit;
   ha::kuka_post_kernel<K><<<grid, ha::kPostThreads, sizeof(S), st>>>(*p, *b, mode);
   return ha::check_cuda(cudaGetLastError(), "kuka_post_kernel launch");
 }
@@ -94,6 +117,14 @@ size_t ha_kuka_pre_bytes_per_env_step(const HaKukaParams* p) {
 
 size_t ha_kuka_bytes_per_env_step(const HaKukaParams* p) {
   return ha_kuka_post_bytes_per_env_step(p) + ha_kuka_pre_bytes_per_env_step(p);
+}
+
+void ha_kuka_fill_derived(HaKukaParams* p) {
+  if (!p) return;
+  for (int d = 0; d < HA_MAX_DOFS; ++d) {
+    const float range = p->dof_upper[d] - p->dof_lower[d];          // fp32 difference, as the kernel forms it
+    p->dof_range_rcp[d] = range != 0.0f ? (float)(1.0 / (double)range) : 0.0f;
+  }
 }
 
 int64_t ha_kuka_stat_accum_init(int i) { return ha::stat_is_max(i) ? (int64_t)ha::kStatMaxInit : 0; }

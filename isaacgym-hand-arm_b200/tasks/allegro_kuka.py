@@ -256,6 +256,7 @@ class AllegroKukaBase(VecTask):
         for d in range(self.num_hand_arm_dofs):
             p.dof_lower[d], p.dof_upper[d], p.dof_default[d] = float(lo[d]), float(hi[d]), float(dflt[d])
             p.dof_reset_noise[d] = self.reset_dof_pos_noise_arm if d < 7 else self.reset_dof_pos_noise_fingers
+        self._lib.ha_kuka_fill_derived(ctypes.byref(p))
         clamp = self.clamp_abs_observations if self.clamp_abs_observations > 0 else math.inf
         clamp = min(clamp, self.clip_obs)            # clamp_obs (:1174-1176) then the VecTask clip (vec_task.py:432)
         p.clamp_abs_obs = clamp if math.isfinite(clamp) else 0.0
