@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--cpu-steps", type=int, default=0, help="steps of the CPU baseline sample (0 = auto, about 10-20 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--layout", default="isaacgym", choices=["isaacgym", "soa"],
+                    help="simulator state layout: Isaac Gym AoS rows or component-major planes (HA_STATE_SOA)")
     ap.add_argument("--l2-fetch", type=int, default=0, help="cudaLimitMaxL2FetchGranularity in bytes (0 = leave the driver default)")
     return ap.parse_args()
 
@@ -158,7 +160,7 @@ def build_blocks(args, device):
     tasks, actions = [], []
     for b in range(args.blocks):
         cfg = hcfg.load_task_config("AllegroKuka", num_envs=args.envs, sim_device=device)
-        sim = SyntheticSim(args.envs, KUKA_LAYOUT, device, seed=1234 + 100 * rank + b, snapshots=args.snapshots)
+        sim = SyntheticSim(args.envs, KUKA_LAYOUT, device, seed=1234 + 100 * rank + b, snapshots=args.snapshots, state_layout=args.layout)
         task = AllegroKukaReorientation(cfg, device, device, 0, True, sim=sim, seed=1234 + rank)
         task.seed_rng(1234 + 100 * rank + b)
         sim.fill_kuka(goal_states=None)
@@ -352,7 +354,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "envs_per_gpu": N, "env_blocks": B, "snapshots_per_block": S,
+            "config": {"workload": WORKLOAD, "envs_per_gpu": N, "state_layout": args.layout, "env_blocks": B, "snapshots_per_block": S,
                        "l2": f"inputs larger than L2: {B} env blocks stepped round-robin, {B}x{N * (post_bytes + pre_bytes) / 1e6:.0f} MB "
                              "algorithmic bytes per round", "launch": f"CUDA graph of {per_graph} steps", "rng": "in-kernel Philox"},
             "roofline": {"bound": "hbm", "kernel": "kuka_post_kernel<4>", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",

@@ -57,6 +57,16 @@ typedef void* ha_stream_t;
 
 enum { HA_KUKA_REORIENTATION = 0, HA_KUKA_REGRASPING = 1, HA_KUKA_THROW = 2 };
 
+/* Layout of the simulator-owned root / rigid-body state tensors.
+ *   HA_STATE_ISAACGYM  what Isaac Gym's tensor API hands out (allegro_kuka_base.py:280-295):
+ *                      root [n_envs*actors_per_env, 13], rigid-body [n_envs*n_bodies, 13] (AoS,
+ *                      52-byte rows); every needed row costs whole 128-byte DRAM lines.
+ *   HA_STATE_SOA       component-major planes for producers that can emit them (the north star's
+ *                      "coalesced 128-bit loads of SoA state"): root [actors_per_env][13][n_envs],
+ *                      rigid-body [n_bodies][13][n_envs]; needs the regular actor numbering
+ *                      (root_regular).  dof_state keeps Isaac Gym's [n_envs, dofs, 2] in both. */
+enum { HA_STATE_ISAACGYM = 0, HA_STATE_SOA = 1 };
+
 /* reward terms kept per episode, in the reference's key order
  * (allegro_kuka_base.py:355-368) */
 enum {
@@ -118,6 +128,7 @@ typedef struct HaKukaParams {
   int32_t actors_per_env;
   int32_t object_slot;
   int32_t goal_slot;
+  int32_t state_layout;     /* HA_STATE_* */
 
   float palm_offset[3];
   float tip_offset[HA_MAX_TIPS][3];
@@ -170,6 +181,7 @@ typedef struct HaKukaBuffers {
   const int32_t* hand_actor;     /* [n_envs, n_arms] rows of the arm actors */
   /* ---- task constants per env ---- */
   const float* object_init_state;     /* [n_envs, 13] */
+  const float* object_init_z;         /* [n_envs] compact copy of object_init_state[:, 2] (nullable: read from the rows) */
   const float* object_keypoint_offsets; /* [n_envs, K, 3] */
   const float* object_scales;         /* [n_envs, 3] */
   const float* finger_rew_coeffs;     /* [n_envs, n_tips] */

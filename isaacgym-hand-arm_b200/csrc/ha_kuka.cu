@@ -43,6 +43,12 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   HA_REQUIRE_ALIGNED16(b->prev_targets);
   HA_REQUIRE_ALIGNED16(b->cur_targets);
   HA_REQUIRE_ALIGNED16(b->actions);
+  HA_REQUIRE(p->state_layout == HA_STATE_ISAACGYM || p->state_layout == HA_STATE_SOA, "unknown state_layout %d", p->state_layout);
+  HA_REQUIRE(p->state_layout != HA_STATE_SOA || p->root_regular, "HA_STATE_SOA needs the regular actor numbering (root_regular)");
+  if (p->state_layout == HA_STATE_SOA) {
+    HA_REQUIRE_ALIGNED16(b->root_state);
+    HA_REQUIRE_ALIGNED16(b->rigid_body_state);
+  }
   if (p->root_regular)
     HA_REQUIRE(p->actors_per_env > 0 && p->object_slot >= 0 && p->object_slot < p->actors_per_env && p->goal_slot < p->actors_per_env,
                "root_regular needs 0 <= object_slot, goal_slot < actors_per_env");
@@ -62,16 +68,16 @@ int post_grid_limit(int blocks_per_sm) {
   return override_grid > 0 ? override_grid : sm_count * blocks_per_sm;
 }
 
-template <int K>
+template <int K, bool SOA>
 int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {
   using S = ha::KukaPostSmem<K>;
   static int blocks_per_sm = 0;
   if (blocks_per_sm == 0) {
-    int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka_post_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
+    int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka_post_kernel<K, SOA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
                             "cudaFuncSetAttribute(kuka_post_kernel)");
     if (rc) return rc;
     int nb = 0;
-    rc = ha::check_cuda(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ha::kuka_post_kernel<K>, ha::kPostThreads, sizeof(S)),
+    rc = ha::check_cuda(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ha::kuka_post_kernel<K, SOA>, ha::kPostThreads, sizeof(S)),
                         "cudaOccupancyMaxActiveBlocksPerMultiprocessor(kuka_post_kernel)");
     if (rc) return rc;
     blocks_per_sm = nb > 0 ? nb : 1;
@@ -80,7 +86,7 @@ int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStr
   const int n_tiles = (p->n_envs + ha::kTile - 1) / ha::kTile;
   const int limit = post_grid_limit(blocks_per_sm);
   const int grid = n_tiles < limit ? n_tiles : limit;
-  ha::kuka_post_kernel<K><<<grid, ha::kPostThreads, sizeof(S), st>>>(*p, *b, mode);
+  ha::kuka_post_kernel<K, SOA><<<grid, ha::kPostThreads, sizeof(S), st>>>(*p, *b, mode);
   return ha::check_cuda(cudaGetLastError(), "kuka_post_kernel launch");
 }
 
@@ -153,8 +159,9 @@ int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float
 static int post_dispatch(const HaKukaParams* p, const HaKukaBuffers* b, int mode, ha_stream_t stream) {
   int rc = validate_kuka(p, b);
   if (rc) return rc;
-  if (p->n_keypoints == 4) return launch_post<4>(p, b, mode, (cudaStream_t)stream);
-  return launch_post<1>(p, b, mode, (cudaStream_t)stream);
+  const bool soa = p->state_layout == HA_STATE_SOA;
+  if (p->n_keypoints == 4) return soa ? launch_post<4, true>(p, b, mode, (cudaStream_t)stream) : launch_post<4, false>(p, b, mode, (cudaStream_t)stream);
+  return soa ? launch_post<1, true>(p, b, mode, (cudaStream_t)stream) : launch_post<1, false>(p, b, mode, (cudaStream_t)stream);
 }
 
 int ha_kuka_post_step(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream) {

@@ -212,13 +212,41 @@ __device__ __forceinline__ float div_by_const(float a, float b, float r) {
 }
 
 // Issue the cp.async copies of one tile (all 128 threads).  Idle envs of a ragged last tile re-read the last valid env.
-template <int K>
+template <int K, bool SOA>
 __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaKukaBuffers& b, KukaPostStage<K>& s, const int env0,
                                                 const int nvalid, const int tid) {
   using S = KukaPostStage<K>;
   const int last = nvalid - 1;
   const size_t rbs = (size_t)p.n_bodies * 13;
   const float* rb0 = b.rigid_body_state + (size_t)env0 * rbs;
+  if constexpr (SOA) {
+    // component planes [body][13][n_envs]: every (body, component) row of the tile is 32 consecutive floats.
+    // rows 0..12 palm, 13..25 object root, 26..53 fingertip (t, c); staged component-major [row][32].
+    constexpr int kRows = 13 + 13 + kT1 * 7;
+    const size_t n = (size_t)p.n_envs;
+    auto row_src = [&](int r) -> const float* {
+      if (r < 13) return b.rigid_body_state + ((size_t)p.palm_body[0] * 13 + r) * n + env0;
+      if (r < 26) return b.root_state + ((size_t)p.object_slot * 13 + (r - 13)) * n + env0;
+      const int rr = r - 26, t = rr / 7, c = rr - 7 * t;
+      return b.rigid_body_state + ((size_t)p.tip_body[t] * 13 + c) * n + env0;
+    };
+    auto row_dst = [&](int r) -> float* { return r < 13 ? s.palm + r * kTile : r < 26 ? s.obj + (r - 13) * kTile : s.tip + (r - 26) * kTile; };
+    if (nvalid == kTile && (p.n_envs & 3) == 0) {       // plane rows are 16-byte aligned: 8 x 16-byte copies per row
+#pragma unroll
+      for (int i = 0; i < (kRows * 8 + kPostThreads - 1) / kPostThreads; ++i) {
+        const int q = tid + kPostThreads * i;
+        if (q < kRows * 8) {
+          const int r = q >> 3, ch = q & 7;
+          cp_async16(row_dst(r) + 4 * ch, row_src(r) + 4 * ch);
+        }
+      }
+    } else {
+      for (int q = tid; q < kRows * kTile; q += kPostThreads) {
+        const int r = q >> 5, e = q & 31;
+        cp_async4(row_dst(r) + e, row_src(r) + min(e, last));
+      }
+    }
+  } else {
   {   // palm rows, 13 floats each
     const float* src = rb0 + (size_t)p.palm_body[0] * 13;
 #pragma unroll
@@ -249,6 +277,7 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
       cp_async4(s.tip + e * S::kTipW + r, rb0 + (size_t)min(e, last) * rbs + (size_t)p.tip_body[t] * 13 + c);
     }
   }
+  }   // !SOA
   {   // goal pose rows (7 of 13 floats)
 #pragma unroll
     for (int i = 0; i < (kTile * 7 + kPostThreads - 1) / kPostThreads; ++i) {
@@ -301,7 +330,7 @@ __device__ __forceinline__ void kuka_post_load_env(const HaKukaParams& p, const 
   r.furthest = b.furthest_hand_dist[env];
   r.near = b.near_goal_steps[env];
   r.lifted = b.lifted_object[env];
-  r.initz = ldg(b.object_init_state + (size_t)env * 13 + 2);
+  r.initz = b.object_init_z ? ldg(b.object_init_z + env) : ldg(b.object_init_state + (size_t)env * 13 + 2);
   r.prev_ep = b.prev_episode_successes[env];
   r.ctip = *reinterpret_cast<const float4*>(b.closest_fingertip_dist + (size_t)env * 4);
   r.coef = __ldg(reinterpret_cast<const float4*>(b.finger_rew_coeffs + (size_t)env * 4));
@@ -317,7 +346,7 @@ __device__ __forceinline__ void kuka_post_load_env(const HaKukaParams& p, const 
   }
 }
 
-template <int K>
+template <int K, bool SOA>
 __global__ void __launch_bounds__(kPostThreads, 4)
 kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b, const int mode) {
   using SM = KukaPostSmem<K>;
@@ -340,7 +369,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   }
   KukaPostAcc acc;
 
-  if (tile < n_tiles) kuka_post_issue<K>(p, b, sm.st[0], tile * kTile, min(kTile, n - tile * kTile), tid);
+  if (tile < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[0], tile * kTile, min(kTile, n - tile * kTile), tid);
   cp_async_commit();
 
   for (int it = 0; tile < n_tiles; ++it, tile += stride) {
@@ -351,7 +380,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     const int env = env0 + min(lane, nvalid - 1);       // idle lanes of a ragged tile re-read a valid env; stores are predicated
     {   // next tile's copies go in flight before this tile is touched
       const int next = tile + stride;
-      if (next < n_tiles) kuka_post_issue<K>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid);
+      if (next < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid);
       cp_async_commit();
     }
     KukaPostEnvState r;
@@ -361,18 +390,19 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
 
     float* o = sm.obs + lane * OBS;
     float obj_z = 0.f;
+    // staged rows: [e][13] / [e][29] images of the AoS rows, or component-major [c][32] planes (SOA)
+    auto PALM = [&](int c) { return SOA ? S.palm[c * kTile + lane] : S.palm[lane * 13 + c]; };
+    auto OBJ = [&](int c) { return SOA ? S.obj[c * kTile + lane] : S.obj[lane * 13 + c]; };
+    auto TIP = [&](int t, int c) { return SOA ? S.tip[(t * 7 + c) * kTile + lane] : S.tip[lane * TIPW + t * 7 + c]; };
     if (warp == 0) {
       // palm_center_pos = palm_pos + quat_rotate(palm_rot, palm_offset)   (:1013-1017); fingertips (:1033-1052)
-      const float* pr = S.palm + lane * 13;
-      const float* ob = S.obj + lane * 13;
-      const f3 pc = f3{pr[0], pr[1], pr[2]} + quat_rotate(f4{pr[3], pr[4], pr[5], pr[6]}, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
-      const f3 obj_pos = {ob[0], ob[1], ob[2]};
+      const f3 pc = f3{PALM(0), PALM(1), PALM(2)} + quat_rotate(f4{PALM(3), PALM(4), PALM(5), PALM(6)}, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
+      const f3 obj_pos = {OBJ(0), OBJ(1), OBJ(2)};
       o[L.palm_pos + 0] = pc.x; o[L.palm_pos + 1] = pc.y; o[L.palm_pos + 2] = pc.z;
 #pragma unroll
       for (int t = 0; t < kT1; ++t) {
-        const float* tr = S.tip + lane * TIPW + t * 7;
-        const f3 to = f3{tr[0], tr[1], tr[2]} +
-                      quat_rotate(f4{tr[3], tr[4], tr[5], tr[6]}, f3{p.tip_offset[t][0], p.tip_offset[t][1], p.tip_offset[t][2]});
+        const f3 to = f3{TIP(t, 0), TIP(t, 1), TIP(t, 2)} +
+                      quat_rotate(f4{TIP(t, 3), TIP(t, 4), TIP(t, 5), TIP(t, 6)}, f3{p.tip_offset[t][0], p.tip_offset[t][1], p.tip_offset[t][2]});
         const f3 rel_obj = to - obj_pos, rel_palm = to - pc;
         sm.xch[t * kTile + lane] = norm3(rel_obj);
         o[L.tip_rel_palm + 3 * t + 0] = rel_palm.x;
@@ -381,12 +411,10 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       }
     } else if (warp == 1) {
       // keypoints (:1057-1073)
-      const float* pr = S.palm + lane * 13;
-      const float* ob = S.obj + lane * 13;
       const float* gl = S.goal + lane * 7;
-      const f3 pc = f3{pr[0], pr[1], pr[2]} + quat_rotate(f4{pr[3], pr[4], pr[5], pr[6]}, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
-      const f3 obj_pos = {ob[0], ob[1], ob[2]}, goal_pos = {gl[0], gl[1], gl[2]};
-      const f4 obj_rot = {ob[3], ob[4], ob[5], ob[6]}, goal_rot = {gl[3], gl[4], gl[5], gl[6]};
+      const f3 pc = f3{PALM(0), PALM(1), PALM(2)} + quat_rotate(f4{PALM(3), PALM(4), PALM(5), PALM(6)}, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
+      const f3 obj_pos = {OBJ(0), OBJ(1), OBJ(2)}, goal_pos = {gl[0], gl[1], gl[2]};
+      const f4 obj_rot = {OBJ(3), OBJ(4), OBJ(5), OBJ(6)}, goal_rot = {gl[3], gl[4], gl[5], gl[6]};
       float kpv[3 * K];
       if constexpr (K == 4) {
         const float4* k4 = reinterpret_cast<const float4*>(S.kp) + lane * 3;
@@ -429,11 +457,9 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       sm.xch[6 * kTile + lane] = sh;
     } else {
       // palm rot + vel (:1112-1117), object rot + vel (:1120), object scales (:1143)
-      const float* pr = S.palm + lane * 13;
-      const float* ob = S.obj + lane * 13;
-      obj_z = ob[2];
+      obj_z = OBJ(2);
 #pragma unroll
-      for (int c = 0; c < 10; ++c) { o[L.palm_rot_vel + c] = pr[3 + c]; o[L.obj_rot_vel + c] = ob[3 + c]; }
+      for (int c = 0; c < 10; ++c) { o[L.palm_rot_vel + c] = PALM(3 + c); o[L.obj_rot_vel + c] = OBJ(3 + c); }
 #pragma unroll
       for (int c = 0; c < 3; ++c) o[L.scales + c] = S.scales[lane * 3 + c];
     }

@@ -143,6 +143,17 @@ __device__ __forceinline__ void kuka_reset_prefetch(const HaKukaParams& p, const
   f.hand_base = hand_base;
 }
 
+// One actor's 13-float root state: a 52-byte row (Isaac Gym layout) or 13 plane elements n_envs apart (HA_STATE_SOA)
+struct RootRow {
+  float* base;
+  size_t stride;
+  __device__ __forceinline__ float& at(int c) const { return base[(size_t)c * stride]; }
+};
+__device__ __forceinline__ RootRow root_row(const HaKukaParams& p, const HaKukaBuffers& b, int actor_row, int env, int slot) {
+  if (p.state_layout == HA_STATE_SOA) return {b.root_state + (size_t)slot * 13 * p.n_envs + env, (size_t)p.n_envs};
+  return {b.root_state + (size_t)actor_row * 13, 1};
+}
+
 // Apply phase: goal / object / episode-state reset of one env (lane = env) from the prefetched values.
 __device__ __forceinline__ void kuka_reset_apply(const HaKukaParams& p, const HaKukaBuffers& b, const KukaResetPrefetch& f, int env,
                                                  bool rst, bool grst) {
@@ -155,25 +166,25 @@ __device__ __forceinline__ void kuka_reset_apply(const HaKukaParams& p, const Ha
     const f4 q = random_quat(f.u_gr.x, f.u_gr.y, f.u_gr.z);
     g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
     float* gs = b.goal_states + (size_t)env * 13;
-    float* rr = b.root_state + (size_t)f.goal_row * 13;
+    const RootRow rr = root_row(p, b, f.goal_row, env, p.goal_slot);
 #pragma unroll
-    for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr[c] = g[c]; }
+    for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr.at(c) = g[c]; }
 #pragma unroll
-    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
+    for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
     b.reset_goal_buf[env] = 0;                       // reset_target_pose (:1194-1196)
     b.near_goal_steps[env] = 0;
     b.closest_keypoint_max_dist[env] = -1.0f;
   }
   if (rst) {
     // reset_object_pose (:1198-1224); torch_rand_float(-1, 1) = 2 u - 1
-    float* rr = b.root_state + (size_t)f.obj_row * 13;
-    rr[0] = f.init0 + p.reset_pos_noise[0] * (2.0f * f.u_op.x + -1.0f);
-    rr[1] = f.init1 + p.reset_pos_noise[1] * (2.0f * f.u_op.y + -1.0f);
-    rr[2] = f.init2 + p.reset_pos_noise[2] * (2.0f * f.u_op.z + -1.0f);
+    const RootRow rr = root_row(p, b, f.obj_row, env, p.object_slot);
+    rr.at(0) = f.init0 + p.reset_pos_noise[0] * (2.0f * f.u_op.x + -1.0f);
+    rr.at(1) = f.init1 + p.reset_pos_noise[1] * (2.0f * f.u_op.y + -1.0f);
+    rr.at(2) = f.init2 + p.reset_pos_noise[2] * (2.0f * f.u_op.z + -1.0f);
     const f4 q = random_quat(f.u_or.x, f.u_or.y, f.u_or.z);
-    rr[3] = q.x; rr[4] = q.y; rr[5] = q.z; rr[6] = q.w;
+    rr.at(3) = q.x; rr.at(4) = q.y; rr.at(5) = q.z; rr.at(6) = q.w;
 #pragma unroll
-    for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
+    for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
     *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
     b.furthest_hand_dist[env] = -1.0f;
     b.random_force_prob[env] = force_prob_from(p, f.u_fp);

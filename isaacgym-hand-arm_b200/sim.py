@@ -91,7 +91,14 @@ def _rand_unit_quat(gen: torch.Generator, shape) -> torch.Tensor:
 class SyntheticSim:
     """Owns the simulator-side tensors and a ring of ``S`` pre-generated snapshots."""
 
-    def __init__(self, num_envs: int, layout: ActorLayout, device: str = "cuda:0", seed: int = 1234, snapshots: int = 1):
+    def __init__(self, num_envs: int, layout: ActorLayout, device: str = "cuda:0", seed: int = 1234, snapshots: int = 1,
+                 state_layout: str = "isaacgym"):
+        """``state_layout``: ``"isaacgym"`` = the tensor API's AoS rows (root ``[N*A, 13]``, rigid-body ``[N*B, 13]``);
+        ``"soa"`` = component-major planes (root ``[A, 13, N]``, rigid-body ``[B, 13, N]``, ``HA_STATE_SOA``) for producers
+        that can emit them.  ``dof_state`` is ``[N*D, 2]`` in both."""
+        if state_layout not in ("isaacgym", "soa"):
+            raise ValueError(f"unknown state_layout {state_layout!r}")
+        self.state_layout = state_layout
         self.num_envs = int(num_envs)
         self.layout = layout
         self.device = torch.device(device)
@@ -101,8 +108,12 @@ class SyntheticSim:
         self.calls: List[Tuple[str, tuple]] = []
         self.record_calls = True
         N, L = self.num_envs, layout
-        self.root_snap = [torch.zeros(N * L.actors_per_env, 13, device=self.device) for _ in range(self.n_snapshots)]
-        self.rb_snap = [torch.zeros(N * L.bodies_per_env, 13, device=self.device) for _ in range(self.n_snapshots)]
+        if state_layout == "soa":
+            self.root_snap = [torch.zeros(L.actors_per_env, 13, N, device=self.device) for _ in range(self.n_snapshots)]
+            self.rb_snap = [torch.zeros(L.bodies_per_env, 13, N, device=self.device) for _ in range(self.n_snapshots)]
+        else:
+            self.root_snap = [torch.zeros(N * L.actors_per_env, 13, device=self.device) for _ in range(self.n_snapshots)]
+            self.rb_snap = [torch.zeros(N * L.bodies_per_env, 13, device=self.device) for _ in range(self.n_snapshots)]
         self.dof_snap = [torch.zeros(N * L.dofs_per_env, 2, device=self.device) for _ in range(self.n_snapshots)]
 
     # ---- the acquire_* surface -----------------------------------------------------------
@@ -117,6 +128,15 @@ class SyntheticSim:
     @property
     def dof_state(self) -> torch.Tensor:
         return self.dof_snap[self.cursor]
+
+    # layout-independent [N, rows, 13] views (strided in the "soa" layout; writes go through)
+    def root_rows(self, snapshot: Optional[int] = None) -> torch.Tensor:
+        t = self.root_snap[self.cursor if snapshot is None else snapshot]
+        return t.permute(2, 0, 1) if self.state_layout == "soa" else t.view(self.num_envs, -1, 13)
+
+    def body_rows(self, snapshot: Optional[int] = None) -> torch.Tensor:
+        t = self.rb_snap[self.cursor if snapshot is None else snapshot]
+        return t.permute(2, 0, 1) if self.state_layout == "soa" else t.view(self.num_envs, -1, 13)
 
     def simulate(self) -> None:
         """One opaque physics step: expose the next pre-generated snapshot (pointer swap, no copy)."""
@@ -165,6 +185,6 @@ class SyntheticSim:
                 g = goal_states.detach().cpu()
                 root[hit, L.object_actor, 0:7] = g[hit, 0:7] + 1e-3 * torch.randn(int(hit.sum()), 7, generator=gen)
                 rb[:, L.object_body] = root[:, L.object_actor]
-            self.root_snap[s].copy_(root.view(-1, 13))
-            self.rb_snap[s].copy_(rb.view(-1, 13))
+            self.root_rows(s).copy_(root)
+            self.body_rows(s).copy_(rb)
             self.dof_snap[s].copy_(dof.view(-1, 2))

@@ -222,6 +222,7 @@ class AllegroKukaBase(VecTask):
         self._object_actor_i32 = self.object_indices.to(torch.int32)
         self._goal_actor_i32 = self.goal_object_indices.to(torch.int32)
         self._hand_actor_i32 = self.allegro_hand_indices.to(torch.int32)
+        self._object_init_z = self.object_init_state[:, 2].contiguous()   # compact copy for the per-step read (task constant)
         self._dynamic = torch.zeros(8, **f)          # HaKukaDynamic (32 bytes)
         self.ext_rand: Optional[torch.Tensor] = None   # parity mode: [N, HA_KUKA_RND_STRIDE] raw draws
         self.use_fast_rng = True
@@ -288,6 +289,7 @@ class AllegroKukaBase(VecTask):
         ar = torch.arange(self.num_envs, dtype=torch.long, device=self.device) * L.actors_per_env
         regular = bool(torch.equal(self.object_indices, ar + L.object_actor)) and bool(torch.equal(self.goal_object_indices, ar + L.goal_actor))
         p.root_regular, p.actors_per_env, p.object_slot, p.goal_slot = int(regular), L.actors_per_env, L.object_actor, L.goal_actor
+        p.state_layout = C["HA_STATE_SOA"] if self.sim.state_layout == "soa" else C["HA_STATE_ISAACGYM"]
         self._params = p
         self._observe_params = _lib.HaKukaParams.from_buffer_copy(p)
         self._observe_params.clamp_abs_obs = 0.0    # VecTask.reset() clips on the host side copy only
@@ -303,7 +305,7 @@ class AllegroKukaBase(VecTask):
         self._bound = dict(
             root_state=self.sim.root_state, rigid_body_state=self.sim.rigid_body_state, dof_state=self.sim.dof_state,
             object_actor=self._object_actor_i32, goal_actor=self._goal_actor_i32, hand_actor=self._hand_actor_i32,
-            object_init_state=self.object_init_state, object_keypoint_offsets=self.object_keypoint_offsets,
+            object_init_state=self.object_init_state, object_init_z=self._object_init_z, object_keypoint_offsets=self.object_keypoint_offsets,
             object_scales=self.object_scales, finger_rew_coeffs=self.finger_rew_coeffs, goal_states=self.goal_states,
             obs_buf=self.obs_buf, rew_buf=self.rew_buf, reset_buf=self.reset_buf, reset_goal_buf=self.reset_goal_buf,
             progress_buf=self.progress_buf, randomize_buf=self.randomize_buf, timeout_buf=self.timeout_buf, successes=self.successes,
@@ -351,11 +353,11 @@ class AllegroKukaBase(VecTask):
     # ---- properties mirroring reference views --------------------------------------------------
     @property
     def root_state_tensor(self):
-        return self.sim.root_state
+        return self.sim.root_state if self.sim.state_layout == "isaacgym" else self.sim.root_rows()
 
     @property
     def rigid_body_states(self):
-        return self.sim.rigid_body_state.view(self.num_envs, -1, 13)
+        return self.sim.body_rows()
 
     @property
     def dof_state(self):

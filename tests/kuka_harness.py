@@ -16,9 +16,12 @@ DIRECT = ["goal_states", "object_init_state", "object_keypoint_offsets", "object
           "closest_fingertip_dist", "furthest_hand_dist", "prev_targets", "cur_targets", "actions", "rb_forces", "random_force_prob"]
 
 
-def make_task(n: int, device: str = "cuda:0", overrides=None, snapshots: int = 1) -> AllegroKukaReorientation:
+STATE_LAYOUT = "isaacgym"      # tests switch this to "soa" to run the same cases on the component-major producer layout
+
+
+def make_task(n: int, device: str = "cuda:0", overrides=None, snapshots: int = 1, state_layout=None) -> AllegroKukaReorientation:
     cfg = hcfg.load_task_config("AllegroKuka", num_envs=n, sim_device=device, overrides=overrides)
-    sim = SyntheticSim(n, KUKA_LAYOUT, device, seed=1, snapshots=snapshots)
+    sim = SyntheticSim(n, KUKA_LAYOUT, device, seed=1, snapshots=snapshots, state_layout=state_layout or STATE_LAYOUT)
     return AllegroKukaReorientation(cfg, device, device, 0, True, sim=sim)
 
 
@@ -28,8 +31,9 @@ def load_state(task, st: Dict[str, torch.Tensor]) -> None:
         getattr(task, k).copy_(st[k].to(dev))
     task._rewards_episode.copy_(st["rewards_episode"].to(dev))
     task._episode_cumulative.copy_(st["episode_cumulative"].to(dev))
-    task.sim.root_state.copy_(st["root_state"].to(dev))
-    task.sim.rigid_body_state.copy_(st["rigid_body_state"].to(dev))
+    task._object_init_z.copy_(st["object_init_state"][:, 2].to(dev))
+    task.sim.root_rows().copy_(st["root_state"].view(task.num_envs, -1, 13).to(dev))
+    task.sim.body_rows().copy_(st["rigid_body_state"].view(task.num_envs, -1, 13).to(dev))
     task.sim.dof_state.copy_(st["dof_state"].view(-1, 2).to(dev))
 
 
@@ -38,8 +42,8 @@ def dump_state(task) -> Dict[str, torch.Tensor]:
     out = {k: getattr(task, k).detach().cpu().clone() for k in DIRECT}
     out["rewards_episode"] = task._rewards_episode.cpu().clone()
     out["episode_cumulative"] = task._episode_cumulative.cpu().clone()
-    out["root_state"] = task.sim.root_state.cpu().clone()
-    out["rigid_body_state"] = task.sim.rigid_body_state.cpu().clone()
+    out["root_state"] = task.sim.root_rows().cpu().reshape(-1, 13).clone()
+    out["rigid_body_state"] = task.sim.body_rows().cpu().reshape(-1, 13).clone()
     out["dof_state"] = task.sim.dof_state.view(task.num_envs, -1, 2).cpu().clone()
     n_root, n_hand = int(task.reset_counts[0]), int(task.reset_counts[1])
     out["root_rows"] = task.root_reset_indices[:n_root].cpu().clone()

@@ -14,6 +14,16 @@ from tests import kuka_harness as kh
 
 pytestmark = pytest.mark.gpu
 
+
+
+@pytest.fixture(autouse=True, params=["isaacgym", "soa"])
+def state_layout(request):
+    """Every case runs on both producer layouts: Isaac Gym's AoS rows and the component-major planes (HA_STATE_SOA)."""
+    kh.STATE_LAYOUT = request.param
+    yield request.param
+    kh.STATE_LAYOUT = "isaacgym"
+
+
 RTOL, ATOL = 1e-5, 2e-6
 EXACT = ["reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf", "timeout_buf", "near_goal_steps", "lifted_object"]
 FLOAT = ["obs_buf", "rew_buf", "successes", "prev_episode_successes", "true_objective", "prev_episode_true_objective",
