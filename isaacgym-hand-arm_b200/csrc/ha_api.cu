@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/handarm_b200.h"
@@ -16,6 +17,15 @@ int set_error(int code, const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
   return code;
+}
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("HA_PDL");
+    v = (e && e[0] == '1') ? 1 : 0;      // opt-in: measured neutral on B200 (the post kernel fills the register file, so no co-residency)
+  }
+  return v == 1;
 }
 
 int check_cuda(cudaError_t e, const char* what) {

@@ -137,4 +137,10 @@ __device__ __forceinline__ float warp_max(float v) {
 
 __device__ __forceinline__ float ldg(const float* p) { return __ldg(p); }
 
+// Programmatic dependent launch (griddepcontrol): a kernel launched with the programmatic-stream-serialization
+// attribute starts while its predecessor drains; nothing may touch global memory before pdl_wait().
+// Both are no-ops when the kernel was launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 }  // namespace ha

@@ -68,16 +68,18 @@ int post_grid_limit(int blocks_per_sm) {
   return override_grid > 0 ? override_grid : sm_count * blocks_per_sm;
 }
 
+constexpr int kPostNS = 2;   // cp.async stages per CTA (1: seven single-tile CTAs per SM; 2: four double-buffered CTAs)
+
 template <int K, bool SOA>
 int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {
-  using S = ha::KukaPostSmem<K>;
+  using S = ha::KukaPostSmem<K, kPostNS>;
   static int blocks_per_sm = 0;
   if (blocks_per_sm == 0) {
-    int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka_post_kernel<K, SOA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
+    int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka_post_kernel<K, SOA, kPostNS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
                             "cudaFuncSetAttribute(kuka_post_kernel)");
     if (rc) return rc;
     int nb = 0;
-    rc = ha::check_cuda(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ha::kuka_post_kernel<K, SOA>, ha::kPostThreads, sizeof(S)),
+    rc = ha::check_cuda(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ha::kuka_post_kernel<K, SOA, kPostNS>, ha::kPostThreads, sizeof(S)),
                         "cudaOccupancyMaxActiveBlocksPerMultiprocessor(kuka_post_kernel)");
     if (rc) return rc;
     blocks_per_sm = nb > 0 ? nb : 1;
@@ -86,8 +88,8 @@ int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStr
   const int n_tiles = (p->n_envs + ha::kTile - 1) / ha::kTile;
   const int limit = post_grid_limit(blocks_per_sm);
   const int grid = n_tiles < limit ? n_tiles : limit;
-  ha::kuka_post_kernel<K, SOA><<<grid, ha::kPostThreads, sizeof(S), st>>>(*p, *b, mode);
-  return ha::check_cuda(cudaGetLastError(), "kuka_post_kernel launch");
+  return ha::check_cuda(ha::launch(ha::kuka_post_kernel<K, SOA, kPostNS>, grid, ha::kPostThreads, sizeof(S), st, *p, *b, mode),
+                        "kuka_post_kernel launch");
 }
 
 }  // namespace
@@ -142,8 +144,8 @@ int ha_kuka_pre_step(const HaKukaParams* p, const HaKukaBuffers* b, const float*
   HA_REQUIRE(ha::aligned16(actions), "actions must be 16-byte aligned");
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
-  ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, actions, ext_rand, ha::kPreFull);
-  return ha::check_cuda(cudaGetLastError(), "kuka_pre_kernel launch");
+  return ha::check_cuda(ha::launch(ha::kuka_pre_kernel, grid, ha::kThreads, 0, (cudaStream_t)stream, *p, *b, actions, ext_rand, (int)ha::kPreFull),
+                        "kuka_pre_kernel launch");
 }
 
 int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float* ext_rand, ha_stream_t stream) {

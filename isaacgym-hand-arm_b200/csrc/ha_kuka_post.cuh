@@ -62,7 +62,6 @@ constexpr int kD1 = 23;              // single arm DOFs
 constexpr int kT1 = 4;               // fingertips
 constexpr int kTile = 32;            // envs per tile (lane = env)
 constexpr int kPostThreads = 128;    // 4 role warps
-constexpr int kPostStages = 2;       // cp.async stages
 constexpr int kNPart = HA_KUKA_N_PARTIAL_STATS;
 
 __host__ __device__ constexpr bool stat_is_max(int i) {
@@ -110,10 +109,10 @@ struct KukaPostStage {
   float dof[kTile * 2 * kD1];                      // contiguous image of dof_state (pos, vel pairs)
 };
 
-template <int K>
+template <int K, int NS>
 struct KukaPostSmem {
   static constexpr int kObs = kuka_layout(kD1, kT1, K).dim;
-  KukaPostStage<K> st[kPostStages];
+  KukaPostStage<K> st[NS];
   float obs[kTile * kObs];            // row-major tile, leaves as one contiguous run
   float xch[8 * kTile];               // [q][e]: cur[0..3], kp_max, sum|vel| arm, sum|vel| hand
 };
@@ -147,6 +146,7 @@ __device__ __forceinline__ void kuka_post_stats(const HaKukaBuffers& b, const Ku
             s_li = warp_sum_i(a.lifted);
   const float v_mx = warp_max(a.mx), v_mn = warp_max(a.neg_mn);
   long long* accum = reinterpret_cast<long long*>(b.stat_accum);
+  int is_last = 0;
   {
     long long val = 0;
     switch (lane) {
@@ -162,16 +162,15 @@ __device__ __forceinline__ void kuka_post_stats(const HaKukaBuffers& b, const Ku
       case HA_KUKA_STAT_SUM_LIFTED: val = s_li; break;
       default: break;
     }
+    // The accumulator atomics return their old values; consuming those values orders them (performed at L2) ahead of
+    // the ticket below without a membar that would also wait for this warp's ~35 per-env stores.
+    long long old = 0;
     if (lane < kNPart) {
-      if (stat_is_max(lane)) atomicMax(accum + lane, val);
-      else atomicAdd(reinterpret_cast<unsigned long long*>(accum + lane), (unsigned long long)val);
+      if (stat_is_max(lane)) old = atomicMax(accum + lane, val);
+      else old = (long long)atomicAdd(reinterpret_cast<unsigned long long*>(accum + lane), (unsigned long long)val);
     }
-  }
-  __syncwarp();
-  int is_last = 0;
-  if (lane == 0) {
-    __threadfence();                                  // this CTA's atomics are ordered before its ticket
-    is_last = (atomicAdd(b.tickets + 0, 1u) == gridDim.x - 1);
+    const unsigned dep = __any_sync(FULL, old == 0x7fffffffffffffffLL) ? 1u : 0u;   // never true; makes the ticket depend on every return
+    if (lane == 0) is_last = (atomicAdd(b.tickets + 0, 1u + dep) == gridDim.x - 1);
   }
   is_last = __shfl_sync(FULL, is_last, 0);
   if (!is_last) return;
@@ -346,21 +345,26 @@ __device__ __forceinline__ void kuka_post_load_env(const HaKukaParams& p, const 
   }
 }
 
-template <int K, bool SOA>
-__global__ void __launch_bounds__(kPostThreads, 4)
+template <int K, bool SOA, int NS>
+__global__ void __launch_bounds__(kPostThreads, NS == 1 ? 7 : 4)
 kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b, const int mode) {
-  using SM = KukaPostSmem<K>;
+  using SM = KukaPostSmem<K, NS>;
   using ST = KukaPostStage<K>;
   constexpr int OBS = SM::kObs, TIPW = ST::kTipW;
   constexpr KukaLayout L = kuka_layout(kD1, kT1, K);
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SM& sm = *reinterpret_cast<SM*>(smem_raw);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  // roles rotate with the CTA index: warp w of every CTA sits on scheduler w % 4, so a fixed role <-> warp
+  // mapping would pile all reward warps of an SM onto one scheduler
+  const int warp = ((tid >> 5) + blockIdx.x) & 3;
   const int n = p.n_envs;
   const int n_tiles = (n + kTile - 1) / kTile;
   const int stride = gridDim.x;
   int tile = blockIdx.x;
 
+  pdl_launch_dependents();      // the next kernel in the stream may start launching as our CTAs retire
+  pdl_wait();                   // everything below reads what the previous kernel wrote
   float keypoint_tol = 0.f, tobj_scale = 0.f, tobj_offset = 0.f;
   if (warp == 3) {
     keypoint_tol = b.dynamic->keypoint_success_tolerance;
@@ -373,19 +377,19 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   cp_async_commit();
 
   for (int it = 0; tile < n_tiles; ++it, tile += stride) {
-    ST& S = sm.st[it & 1];
+    ST& S = sm.st[NS == 2 ? (it & 1) : 0];
     const int env0 = tile * kTile;
     const int nvalid = min(kTile, n - env0);
     const bool valid = lane < nvalid;
     const int env = env0 + min(lane, nvalid - 1);       // idle lanes of a ragged tile re-read a valid env; stores are predicated
-    {   // next tile's copies go in flight before this tile is touched
-      const int next = tile + stride;
+    const int next = tile + stride;
+    if constexpr (NS == 2) {   // next tile's copies go in flight before this tile is touched
       if (next < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid);
       cp_async_commit();
     }
     KukaPostEnvState r;
     if (warp == 3) kuka_post_load_env<OBS, L.reward>(p, b, env, mode, r);
-    cp_async_wait<1>();
+    cp_async_wait<NS - 1>();
     __syncthreads();                                    // B1: this tile's inputs are in shared memory
 
     float* o = sm.obs + lane * OBS;
@@ -586,36 +590,45 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       }
     }
     __syncthreads();                                    // B3: the observation tile is complete
-    {
+    // on its last tile the state warp goes straight to the statistics (fence + atomics round trips) while the
+    // other three warps store the tile
+    const bool stats_now = (next >= n_tiles) && (mode == kPostFull);
+    if (stats_now && warp == 3) {
+      kuka_post_stats(b, acc, lane);
+    } else {
       // obs tile: clamp (:1174-1176 clamp_obs, vec_task.py:432 clip) and store as one contiguous run
       const float c = p.clamp_abs_obs;
       const bool do_clamp = c > 0.0f;
       float4* dst = reinterpret_cast<float4*>(b.obs_buf + (size_t)env0 * OBS);   // 16-byte aligned: env0 % 32 == 0
       const float4* src = reinterpret_cast<const float4*>(sm.obs);
       const int total = nvalid * OBS, nvec = total >> 2;
-      constexpr int kObsIters = (kTile * OBS / 4 + kPostThreads - 1) / kPostThreads;
-#pragma unroll
-      for (int i = 0; i < kObsIters; ++i) {
-        const int q = tid + kPostThreads * i;
-        if (q < nvec) {
-          float4 v = src[q];
-          if (do_clamp) {
-            v.x = fminf(fmaxf(v.x, -c), c); v.y = fminf(fmaxf(v.y, -c), c);
-            v.z = fminf(fmaxf(v.z, -c), c); v.w = fminf(fmaxf(v.w, -c), c);
-          }
-          dst[q] = v;
+      const int sid = warp * 32 + lane, nst = stats_now ? kPostThreads - 32 : kPostThreads;
+#pragma unroll 2
+      for (int q = sid; q < nvec; q += nst) {
+        float4 v = src[q];
+        if (do_clamp) {
+          v.x = fminf(fmaxf(v.x, -c), c); v.y = fminf(fmaxf(v.y, -c), c);
+          v.z = fminf(fmaxf(v.z, -c), c); v.w = fminf(fmaxf(v.w, -c), c);
         }
+        dst[q] = v;
       }
-      const int f = (nvec << 2) + tid;                  // ragged last tile: up to 3 trailing floats
+      const int f = (nvec << 2) + sid;                  // ragged last tile: up to 3 trailing floats
       if (f < total) {
         float v = sm.obs[f];
         if (do_clamp) v = fminf(fmaxf(v, -c), c);
         b.obs_buf[(size_t)env0 * OBS + f] = v;
       }
     }
+    if constexpr (NS == 1) {
+      if (next < n_tiles) {
+        __syncthreads();                                // every warp is done with the stage and the obs tile
+        kuka_post_issue<K, SOA>(p, b, sm.st[0], next * kTile, min(kTile, n - next * kTile), tid);
+      }
+      cp_async_commit();
+    }
   }
   cp_async_wait<0>();
-  if (warp == 3 && mode == kPostFull) kuka_post_stats(b, acc, lane);
+  if (blockIdx.x >= n_tiles && warp == 3 && mode == kPostFull) kuka_post_stats(b, acc, lane);   // CTA without a tile still owes its ticket
 }
 
 }  // namespace ha

@@ -223,6 +223,8 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   const bool valid = lane < nvalid;
   const bool reset_only = (mode == kPreResetOnly);   // VecTask.reset_idx / reset_done outside of a step
 
+  pdl_launch_dependents();
+  pdl_wait();
   // ---- issue the tile's vector loads first: they do not depend on the masks ----
   const size_t base = (size_t)env0 * D;
   const int total = nvalid * D, nvec = total >> 2;     // tile base is 16-byte aligned (env0 % 32 == 0)
