@@ -92,6 +92,8 @@ def load_reference() -> Dict[str, types.ModuleType]:
     _loaded["akr"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_reorientation")
     _loaded["aku"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_utils")
     _loaded["vt"] = importlib.import_module("isaacgymenvs.tasks.base.vec_task")
+    _loaded["sh"] = importlib.import_module("isaacgymenvs.tasks.shadow_hand")
+    _loaded["ah"] = importlib.import_module("isaacgymenvs.tasks.allegro_hand")
     return _loaded
 
 
@@ -207,7 +209,8 @@ def scripted_randoms(queue: List[torch.Tensor]):
         return pop(shape)
 
     saved = {}
-    for key in ("akb", "akr"):
+    patched = [k for k in ("akb", "akr", "sh", "ah", "ak2", "ak2g", "dx") if k in mods and hasattr(mods[k], "torch_rand_float")]
+    for key in patched:
         saved[key] = mods[key].torch_rand_float
         mods[key].torch_rand_float = fake_rand_float
     old_rand, old_randn = torch.rand, torch.randn
@@ -216,7 +219,7 @@ def scripted_randoms(queue: List[torch.Tensor]):
         yield q
     finally:
         torch.rand, torch.randn = old_rand, old_randn
-        for key in ("akb", "akr"):
+        for key in patched:
             mods[key].torch_rand_float = saved[key]
 
 
@@ -263,4 +266,100 @@ def harvest(env, st: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     if cum is not None:
         from .kuka_oracle import STEP_TERMS
         out["episode_cumulative"] = torch.stack([cum[k] for k in STEP_TERMS])
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# ShadowHand / AllegroHand (shadow_hand.py, allegro_hand.py)
+# ---------------------------------------------------------------------------------------------
+def make_reference_hand(st: Dict[str, torch.Tensor], c) -> object:
+    """A reference ``ShadowHand`` / ``AllegroHand`` instance aliasing the tensors of ``st`` (``oracle/hand_state.py`` layout)."""
+    mods = load_reference()
+    cls = mods["sh"].ShadowHand if c.kind == "shadow" else mods["ah"].AllegroHand
+    env = object.__new__(cls)
+    N, D = st["reset_buf"].shape[0], c.n_dofs
+    env.__dict__.update(
+        gym=FakeGym(), sim=None, device="cpu", rl_device="cpu", num_environments=N, viewer=None, debug_viz=False, headless=True,
+        num_actions=c.n_actions, num_shadow_hand_dofs=D, num_fingertips=c.n_tips, obs_type=c.obs_type, asymmetric_obs=c.asymmetric,
+        randomize=False, randomization_params={}, object_type="pen" if c.ignore_z_rot else "block", up_axis_idx=c.up_axis_idx,
+        dt=c.dt, use_relative_control=c.use_relative_control, shadow_hand_dof_speed_scale=c.dof_speed_scale,
+        act_moving_average=c.act_moving_average, force_scale=c.force_scale, force_decay_interval=c.force_decay_interval,
+        max_episode_length=c.max_episode_length, dist_reward_scale=c.dist_reward_scale, rot_reward_scale=c.rot_reward_scale,
+        rot_eps=c.rot_eps, action_penalty_scale=c.action_penalty_scale, success_tolerance=c.success_tolerance,
+        reach_goal_bonus=c.reach_goal_bonus, fall_dist=c.fall_dist, fall_penalty=c.fall_penalty,
+        max_consecutive_successes=c.max_consecutive_successes, print_success_stat=False, vel_obs_scale=c.vel_obs_scale,
+        force_torque_obs_scale=c.force_torque_obs_scale, reset_position_noise=c.reset_position_noise,
+        reset_dof_pos_noise=c.reset_dof_pos_noise, reset_dof_vel_noise=c.reset_dof_vel_noise, extras={}, total_successes=0, total_resets=0,
+    )
+    env.av_factor = torch.tensor(c.av_factor, dtype=torch.float32)
+    env.force_decay = torch.tensor(c.force_decay, dtype=torch.float32)
+    env.force_prob_range = torch.tensor(c.force_prob_range, dtype=torch.float32)
+    env.goal_displacement_tensor = torch.tensor(c.goal_displacement, dtype=torch.float32)
+    env.x_unit_tensor = torch.tensor([1.0, 0.0, 0.0]).repeat(N, 1)
+    env.y_unit_tensor = torch.tensor([0.0, 1.0, 0.0]).repeat(N, 1)
+    env.z_unit_tensor = torch.tensor([0.0, 0.0, 1.0]).repeat(N, 1)
+    env.actuated_dof_indices = torch.tensor(c.actuated, dtype=torch.long)
+    env.fingertip_handles = torch.tensor(list(c.tip_bodies), dtype=torch.long)
+    env.object_rb_handles = torch.tensor([c.object_body], dtype=torch.long)
+    env.object_rb_masses = torch.tensor([c.object_mass], dtype=torch.float32)
+    env.root_state_tensor = st["root_state"]
+    env.rigid_body_states = st["rigid_body_state"].view(N, -1, 13)
+    env.dof_state = st["dof_state"].view(-1, 2)
+    env.shadow_hand_dof_state = env.dof_state.view(N, -1, 2)[:, :D]
+    env.shadow_hand_dof_pos = env.shadow_hand_dof_state[..., 0]
+    env.shadow_hand_dof_vel = env.shadow_hand_dof_state[..., 1]
+    env.dof_force_tensor = st["dof_force"]
+    env.vec_sensor_tensor = st["sensors"]
+    env.shadow_hand_dof_lower_limits = st["dof_lower"]
+    env.shadow_hand_dof_upper_limits = st["dof_upper"]
+    env.shadow_hand_default_dof_pos = st["dof_default"]
+    env.shadow_hand_dof_default_pos = st["dof_default"]
+    env.shadow_hand_dof_default_vel = torch.zeros(D)
+    env.num_bodies = env.rigid_body_states.shape[1]
+    for name in ("hand_indices", "object_indices", "goal_object_indices", "goal_states", "goal_init_state", "object_init_state", "obs_buf",
+                 "states_buf", "rew_buf", "reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf", "successes",
+                 "consecutive_successes", "prev_targets", "cur_targets", "rb_forces", "random_force_prob"):
+        setattr(env, name, st[name])
+    env.actions = st["actions"]
+    return env
+
+
+def hand_random_queue(st: Dict[str, torch.Tensor], c, rnd: torch.Tensor) -> List[torch.Tensor]:
+    """Order of draws of one hand ``pre_physics_step`` for table ``rnd`` (``HA_HAND_RND_*``)."""
+    from . import hand_oracle as ho
+    D = c.n_dofs
+    goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
+    ids = st["reset_buf"].nonzero(as_tuple=False).squeeze(-1)
+    q: List[torch.Tensor] = []
+    if len(goal_ids) > 0:
+        q.append(rnd[goal_ids, ho.RND_GOAL:ho.RND_GOAL + 4])
+    prob = st["random_force_prob"].clone()
+    if len(ids) > 0:
+        q += [rnd[ids, ho.RND_RESET:ho.RND_RESET + 2 * D + 5], rnd[ids, ho.RND_RESET_GOAL:ho.RND_RESET_GOAL + 4], rnd[ids, ho.RND_FORCE_PROB]]
+        pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
+        prob[ids] = torch.exp((torch.log(pr[0]) - torch.log(pr[1])) * rnd[ids, ho.RND_FORCE_PROB] + torch.log(pr[1]))
+    if c.force_scale > 0.0:
+        q.append(rnd[:, ho.RND_FORCE_TEST])
+        hit = (rnd[:, ho.RND_FORCE_TEST] < prob).nonzero(as_tuple=False)
+        q.append(rnd[hit.squeeze(-1), ho.RND_FORCE_NORMAL:ho.RND_FORCE_NORMAL + 3].unsqueeze(1))
+    return q
+
+
+def reference_hand_step(env, c, actions: torch.Tensor, rnd: torch.Tensor, st: Dict[str, torch.Tensor]) -> None:
+    with scripted_randoms(hand_random_queue(st, c, rnd)) as q:
+        env.pre_physics_step(actions)
+        assert len(q) == 0, f"{len(q)} scripted random tensors were not consumed"
+    env.post_physics_step()
+    env.timeout_buf = (env.progress_buf >= env.max_episode_length - 1) & (env.reset_buf != 0)
+
+
+def harvest_hand(env, st: Dict[str, torch.Tensor], c) -> Dict[str, torch.Tensor]:
+    out = dict(st)
+    for name in ("progress_buf", "successes", "consecutive_successes", "timeout_buf", "reset_buf", "reset_goal_buf", "randomize_buf",
+                 "random_force_prob", "obs_buf", "states_buf", "rew_buf", "rb_forces"):
+        out[name] = getattr(env, name)
+    out["actions"] = env.actions
+    out["obs_out"] = torch.clamp(env.obs_buf, -c.clip_obs, c.clip_obs)
+    if c.asymmetric:
+        out["states_out"] = torch.clamp(env.states_buf, -c.clip_obs, c.clip_obs)
     return out
