@@ -282,6 +282,147 @@ int ha_kuka_post_step(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t
  * obs_buf from the current state without touching reward / reset state. */
 int ha_kuka_observe(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream);
 
+
+/* ------------------------------------------------------------------------ */
+/* In-hand reorientation family: ShadowHand (shadow_hand.py) and AllegroHand   */
+/* (allegro_hand.py).  ha_hand_pre_step replaces pre_physics_step              */
+/* (shadow_hand.py:670-708 / allegro_hand.py:586-625) incl. reset_idx          */
+/* (:604-668 / :524-584) and reset_target_pose (:586-602 / :506-522);          */
+/* ha_hand_post_step replaces post_physics_step (:710-715 / :627-632) =        */
+/* compute_observations (:437-584 / :406-504, all observation layouts and the  */
+/* asymmetric states_buf) + compute_hand_reward (:746-800 / :663-719) and the  */
+/* VecTask.step tail (vec_task.py:424-432).                                    */
+/* ------------------------------------------------------------------------ */
+#define HA_HAND_MAX_DOFS 24
+#define HA_HAND_MAX_TIPS 5
+#define HA_HAND_MAX_OBS 224
+
+/* observationType (shadow_hand.py:111-116, allegro_hand.py:108-112) */
+enum { HA_HAND_OBS_OPENAI = 0, HA_HAND_OBS_FULL_NO_VEL = 1, HA_HAND_OBS_FULL = 2, HA_HAND_OBS_FULL_STATE = 3 };
+
+/* one env's row of externally supplied raw draws (parity mode): U(0,1) everywhere, N(0,1) in the force-normal slots */
+enum {
+  HA_HAND_RND_GOAL = 0,          /* 4: reset_target_pose of a goal-only reset                 */
+  HA_HAND_RND_RESET_GOAL = 4,    /* 4: reset_target_pose inside reset_idx                      */
+  HA_HAND_RND_FORCE_PROB = 8,    /* 1                                                          */
+  HA_HAND_RND_FORCE_TEST = 9,    /* 1                                                          */
+  HA_HAND_RND_FORCE_NORMAL = 10, /* 3: N(0,1)                                                  */
+  HA_HAND_RND_RESET = 13         /* 2*n_dofs + 5: rand_floats of reset_idx                     */
+};
+#define HA_HAND_RND_STRIDE(n_dofs) (18 + 2 * (n_dofs))
+
+typedef struct HaHandParams {
+  int32_t abi_version;
+  int32_t n_envs;
+  int32_t is_shadow;        /* 1: ShadowHand (fingertip states + force sensors observed), 0: AllegroHand */
+  int32_t n_dofs;           /* 24 / 16 */
+  int32_t dofs_per_env;     /* row width of dof_state / targets (>= n_dofs) */
+  int32_t n_actions;        /* 20 / 16 */
+  int32_t n_bodies;
+  int32_t n_tips;           /* 5 / 0 */
+  int32_t obs_type;         /* HA_HAND_OBS_* */
+  int32_t obs_dim;          /* see ha_hand_obs_dim() */
+  int32_t states_dim;       /* 0, or the full_state width when asymmetric_observations */
+  int32_t object_body;
+  int32_t max_episode_length;
+  int32_t max_consecutive_successes;
+  int32_t use_relative_control;
+  int32_t ignore_z_rot;     /* objectType == "pen" */
+  int32_t use_fast_rng;
+  int32_t force_enabled;
+  int32_t root_regular;     /* actor rows follow env * actors_per_env + slot */
+  int32_t actors_per_env, object_slot, goal_slot;
+  int32_t up_axis_idx;
+  int32_t actuated_dof[HA_HAND_MAX_DOFS];   /* actuated_dof_indices, n_actions entries */
+  int32_t tip_body[HA_HAND_MAX_TIPS];
+  float dof_lower[HA_HAND_MAX_DOFS], dof_upper[HA_HAND_MAX_DOFS], dof_default[HA_HAND_MAX_DOFS];
+  float dof_range_rcp[HA_HAND_MAX_DOFS];    /* filled by ha_hand_fill_derived() */
+  float clip_obs;           /* clipObservations (vec_task.py:432); <= 0: none */
+  float vel_obs_scale, force_torque_obs_scale;
+  /* reward (compute_hand_reward) */
+  float dist_reward_scale, rot_reward_scale, rot_eps, action_penalty_scale, success_tolerance, reach_goal_bonus;
+  float fall_dist, fall_penalty, av_factor;
+  /* pre-physics */
+  float rel_action_gain;    /* dofSpeedScale * dt */
+  float act_moving_average, one_minus_act_moving_average;
+  float force_decay_pow, force_gain[2], force_log_c0, force_log_c1;
+  /* reset */
+  float reset_position_noise, reset_dof_pos_noise, reset_dof_vel_noise;
+  float goal_displacement[3];
+} HaHandParams;
+
+typedef struct HaHandDynamic {
+  uint64_t rng_seed;
+  uint64_t rng_step;
+} HaHandDynamic;
+
+typedef struct HaHandBuffers {
+  /* simulator-owned (Isaac Gym layout) */
+  float* root_state;              /* [n_envs*actors_per_env, 13] */
+  const float* rigid_body_state;  /* [n_envs, n_bodies, 13] */
+  float* dof_state;               /* [n_envs, dofs_per_env, 2] */
+  const float* dof_force;         /* [n_envs, n_dofs] (full_state / asymmetric; nullable otherwise) */
+  const float* force_sensors;     /* [n_envs, 6*n_tips] (ShadowHand full_state / asymmetric; nullable otherwise) */
+  const int32_t* object_actor;    /* [n_envs] */
+  const int32_t* goal_actor;      /* [n_envs] */
+  const int32_t* hand_actor;      /* [n_envs] */
+  /* task constants */
+  const float* object_init_state; /* [n_envs, 13] */
+  const float* goal_init_state;   /* [n_envs, 13] */
+  /* task state */
+  float* goal_states;             /* [n_envs, 13] */
+  float* obs_buf;                 /* [n_envs, obs_dim], clipped to +-clip_obs */
+  float* states_buf;              /* [n_envs, states_dim] (nullable iff states_dim == 0) */
+  float* rew_buf;
+  int64_t* reset_buf;
+  int64_t* reset_goal_buf;
+  int64_t* progress_buf;
+  int64_t* randomize_buf;         /* nullable */
+  uint8_t* timeout_buf;
+  float* successes;
+  float* consecutive_successes;   /* [1] */
+  float* prev_targets;            /* [n_envs, dofs_per_env] */
+  float* cur_targets;
+  float* actions;                 /* [n_envs, n_actions] task-owned copy */
+  float* rb_forces;               /* [n_envs, n_bodies, 3] */
+  float* random_force_prob;       /* [n_envs] */
+  /* outputs for the simulator's *_indexed setters */
+  int32_t* root_reset_indices;    /* [2*n_envs] */
+  int32_t* hand_reset_indices;    /* [n_envs] */
+  int32_t* reset_counts;          /* [4]: n_root, n_hand, n_reset_envs, n_goal_resets */
+  /* reductions */
+  float* stats;                   /* [HA_STATS_LEN], HA_HAND_STAT_* */
+  int64_t* stat_accum;            /* [HA_STATS_LEN], zero-initialised once */
+  uint32_t* tickets;              /* [8], zero-initialised once */
+  HaHandDynamic* dynamic;
+} HaHandBuffers;
+
+enum {
+  HA_HAND_STAT_N = 0,
+  HA_HAND_STAT_SUM_REWARD,
+  HA_HAND_STAT_SUM_RESETS,               /* num_resets of compute_hand_reward */
+  HA_HAND_STAT_SUM_FINISHED_SUCCESSES,   /* sum(successes * resets) */
+  HA_HAND_STAT_SUM_GOAL_RESETS,
+  HA_HAND_STAT_SUM_SUCCESSES,
+  HA_HAND_STAT_SUM_TIMEOUTS,
+  HA_HAND_N_PARTIAL_STATS,
+  HA_HAND_STAT_MEAN_REWARD = HA_HAND_N_PARTIAL_STATS,
+  HA_HAND_STAT_CONSECUTIVE_SUCCESSES,
+  HA_HAND_N_STATS
+};
+
+size_t ha_sizeof_hand_params(void);
+size_t ha_sizeof_hand_buffers(void);
+int ha_hand_obs_dim(int is_shadow, int obs_type);
+void ha_hand_fill_derived(HaHandParams* p);
+size_t ha_hand_post_bytes_per_env_step(const HaHandParams* p);
+size_t ha_hand_pre_bytes_per_env_step(const HaHandParams* p);
+size_t ha_hand_bytes_per_env_step(const HaHandParams* p);
+int ha_hand_pre_step(const HaHandParams* p, const HaHandBuffers* b, const float* actions, const float* ext_rand, ha_stream_t stream);
+int ha_hand_reset_idx(const HaHandParams* p, const HaHandBuffers* b, const float* ext_rand, ha_stream_t stream);
+int ha_hand_post_step(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream);
+int ha_hand_observe(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -107,6 +107,9 @@ CONSTS, STRUCTS = _parse_header(HEADER_PATH)
 HaKukaParams = STRUCTS["HaKukaParams"]
 HaKukaBuffers = STRUCTS["HaKukaBuffers"]
 HaKukaDynamic = STRUCTS["HaKukaDynamic"]
+HaHandParams = STRUCTS["HaHandParams"]
+HaHandBuffers = STRUCTS["HaHandBuffers"]
+HaHandDynamic = STRUCTS["HaHandDynamic"]
 
 _lib = None
 
@@ -147,6 +150,22 @@ def load():
     lib.ha_kuka_fill_derived.argtypes = [ctypes.c_void_p]
     lib.ha_kuka_fill_derived.restype = None
     for fn in ("ha_kuka_bytes_per_env_step", "ha_kuka_post_bytes_per_env_step", "ha_kuka_pre_bytes_per_env_step"):
+        getattr(lib, fn).argtypes = [ctypes.c_void_p]
+    # in-hand family
+    for fn in ("ha_sizeof_hand_params", "ha_sizeof_hand_buffers", "ha_hand_bytes_per_env_step", "ha_hand_post_bytes_per_env_step",
+               "ha_hand_pre_bytes_per_env_step"):
+        getattr(lib, fn).restype = ctypes.c_size_t
+    for cls, fn in ((HaHandParams, lib.ha_sizeof_hand_params), (HaHandBuffers, lib.ha_sizeof_hand_buffers)):
+        if ctypes.sizeof(cls) != fn():
+            raise HandArmLibraryError(f"struct {cls.__name__}: ctypes size {ctypes.sizeof(cls)} != C size {fn()}")
+    lib.ha_hand_pre_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_hand_reset_idx.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_hand_post_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_hand_observe.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_hand_obs_dim.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.ha_hand_fill_derived.argtypes = [ctypes.c_void_p]
+    lib.ha_hand_fill_derived.restype = None
+    for fn in ("ha_hand_bytes_per_env_step", "ha_hand_post_bytes_per_env_step", "ha_hand_pre_bytes_per_env_step"):
         getattr(lib, fn).argtypes = [ctypes.c_void_p]
     _lib = lib
     return lib

@@ -143,4 +143,47 @@ __device__ __forceinline__ float ldg(const float* p) { return __ldg(p); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ---- cp.async (LDGSTS) ----
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+
+__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#pragma unroll
+  for (int ofs = 16; ofs > 0; ofs >>= 1) v += __shfl_xor_sync(0xffffffffu, v, ofs);
+  return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+  for (int ofs = 16; ofs > 0; ofs >>= 1) v += __shfl_xor_sync(0xffffffffu, v, ofs);
+  return v;
+}
+
+
+// a / b with r = RN(1 / b) precomputed on the host: one Newton-style residual step (Markstein) gives the
+// correctly rounded quotient for all but a vanishing fraction of operands (<= 1 ulp otherwise), in 3 instructions
+__device__ __forceinline__ float div_by_const(float a, float b, float r) {
+  const float q = a * r;
+  const float e = fmaf(-b, q, a);
+  return fmaf(e, r, q);
+}
+
+
+// order-preserving float <-> int64 key (for atomicMax on signed integers)
+__device__ __forceinline__ long long float_key(float f) {
+  const int b = __float_as_int(f);
+  return (long long)(b >= 0 ? b : (b ^ 0x7fffffff));
+}
+__device__ __forceinline__ float key_float(long long k) {
+  const int b = (int)k;
+  return __int_as_float(b >= 0 ? b : (b ^ 0x7fffffff));
+}
+
 }  // namespace ha

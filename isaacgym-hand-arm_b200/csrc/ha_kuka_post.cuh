@@ -72,27 +72,7 @@ __host__ __device__ constexpr float stat_scale(int i) {
   return (i == HA_KUKA_STAT_SUM_REWARD) ? 65536.0f
          : (i == HA_KUKA_STAT_SUM_TRUE_OBJECTIVE || i == HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES) ? 1048576.0f : 1.0f;
 }
-// order-preserving float <-> int64 key (for atomicMax on signed integers)
-__device__ __forceinline__ long long float_key(float f) {
-  const int b = __float_as_int(f);
-  return (long long)(b >= 0 ? b : (b ^ 0x7fffffff));
-}
-__device__ __forceinline__ float key_float(long long k) {
-  const int b = (int)k;
-  return __int_as_float(b >= 0 ? b : (b ^ 0x7fffffff));
-}
 constexpr long long kStatMaxInit = -0x7fffffffLL - 1;   // below every float key
-
-// ---- cp.async (LDGSTS) ----
-__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // One tile's inputs as they land in shared memory.  Row strides are odd (13, 29, 7) so lane = env reads are
 // conflict-free; the contiguous images (kp, dof) are read with 128 / 64-bit loads, which are conflict-free at
@@ -125,17 +105,6 @@ struct KukaPostAcc {
   float mx = -3.0e38f, neg_mn = -3.0e38f;
   int n = 0, resets = 0, success = 0, timeout = 0, lifted = 0;
 };
-
-__device__ __forceinline__ long long warp_sum_ll(long long v) {
-#pragma unroll
-  for (int ofs = 16; ofs > 0; ofs >>= 1) v += __shfl_xor_sync(0xffffffffu, v, ofs);
-  return v;
-}
-__device__ __forceinline__ int warp_sum_i(int v) {
-#pragma unroll
-  for (int ofs = 16; ofs > 0; ofs >>= 1) v += __shfl_xor_sync(0xffffffffu, v, ofs);
-  return v;
-}
 
 // Episode statistics of one CTA -> global fixed-point accumulators; the last CTA of the grid converts them
 // to floats.  Called once per CTA by warp 3 after its last tile.
@@ -200,14 +169,6 @@ __device__ __forceinline__ void kuka_post_stats(const HaKukaBuffers& b, const Ku
     // fast-mode RNG: one counter tick per step
     b.dynamic->rng_step = b.dynamic->rng_step + 1;
   }
-}
-
-// a / b with r = RN(1 / b) precomputed on the host: one Newton-style residual step (Markstein) gives the
-// correctly rounded quotient for all but a vanishing fraction of operands (<= 1 ulp otherwise), in 3 instructions
-__device__ __forceinline__ float div_by_const(float a, float b, float r) {
-  const float q = a * r;
-  const float e = fmaf(-b, q, a);
-  return fmaf(e, r, q);
 }
 
 // Issue the cp.async copies of one tile (all 128 threads).  Idle envs of a ragged last tile re-read the last valid env.

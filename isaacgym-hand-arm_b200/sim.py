@@ -44,6 +44,23 @@ KUKA_LAYOUT = ActorLayout(actors_per_env=4, bodies_per_env=27, dofs_per_env=23, 
                           palm_body=(7,), tip_body=(11, 15, 19, 23), object_body=24)
 
 
+# ShadowHand (mjcf/open_ai_assets/hand/shadow_hand.xml): 26 hand bodies + object + goal, 24 joints, fingertips = the five
+# *distal bodies; AllegroHand (allegro_touch_sensor.urdf): 17 hand bodies + object + goal, 16 joints.  Actors: hand, object, goal.
+SHADOW_HAND_LAYOUT = ActorLayout(actors_per_env=3, bodies_per_env=28, dofs_per_env=24, hand_actor=(0,), object_actor=1, goal_actor=2,
+                                 palm_body=(), tip_body=(7, 11, 15, 20, 25), object_body=26)
+ALLEGRO_HAND_LAYOUT = ActorLayout(actors_per_env=3, bodies_per_env=19, dofs_per_env=16, hand_actor=(0,), object_actor=1, goal_actor=2,
+                                  palm_body=(), tip_body=(), object_body=17)
+# joint limits of assets/mjcf/open_ai_assets/hand/robot.xml (WRJ1 WRJ0 FFJ3..0 MFJ3..0 RFJ3..0 LFJ4..0 THJ4..0)
+SHADOW_HAND_LOWER = [-0.489, -0.698, -0.349, 0.0, 0.0, 0.0, -0.349, 0.0, 0.0, 0.0, -0.349, 0.0, 0.0, 0.0, 0.0, -0.349, 0.0, 0.0, 0.0,
+                     -1.047, 0.0, -0.209, -0.524, -1.571]
+SHADOW_HAND_UPPER = [0.14, 0.489, 0.349, 1.571, 1.571, 1.571, 0.349, 1.571, 1.571, 1.571, 0.349, 1.571, 1.571, 1.571, 0.785, 0.349,
+                     1.571, 1.571, 1.571, 1.047, 1.222, 0.209, 0.524, 0.0]
+ALLEGRO_HAND_LOWER = KUKA_ALLEGRO_LOWER[7:]
+ALLEGRO_HAND_UPPER = KUKA_ALLEGRO_UPPER[7:]
+# actuated joints of shared.xml (all but FFJ0 / MFJ0 / RFJ0 / LFJ0, which are tendon-coupled)
+SHADOW_HAND_ACTUATED = [0, 1, 2, 3, 4, 6, 7, 8, 10, 11, 12, 14, 15, 16, 17, 19, 20, 21, 22, 23]
+
+
 def cuboid_scales(small: bool = True, big: bool = True, sticks: bool = True) -> List[List[float]]:
     """Object scale table the reference derives from its generated cuboid assets.
 
@@ -115,6 +132,9 @@ class SyntheticSim:
             self.root_snap = [torch.zeros(N * L.actors_per_env, 13, device=self.device) for _ in range(self.n_snapshots)]
             self.rb_snap = [torch.zeros(N * L.bodies_per_env, 13, device=self.device) for _ in range(self.n_snapshots)]
         self.dof_snap = [torch.zeros(N * L.dofs_per_env, 2, device=self.device) for _ in range(self.n_snapshots)]
+        # acquire_dof_force_tensor / acquire_force_sensor_tensor (hand tasks, full_state observations)
+        self.dof_force_snap = [torch.zeros(N, L.dofs_per_env, device=self.device) for _ in range(self.n_snapshots)]
+        self.sensor_snap = [torch.zeros(N, 6 * max(len(L.tip_body), 1), device=self.device) for _ in range(self.n_snapshots)]
 
     # ---- the acquire_* surface -----------------------------------------------------------
     @property
@@ -128,6 +148,14 @@ class SyntheticSim:
     @property
     def dof_state(self) -> torch.Tensor:
         return self.dof_snap[self.cursor]
+
+    @property
+    def dof_force(self) -> torch.Tensor:
+        return self.dof_force_snap[self.cursor]
+
+    @property
+    def force_sensors(self) -> torch.Tensor:
+        return self.sensor_snap[self.cursor]
 
     # layout-independent [N, rows, 13] views (strided in the "soa" layout; writes go through)
     def root_rows(self, snapshot: Optional[int] = None) -> torch.Tensor:
@@ -188,3 +216,39 @@ class SyntheticSim:
             self.root_rows(s).copy_(root)
             self.body_rows(s).copy_(rb)
             self.dof_snap[s].copy_(dof.view(-1, 2))
+
+    def fill_hand(self, object_init: Sequence[float], goal_states: Optional[torch.Tensor], lower: Sequence[float],
+                  upper: Sequence[float]) -> None:
+        """Seeded in-hand state for every snapshot (ShadowHand / AllegroHand): the object hovers around its start pose,
+        ~3 % of the objects have fallen (goal_dist >= fallDistance), ~2 % sit at the goal orientation."""
+        N, L = self.num_envs, self.layout
+        lo, hi = torch.tensor(lower, dtype=torch.float32), torch.tensor(upper, dtype=torch.float32)
+        D = L.dofs_per_env
+        for s in range(self.n_snapshots):
+            gen = torch.Generator().manual_seed(self.seed * 1000003 + s)
+            root = torch.zeros(N, L.actors_per_env, 13)
+            root[..., 0:3] = torch.tensor(list(object_init), dtype=torch.float32) + 0.03 * torch.randn(N, L.actors_per_env, 3, generator=gen)
+            root[..., 3:7] = _rand_unit_quat(gen, (N, L.actors_per_env))
+            root[..., 7:10] = 0.5 * torch.randn(N, L.actors_per_env, 3, generator=gen)
+            root[..., 10:13] = 2.0 * torch.randn(N, L.actors_per_env, 3, generator=gen)
+            fallen = torch.rand(N, generator=gen) < 0.03
+            root[fallen, L.object_actor, 2] -= 0.4
+            if goal_states is not None:
+                hit = torch.rand(N, generator=gen) < 0.02
+                g = goal_states.detach().cpu()
+                q = g[hit, 3:7] + 1e-3 * torch.randn(int(hit.sum()), 4, generator=gen)
+                root[hit, L.object_actor, 3:7] = q / q.norm(dim=-1, keepdim=True)
+            rb = torch.zeros(N, L.bodies_per_env, 13)
+            rb[..., 0:3] = root[:, L.object_actor:L.object_actor + 1, 0:3] + 0.08 * torch.randn(N, L.bodies_per_env, 3, generator=gen)
+            rb[..., 3:7] = _rand_unit_quat(gen, (N, L.bodies_per_env))
+            rb[..., 7:10] = 0.5 * torch.randn(N, L.bodies_per_env, 3, generator=gen)
+            rb[..., 10:13] = 2.0 * torch.randn(N, L.bodies_per_env, 3, generator=gen)
+            rb[:, L.object_body] = root[:, L.object_actor]
+            dof = torch.zeros(N, D, 2)
+            dof[..., 0] = lo + (hi - lo) * torch.rand(N, D, generator=gen)
+            dof[..., 1] = 3.0 * torch.randn(N, D, generator=gen)
+            self.root_rows(s).copy_(root)
+            self.body_rows(s).copy_(rb)
+            self.dof_snap[s].copy_(dof.view(-1, 2))
+            self.dof_force_snap[s].copy_(0.3 * torch.randn(N, D, generator=gen))
+            self.sensor_snap[s].copy_(0.2 * torch.randn(self.sensor_snap[s].shape, generator=gen))

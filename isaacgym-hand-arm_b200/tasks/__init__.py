@@ -1,5 +1,6 @@
 """Task registry (subset of ``isaacgymenvs/tasks/__init__.py:66-123`` that lies on the hot path)."""
 from .allegro_kuka import AllegroKukaBase, AllegroKukaReorientation
+from .hand import AllegroHand, ShadowHand
 
 
 def resolve_allegro_kuka(cfg, *args, **kwargs):
@@ -11,4 +12,5 @@ def resolve_allegro_kuka(cfg, *args, **kwargs):
     return table[subtask](cfg, *args, **kwargs)
 
 
-isaacgym_task_map = {"AllegroKuka": resolve_allegro_kuka, "AllegroKukaLSTM": resolve_allegro_kuka}
+isaacgym_task_map = {"AllegroKuka": resolve_allegro_kuka, "AllegroKukaLSTM": resolve_allegro_kuka, "ShadowHand": ShadowHand,
+                     "AllegroHand": AllegroHand}

@@ -321,6 +321,7 @@ def make_reference_hand(st: Dict[str, torch.Tensor], c) -> object:
                  "consecutive_successes", "prev_targets", "cur_targets", "rb_forces", "random_force_prob"):
         setattr(env, name, st[name])
     env.actions = st["actions"]
+    env.timeout_buf = st["timeout_buf"]
     return env
 
 

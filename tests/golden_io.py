@@ -36,3 +36,27 @@ def load_fixture(name: str):
             d[phase] = {k[len(pre):]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith(pre)}
         steps.append(d)
     return c, st, steps
+
+
+def hand_fixture_names() -> List[str]:
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "hand_*.npz")))
+
+
+def load_hand_fixture(name: str):
+    """-> (HandConsts, input state dict, [per-step dict(actions, rnd, pre={...}, post={...})])"""
+    import json
+    from oracle import hand_oracle as ho
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    d = json.loads(str(z["meta/consts_json"]))
+    for k in ("actuated", "tip_bodies", "force_prob_range", "goal_displacement"):
+        d[k] = tuple(d[k])
+    c = ho.HandConsts(**d)
+    st = {k.split("/", 1)[1]: torch.from_numpy(z[k].copy()) for k in z.files if k.startswith("in/")}
+    steps = []
+    for i in range(int(z["meta/steps"])):
+        s: Dict[str, object] = {"actions": torch.from_numpy(z[f"s{i}/actions"].copy()), "rnd": torch.from_numpy(z[f"s{i}/rnd"].copy())}
+        for phase in ("pre", "post"):
+            pre = f"s{i}/{phase}/"
+            s[phase] = {k[len(pre):]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith(pre)}
+        steps.append(s)
+    return c, st, steps
