@@ -92,6 +92,8 @@ def load_reference() -> Dict[str, types.ModuleType]:
     _loaded["akr"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_reorientation")
     _loaded["aku"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_utils")
     _loaded["vt"] = importlib.import_module("isaacgymenvs.tasks.base.vec_task")
+    _loaded["ak2"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms")
+    _loaded["ak2g"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms_regrasping")
     _loaded["sh"] = importlib.import_module("isaacgymenvs.tasks.shadow_hand")
     _loaded["ah"] = importlib.import_module("isaacgymenvs.tasks.allegro_hand")
     return _loaded
@@ -363,4 +365,116 @@ def harvest_hand(env, st: Dict[str, torch.Tensor], c) -> Dict[str, torch.Tensor]
     out["obs_out"] = torch.clamp(env.obs_buf, -c.clip_obs, c.clip_obs)
     if c.asymmetric:
         out["states_out"] = torch.clamp(env.states_buf, -c.clip_obs, c.clip_obs)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# AllegroKukaTwoArmsRegrasping (allegro_kuka_two_arms.py, allegro_kuka_two_arms_regrasping.py)
+# ---------------------------------------------------------------------------------------------
+def make_reference_kuka2(st: Dict[str, torch.Tensor], c) -> object:
+    """A reference ``AllegroKukaTwoArmsRegrasping`` instance aliasing the tensors of ``st`` (``oracle/kuka2_oracle.make_state``)."""
+    from .kuka2_oracle import EPISODE_TERMS
+    mods = load_reference()
+    env = object.__new__(mods["ak2g"].AllegroKukaTwoArmsRegrasping)
+    N = st["reset_buf"].shape[0]
+    K = st["object_keypoint_offsets"].shape[1]
+    env.__dict__.update(
+        gym=FakeGym(), sim=None, device="cpu", rl_device="cpu", num_environments=N, viewer=None, debug_viz=False, headless=True,
+        num_arms=c.n_arms, num_arm_dofs=c.n_arm_dofs, num_hand_dofs=16, num_hand_arm_dofs=23, num_finger_dofs=4, num_fingertips=4,
+        num_allegro_fingertips=4, num_keypoints=K, obs_type="full_state", num_observations=st["obs_buf"].shape[1],
+        privileged_actions=False, use_relative_control=False, randomize=False, should_load_initial_states=False, save_states=False,
+        eval_stats=False, dt=c.dt, act_moving_average=c.act_moving_average, force_scale=c.force_scale,
+        force_decay_interval=c.force_decay_interval, clamp_abs_observations=c.clamp_abs_observations,
+        max_episode_length=c.max_episode_length, max_consecutive_successes=c.max_consecutive_successes, success_steps=c.success_steps,
+        success_tolerance=c.success_tolerance, initial_tolerance=c.initial_tolerance, target_tolerance=c.target_tolerance,
+        tolerance_curriculum_increment=0.9, tolerance_curriculum_interval=10 ** 9, keypoint_scale=c.keypoint_scale,
+        lifting_bonus_threshold=c.lifting_bonus_threshold, lifting_bonus=c.lifting_bonus, lifting_rew_scale=c.lifting_rew_scale,
+        keypoint_rew_scale=c.keypoint_rew_scale, distance_delta_rew_scale=c.distance_delta_rew_scale, reach_goal_bonus=c.reach_goal_bonus,
+        reset_position_noise_x=c.reset_position_noise[0], reset_position_noise_y=c.reset_position_noise[1],
+        reset_position_noise_z=c.reset_position_noise[2], reset_dof_vel_noise=c.reset_dof_vel_noise, frame_since_restart=0,
+        last_curriculum_update=0, control_freq_inv=1, extras={}, total_successes=0, total_resets=0,
+        set_actor_root_state_object_indices=[], randomization_params={},
+    )
+    env.full_state_size = st["obs_buf"].shape[1]
+    env.force_decay = torch.tensor(c.force_decay, dtype=torch.float32)
+    env.force_prob_range = torch.tensor(c.force_prob_range, dtype=torch.float32)
+    env.palm_center_offset = torch.tensor(c.palm_offset, dtype=torch.float32).repeat(N, 1)
+    env.palm_center_pos = torch.zeros(N, c.n_arms, 3)
+    env.fingertip_offsets = torch.tensor(np.asarray(c.tip_offsets, dtype=np.float32)).repeat(N, 1, 1)
+    env.target_volume_origin = torch.tensor(c.target_volume_origin, dtype=torch.float32)
+    env.target_volume_extent = torch.tensor(c.target_volume_extent, dtype=torch.float32)
+    env.allegro_palm_handles = list(c.palm_bodies)
+    env.allegro_fingertip_handles = torch.tensor(list(c.tip_bodies), dtype=torch.long)
+    env.object_rb_handles = torch.tensor([c.object_body], dtype=torch.long)
+    env.object_rb_masses = torch.tensor([c.object_mass], dtype=torch.float32)
+    env.root_state_tensor = st["root_state"]
+    env.rigid_body_states = st["rigid_body_state"].view(N, -1, 13)
+    env.dof_state = st["dof_state"].view(-1, 2)
+    env.arm_hand_dof_state = env.dof_state.view(N, -1, 2)[:, : c.n_dofs]
+    env.arm_hand_dof_pos = env.arm_hand_dof_state[..., 0]
+    env.arm_hand_dof_vel = env.arm_hand_dof_state[..., 1]
+    env.num_bodies = env.rigid_body_states.shape[1]
+    for name in ("arm_indices", "object_indices", "goal_object_indices", "goal_states", "object_init_state", "object_keypoint_offsets",
+                 "object_scales", "obs_buf", "rew_buf", "reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf", "successes",
+                 "prev_episode_successes", "true_objective", "prev_episode_true_objective", "near_goal_steps", "lifted_object",
+                 "closest_keypoint_max_dist", "closest_fingertip_dist", "prev_targets", "cur_targets", "rb_forces", "random_force_prob",
+                 "pos_noise_coeff"):
+        setattr(env, name, st[name])
+    env.arm_hand_dof_lower_limits = st["dof_lower"]
+    env.arm_hand_dof_upper_limits = st["dof_upper"]
+    env.hand_arm_default_dof_pos = st["dof_default"]
+    env.obj_keypoint_pos = torch.zeros(N, K, 3)
+    env.goal_keypoint_pos = torch.zeros(N, K, 3)
+    env.rewards_episode = {k: st["rewards_episode"][i] for i, k in enumerate(EPISODE_TERMS)}
+    env.timeout_buf = torch.zeros(N, dtype=torch.long)
+    return env
+
+
+def kuka2_random_queue(st: Dict[str, torch.Tensor], c, rnd: torch.Tensor) -> List[torch.Tensor]:
+    """Order of draws of one two-arm regrasping ``pre_physics_step`` for table ``rnd`` (``HA_KUKA2_RND_*``)."""
+    from . import kuka2_oracle as k2
+    D = c.n_dofs
+    goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
+    ids = st["reset_buf"].nonzero(as_tuple=False).squeeze(-1)
+
+    def goal_block(rows, base):       # _reset_target: position, side; reset_object_pose: side, position, rotation
+        return [rnd[rows, base:base + 3], rnd[rows, base + 3:base + 4], rnd[rows, base + 4:base + 5], rnd[rows, base + 5:base + 8],
+                rnd[rows, base + 8:base + 11]]
+
+    q = goal_block(goal_ids, k2.RND_GOAL)
+    prob = st["random_force_prob"].clone()
+    if len(ids) > 0:
+        q += goal_block(ids, k2.RND_RESET_GOAL)
+        b = k2.RND_RESET_OBJ
+        q += [rnd[ids, b:b + 1], rnd[ids, b + 1:b + 4], rnd[ids, b + 4:b + 7], rnd[ids, k2.RND_FORCE_PROB],
+              rnd[ids, k2.RND_DOF_POS:k2.RND_DOF_POS + D], rnd[ids, k2.RND_DOF_POS + D:k2.RND_DOF_POS + 2 * D]]
+        pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
+        prob[ids] = torch.exp((torch.log(pr[0]) - torch.log(pr[1])) * rnd[ids, k2.RND_FORCE_PROB] + torch.log(pr[1]))
+    if c.force_scale > 0.0:
+        q.append(rnd[:, k2.RND_FORCE_TEST])
+        hit = (rnd[:, k2.RND_FORCE_TEST] < prob).nonzero(as_tuple=False)
+        q.append(rnd[hit.squeeze(-1), k2.RND_FORCE_NORMAL:k2.RND_FORCE_NORMAL + 3].unsqueeze(1))
+    return q
+
+
+def reference_kuka2_step(env, c, actions: torch.Tensor, rnd: torch.Tensor, st: Dict[str, torch.Tensor]) -> None:
+    with scripted_randoms(kuka2_random_queue(st, c, rnd)) as q:
+        env.pre_physics_step(actions)
+        assert len(q) == 0, f"{len(q)} scripted random tensors were not consumed"
+    env.post_physics_step()
+    env.timeout_buf = (env.progress_buf >= env.max_episode_length - 1) & (env.reset_buf != 0)
+
+
+def harvest_kuka2(env, st: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    from .kuka2_oracle import EPISODE_TERMS, STEP_TERMS
+    out = dict(st)
+    for name in ("progress_buf", "successes", "true_objective", "near_goal_steps", "lifted_object", "closest_keypoint_max_dist",
+                 "closest_fingertip_dist", "timeout_buf", "reset_buf", "reset_goal_buf", "randomize_buf", "prev_episode_successes",
+                 "prev_episode_true_objective", "random_force_prob", "obs_buf", "rew_buf"):
+        out[name] = getattr(env, name)
+    out["actions"] = env.actions
+    out["rewards_episode"] = torch.stack([env.rewards_episode[k] for k in EPISODE_TERMS])
+    cum = env.extras.get("episode_cumulative")
+    if cum is not None:
+        out["episode_cumulative"] = torch.stack([cum[k] for k in STEP_TERMS])
     return out
