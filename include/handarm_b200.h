@@ -102,6 +102,24 @@ enum {
 };
 #define HA_KUKA_RND_STRIDE(n_dofs) (25 + 2 * (n_dofs))
 
+/* two-arm regrasping (allegro_kuka_two_arms.py:1298-1351 + allegro_kuka_two_arms_regrasping.py:75-110): a goal block is
+ * target position 3, target side 1, then the object reset that _reset_target performs (side 1, position 3, rotation 3);
+ * reset_idx draws a second goal block and one more object block (reset_object_pose is called twice, the last one wins) */
+enum {
+  HA_KUKA2_RND_GOAL = 0,         /* 11: goal-only reset                                      */
+  HA_KUKA2_RND_RESET_GOAL = 11,  /* 11: reset_target_pose inside reset_idx                   */
+  HA_KUKA2_RND_RESET_OBJ = 22,   /* 7: reset_object_pose inside reset_idx                    */
+  HA_KUKA2_RND_FORCE_PROB = 29,
+  HA_KUKA2_RND_FORCE_TEST = 30,
+  HA_KUKA2_RND_FORCE_NORMAL = 31, /* 3: N(0,1)                                               */
+  HA_KUKA2_RND_DOF_POS = 34      /* n_dofs position draws, then n_dofs velocity draws        */
+};
+#define HA_KUKA2_RND_STRIDE(n_dofs) (34 + 2 * (n_dofs))
+/* two arms keep 8 per-episode terms / 5 per-step terms (allegro_kuka_two_arms.py:345-354, :861-867):
+ * raw_fingertip_delta, raw_lifting, raw_keypoint, fingertip_delta, lifting, lift_bonus, keypoint, bonus */
+#define HA_KUKA2_N_EPISODE_TERMS 8
+#define HA_KUKA2_N_STEP_TERMS 5
+
 typedef struct HaKukaParams {
   int32_t abi_version;
   int32_t n_envs;
@@ -155,8 +173,9 @@ typedef struct HaKukaParams {
   float target_min[3], target_size[3];      /* target volume */
   float reset_pos_noise[3];
   float reset_dof_vel_noise;
-  float two_arm_x_ofs;      /* two arms: +-x offset of object/goal sides */
-  float reserved_f[7];
+  float two_arm_x_ofs;      /* two arms: +-x offset of the goal side (0.75) */
+  float two_arm_obj_x_ofs;  /* two arms: +-x offset of the object side (table_width / 2 - 0.2) */
+  float reserved_f[6];
 } HaKukaParams;
 
 /* values that change while training (tolerance curriculum); they live in

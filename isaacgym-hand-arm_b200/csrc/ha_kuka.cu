@@ -6,6 +6,8 @@
 #include "ha_host.h"
 #include "ha_kuka_post.cuh"
 #include "ha_kuka_pre.cuh"
+#include "ha_kuka2_post.cuh"
+#include "ha_kuka2_pre.cuh"
 
 namespace {
 
@@ -13,10 +15,15 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   HA_REQUIRE(p != nullptr && b != nullptr, "null params / buffers");
   HA_REQUIRE(p->abi_version == HA_ABI_VERSION, "HaKukaParams.abi_version %d != %d", p->abi_version, HA_ABI_VERSION);
   HA_REQUIRE(p->n_envs > 0, "n_envs must be positive (got %d)", p->n_envs);
-  HA_REQUIRE(p->n_arms == 1, "n_arms=%d: only the single-arm kernels are built into this entry point", p->n_arms);
-  HA_REQUIRE(p->n_dofs == 23 && p->dofs_per_env == 23, "single-arm AllegroKuka needs n_dofs == dofs_per_env == 23 (got %d/%d)",
-             p->n_dofs, p->dofs_per_env);
-  HA_REQUIRE(p->n_tips == 4, "n_tips must be 4 (got %d)", p->n_tips);
+  HA_REQUIRE(p->n_arms == 1 || p->n_arms == 2, "n_arms must be 1 or 2 (got %d)", p->n_arms);
+  const int A = p->n_arms;
+  HA_REQUIRE(p->n_dofs == 23 * A && p->dofs_per_env == 23 * A, "AllegroKuka with %d arm(s) needs n_dofs == dofs_per_env == %d (got %d/%d)",
+             A, 23 * A, p->n_dofs, p->dofs_per_env);
+  HA_REQUIRE(p->n_tips == 4 * A, "n_tips must be %d (got %d)", 4 * A, p->n_tips);
+  if (A == 2) {
+    HA_REQUIRE(p->state_layout == HA_STATE_ISAACGYM, "the two-arm kernels read Isaac Gym's AoS state tensors (HA_STATE_ISAACGYM)");
+    HA_REQUIRE(p->palm_body[1] >= 0 && p->palm_body[1] < p->n_bodies, "palm_body[1] out of range");
+  }
   HA_REQUIRE(p->n_keypoints == 1 || p->n_keypoints == 4, "n_keypoints must be 1 or 4 (got %d)", p->n_keypoints);
   HA_REQUIRE(p->obs_dim == ha_kuka_obs_dim(p->n_arms, p->n_keypoints), "obs_dim %d does not match the task layout %d", p->obs_dim,
              ha_kuka_obs_dim(p->n_arms, p->n_keypoints));
@@ -26,18 +33,20 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
     HA_REQUIRE(p->tip_body[t] >= 0 && p->tip_body[t] < p->n_bodies, "tip_body[%d] out of range", t);
   HA_REQUIRE(p->success_steps >= 1, "success_steps must be >= 1");
   const void* need[] = {b->root_state, b->rigid_body_state, b->dof_state, b->object_actor, b->goal_actor, b->hand_actor,
-                        b->object_init_state, b->object_keypoint_offsets, b->object_scales, b->finger_rew_coeffs, b->goal_states,
+                        b->object_init_state, b->object_keypoint_offsets, b->object_scales, b->goal_states,
                         b->obs_buf, b->rew_buf, b->reset_buf, b->reset_goal_buf, b->progress_buf, b->timeout_buf, b->successes,
                         b->prev_episode_successes, b->true_objective, b->prev_episode_true_objective, b->near_goal_steps,
-                        b->lifted_object, b->closest_keypoint_max_dist, b->closest_fingertip_dist, b->furthest_hand_dist,
+                        b->lifted_object, b->closest_keypoint_max_dist, b->closest_fingertip_dist,
                         b->rewards_episode, b->episode_cumulative, b->prev_targets, b->cur_targets, b->actions, b->rb_forces,
                         b->random_force_prob, b->root_reset_indices, b->hand_reset_indices, b->reset_counts, b->stats, b->stat_accum,
                         b->tickets, b->dynamic};
   for (size_t i = 0; i < sizeof(need) / sizeof(need[0]); ++i) HA_REQUIRE(need[i] != nullptr, "HaKukaBuffers field #%zu is null", i);
+  HA_REQUIRE(A == 2 || (b->finger_rew_coeffs != nullptr && b->furthest_hand_dist != nullptr),
+             "finger_rew_coeffs / furthest_hand_dist are required by the single-arm task");
   HA_REQUIRE_ALIGNED16(b->dof_state);
   HA_REQUIRE_ALIGNED16(b->obs_buf);
   HA_REQUIRE_ALIGNED16(b->closest_fingertip_dist);
-  HA_REQUIRE_ALIGNED16(b->finger_rew_coeffs);
+  if (b->finger_rew_coeffs) HA_REQUIRE_ALIGNED16(b->finger_rew_coeffs);
   HA_REQUIRE_ALIGNED16(b->object_keypoint_offsets);
   HA_REQUIRE_ALIGNED16(b->object_scales);
   HA_REQUIRE_ALIGNED16(b->prev_targets);
@@ -92,6 +101,20 @@ int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStr
                         "kuka_post_kernel launch");
 }
 
+template <int K>
+int launch_post2(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {
+  using S = ha::Kuka2PostSmem<K>;
+  static bool configured = false;
+  if (!configured) {
+    int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka2_post_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
+                            "cudaFuncSetAttribute(kuka2_post_kernel)");
+    if (rc) return rc;
+    configured = true;
+  }
+  const int grid = (p->n_envs + ha::kTile - 1) / ha::kTile;
+  return ha::check_cuda(ha::launch(ha::kuka2_post_kernel<K>, grid, ha::kPostThreads, sizeof(S), st, *p, *b, mode), "kuka2_post_kernel launch");
+}
+
 }  // namespace
 
 extern "C" {
@@ -144,6 +167,11 @@ int ha_kuka_pre_step(const HaKukaParams* p, const HaKukaBuffers* b, const float*
   HA_REQUIRE(ha::aligned16(actions), "actions must be 16-byte aligned");
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  if (p->n_arms == 2) {
+    HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING, "two arms: only the regrasping reset path is built (subtask %d)", p->subtask);
+    return ha::check_cuda(ha::launch(ha::kuka2_pre_kernel, grid, ha::kThreads, 0, (cudaStream_t)stream, *p, *b, actions, ext_rand,
+                                     (int)ha::kPreFull), "kuka2_pre_kernel launch");
+  }
   return ha::check_cuda(ha::launch(ha::kuka_pre_kernel, grid, ha::kThreads, 0, (cudaStream_t)stream, *p, *b, actions, ext_rand, (int)ha::kPreFull),
                         "kuka_pre_kernel launch");
 }
@@ -153,7 +181,12 @@ int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float
   if (rc) return rc;
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
-  ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);
+  if (p->n_arms == 2) {
+    HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING, "two arms: only the regrasping reset path is built (subtask %d)", p->subtask);
+    ha::kuka2_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);
+  } else {
+    ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);
+  }
   if (p->use_fast_rng) ha::kuka_rng_tick_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(b->dynamic);
   return ha::check_cuda(cudaGetLastError(), "kuka_pre_kernel(reset_only) launch");
 }
@@ -161,6 +194,7 @@ int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float
 static int post_dispatch(const HaKukaParams* p, const HaKukaBuffers* b, int mode, ha_stream_t stream) {
   int rc = validate_kuka(p, b);
   if (rc) return rc;
+  if (p->n_arms == 2) return p->n_keypoints == 4 ? launch_post2<4>(p, b, mode, (cudaStream_t)stream) : launch_post2<1>(p, b, mode, (cudaStream_t)stream);
   const bool soa = p->state_layout == HA_STATE_SOA;
   if (p->n_keypoints == 4) return soa ? launch_post<4, true>(p, b, mode, (cudaStream_t)stream) : launch_post<4, false>(p, b, mode, (cudaStream_t)stream);
   return soa ? launch_post<1, true>(p, b, mode, (cudaStream_t)stream) : launch_post<1, false>(p, b, mode, (cudaStream_t)stream);

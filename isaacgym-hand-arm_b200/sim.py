@@ -44,6 +44,10 @@ KUKA_LAYOUT = ActorLayout(actors_per_env=4, bodies_per_env=27, dofs_per_env=23, 
                           palm_body=(7,), tip_body=(11, 15, 19, 23), object_body=24)
 
 
+# two arms (allegro_kuka_two_arms.py:652-680): arm0 (24 bodies), arm1 (24), object, table, goal ball
+KUKA2_LAYOUT = ActorLayout(actors_per_env=5, bodies_per_env=51, dofs_per_env=46, hand_actor=(0, 1), object_actor=2, goal_actor=4,
+                           palm_body=(7, 31), tip_body=(11, 15, 19, 23, 35, 39, 43, 47), object_body=48)
+
 # ShadowHand (mjcf/open_ai_assets/hand/shadow_hand.xml): 26 hand bodies + object + goal, 24 joints, fingertips = the five
 # *distal bodies; AllegroHand (allegro_touch_sensor.urdf): 17 hand bodies + object + goal, 16 joints.  Actors: hand, object, goal.
 SHADOW_HAND_LAYOUT = ActorLayout(actors_per_env=3, bodies_per_env=28, dofs_per_env=24, hand_actor=(0,), object_actor=1, goal_actor=2,

@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from .. import _lib
-from ..sim import KUKA_ALLEGRO_LOWER, KUKA_ALLEGRO_UPPER, KUKA_LAYOUT, ActorLayout, SyntheticSim, cuboid_scales
+from ..sim import (KUKA2_LAYOUT, KUKA_ALLEGRO_LOWER, KUKA_ALLEGRO_UPPER, KUKA_LAYOUT, ActorLayout, SyntheticSim, cuboid_scales)
 from ..vec_task import VecTask
 
 C = _lib.CONSTS
@@ -30,6 +30,9 @@ STEP_TERM_KEYS = [
     "fingertip_delta_rew", "hand_delta_penalty", "lifting_rew", "lift_bonus_rew", "keypoint_rew", "kuka_actions_penalty",
     "allegro_actions_penalty", "bonus_rew",
 ]   # allegro_kuka_base.py:912-921
+EPISODE_TERM_KEYS_2ARMS = ["raw_fingertip_delta_rew", "raw_lifting_rew", "raw_keypoint_rew", "fingertip_delta_rew", "lifting_rew",
+                           "lift_bonus_rew", "keypoint_rew", "bonus_rew"]                      # allegro_kuka_two_arms.py:345-354
+STEP_TERM_KEYS_2ARMS = ["fingertip_delta_rew", "lifting_rew", "lift_bonus_rew", "keypoint_rew", "bonus_rew"]   # :861-867
 
 
 def tolerance_curriculum(last_update: int, frames: int, interval: int, prev_episode_successes: torch.Tensor, tol: float,
@@ -52,12 +55,15 @@ def true_objective_coeffs(tol: float, initial_tol: float, target_tol: float):
 
 class AllegroKukaBase(VecTask):
     subtask_id = C["HA_KUKA_REORIENTATION"]
+    num_arms = 1                      # AllegroKukaTwoArmsBase (allegro_kuka_two_arms.py) sets 2
+    default_layout = KUKA_LAYOUT
+    episode_term_keys, step_term_keys = EPISODE_TERM_KEYS, STEP_TERM_KEYS
 
     def __init__(self, cfg, rl_device, sim_device, graphics_device_id, headless, virtual_screen_capture=False, force_render=False,
-                 sim: Optional[SyntheticSim] = None, layout: ActorLayout = KUKA_LAYOUT, seed: int = 1234, snapshots: int = 1):
+                 sim: Optional[SyntheticSim] = None, layout: Optional[ActorLayout] = None, seed: int = 1234, snapshots: int = 1):
         self.cfg = cfg
         env = cfg["env"]
-        self._injected_sim, self._layout, self._seed, self._snapshots = sim, layout, seed, snapshots
+        self._injected_sim, self._layout, self._seed, self._snapshots = sim, layout or self.default_layout, seed, snapshots
         self.frame_since_restart = 0
         self.clamp_abs_observations = env["clampAbsObservations"]
         self.privileged_actions = env["privilegedActions"]
@@ -66,7 +72,7 @@ class AllegroKukaBase(VecTask):
         self.num_arm_dofs, self.num_finger_dofs, self.num_allegro_fingertips = 7, 4, 4
         self.num_hand_dofs = self.num_finger_dofs * self.num_allegro_fingertips
         self.num_hand_arm_dofs = self.num_hand_dofs + self.num_arm_dofs
-        self.num_allegro_kuka_actions = self.num_hand_arm_dofs
+        self.num_allegro_kuka_actions = self.num_hand_arm_dofs * self.num_arms
         self.randomize = cfg["task"]["randomize"]
         self.randomization_params = cfg["task"]["randomization_params"]
         self.distance_delta_rew_scale = env["distanceDeltaRewScale"]
@@ -120,7 +126,11 @@ class AllegroKukaBase(VecTask):
         if self.obs_type not in ["full_state"]:
             raise Exception("Unknown type of observations!")            # allegro_kuka_base.py:180-181
         T, K, D = self.num_allegro_fingertips, self.num_keypoints, self.num_hand_arm_dofs
-        self.full_state_size = 2 * D + 3 + 10 + 10 + 3 * T + 6 * K + 3 + 1 + 1 + 2 + T + 1   # allegro_kuka_base.py:185-220
+        if self.num_arms == 1:
+            self.full_state_size = 2 * D + 3 + 10 + 10 + 3 * T + 6 * K + 3 + 1 + 1 + 2 + T + 1   # allegro_kuka_base.py:185-220
+        else:   # allegro_kuka_two_arms.py:176-211: no closest_fingertip_dist slots, keypoints relative to both palms
+            A = self.num_arms
+            self.full_state_size = 2 * D * A + 3 * A + 10 * A + 10 + 3 * T * A + 3 * K * A + 3 * K + 3 + 1 + 1 + 2 + 1
         self.num_obs_dict = {"full_state": self.full_state_size}
         self.up_axis, self.up_axis_idx = "z", 2
         cfg["env"]["numObservations"] = self.num_obs_dict[self.obs_type]
@@ -147,14 +157,16 @@ class AllegroKukaBase(VecTask):
         N, dev = self.num_envs, self.device
         self.num_bodies = L.bodies_per_env
         self.num_dofs = L.dofs_per_env
-        self.arm_hand_dof_lower_limits = torch.tensor(KUKA_ALLEGRO_LOWER, dtype=torch.float, device=dev)
-        self.arm_hand_dof_upper_limits = torch.tensor(KUKA_ALLEGRO_UPPER, dtype=torch.float, device=dev)
+        self.arm_hand_dof_lower_limits = torch.tensor(KUKA_ALLEGRO_LOWER * self.num_arms, dtype=torch.float, device=dev)
+        self.arm_hand_dof_upper_limits = torch.tensor(KUKA_ALLEGRO_UPPER * self.num_arms, dtype=torch.float, device=dev)
         self.allegro_palm_handle = L.palm_body[0]
+        self.allegro_palm_handles = list(L.palm_body)
         self.allegro_fingertip_handles = torch.tensor(list(L.tip_body), dtype=torch.long, device=dev)
         self.object_rb_handles = torch.tensor([L.object_body], dtype=torch.long, device=dev)
         self.object_rb_masses = torch.tensor([400.0 * self.object_base_size ** 3], dtype=torch.float, device=dev)
         ar = torch.arange(N, dtype=torch.long, device=dev) * L.actors_per_env
         self.allegro_hand_indices = ar + L.hand_actor[0]
+        self.arm_indices = torch.stack([ar + h for h in L.hand_actor], dim=1)     # [N, num_arms] (allegro_kuka_two_arms.py:661-680)
         self.object_indices = ar + L.object_actor
         self.goal_object_indices = ar + L.goal_actor
         scales = cuboid_scales(self.with_small_cuboids, self.with_big_cuboids, self.with_sticks)
@@ -181,10 +193,17 @@ class AllegroKukaBase(VecTask):
         """allegro_kuka_base.py:258-372, same names and dtypes."""
         N, dev, T = self.num_envs, self.device, self.num_allegro_fingertips
         f = dict(dtype=torch.float, device=dev)
-        self.target_volume_origin = torch.tensor([0, 0.05, 0.8], **f)
-        self.target_volume_extent = torch.tensor([[-0.4, 0.4], [-0.05, 0.3], [-0.12, 0.25]], **f)
-        self.hand_arm_default_dof_pos = torch.zeros(self.num_hand_arm_dofs, **f)
-        self.hand_arm_default_dof_pos[:7] = torch.tensor([-1.571, 1.571, -0.000, 1.376, -0.000, 1.485, 2.358])
+        if self.num_arms == 1:
+            self.target_volume_origin = torch.tensor([0, 0.05, 0.8], **f)
+            self.target_volume_extent = torch.tensor([[-0.4, 0.4], [-0.05, 0.3], [-0.12, 0.25]], **f)
+            self.hand_arm_default_dof_pos = torch.zeros(self.num_hand_arm_dofs, **f)
+            self.hand_arm_default_dof_pos[:7] = torch.tensor([-1.571, 1.571, -0.000, 1.376, -0.000, 1.485, 2.358])
+        else:   # allegro_kuka_two_arms.py:243-276
+            self.target_volume_origin = torch.tensor([0, 0.0, 0.8], **f)
+            self.target_volume_extent = torch.tensor([[-0.2, 0.2], [-0.5, 0.5], [-0.12, 0.25]], **f)
+            dflt = torch.zeros([self.num_arms, self.num_hand_arm_dofs], **f)
+            dflt[:, :7] = torch.tensor([-1.571, 1.571, -0.000, 1.6, -0.000, 1.485, 2.358])
+            self.hand_arm_default_dof_pos = dflt.flatten()
         self.prev_targets = torch.zeros((N, self.num_dofs), **f)
         self.cur_targets = torch.zeros((N, self.num_dofs), **f)
         self.actions = torch.zeros((N, self.num_actions), **f)
@@ -204,24 +223,24 @@ class AllegroKukaBase(VecTask):
         self.near_goal_steps = torch.zeros(N, dtype=torch.int, device=dev)
         self.lifted_object = torch.zeros(N, dtype=torch.bool, device=dev)
         self.closest_keypoint_max_dist = -torch.ones(N, **f)
-        self.closest_fingertip_dist = -torch.ones([N, T], **f)
+        self.closest_fingertip_dist = -torch.ones([N, T] if self.num_arms == 1 else [N, self.num_arms, T], **f)
         self.furthest_hand_dist = -torch.ones([N], **f)
         self.finger_rew_coeffs = torch.ones([N, T], **f)
-        # SoA: one [12, N] block, exposed under the reference's dict keys as row views
-        self._rewards_episode = torch.zeros((len(EPISODE_TERM_KEYS), N), **f)
-        self.rewards_episode = {k: self._rewards_episode[i] for i, k in enumerate(EPISODE_TERM_KEYS)}
-        self._episode_cumulative = torch.zeros((len(STEP_TERM_KEYS), N), **f)
-        self.episode_cumulative = {k: self._episode_cumulative[i] for i, k in enumerate(STEP_TERM_KEYS)}
+        # SoA: one [terms, N] block, exposed under the reference's dict keys as row views
+        self._rewards_episode = torch.zeros((len(self.episode_term_keys), N), **f)
+        self.rewards_episode = {k: self._rewards_episode[i] for i, k in enumerate(self.episode_term_keys)}
+        self._episode_cumulative = torch.zeros((len(self.step_term_keys), N), **f)
+        self.episode_cumulative = {k: self._episode_cumulative[i] for i, k in enumerate(self.step_term_keys)}
         self.last_curriculum_update = 0
         # engine-side buffers
         self.root_reset_indices = torch.zeros(2 * N, dtype=torch.int32, device=dev)
-        self.hand_reset_indices = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.hand_reset_indices = torch.zeros(N * self.num_arms, dtype=torch.int32, device=dev)
         self.reset_counts = torch.zeros(4, dtype=torch.int32, device=dev)
         self.stats = torch.zeros(C["HA_STATS_LEN"], **f)
         self._tickets = torch.zeros(8, dtype=torch.int32, device=dev)
         self._object_actor_i32 = self.object_indices.to(torch.int32)
         self._goal_actor_i32 = self.goal_object_indices.to(torch.int32)
-        self._hand_actor_i32 = self.allegro_hand_indices.to(torch.int32)
+        self._hand_actor_i32 = self.arm_indices.to(torch.int32).contiguous()
         self._object_init_z = self.object_init_state[:, 2].contiguous()   # compact copy for the per-step read (task constant)
         self._dynamic = torch.zeros(8, **f)          # HaKukaDynamic (32 bytes)
         self.ext_rand: Optional[torch.Tensor] = None   # parity mode: [N, HA_KUKA_RND_STRIDE] raw draws
@@ -236,10 +255,14 @@ class AllegroKukaBase(VecTask):
         L = self._layout
         p = _lib.HaKukaParams()
         p.abi_version = C["HA_ABI_VERSION"]
-        p.n_envs, p.n_arms, p.n_dofs, p.dofs_per_env = self.num_envs, 1, self.num_hand_arm_dofs, self.num_dofs
-        p.n_bodies, p.n_tips, p.n_keypoints, p.obs_dim = self.num_bodies, self.num_allegro_fingertips, self.num_keypoints, self.num_obs
+        n_dofs = self.num_hand_arm_dofs * self.num_arms
+        p.n_envs, p.n_arms, p.n_dofs, p.dofs_per_env = self.num_envs, self.num_arms, n_dofs, self.num_dofs
+        p.n_bodies, p.n_tips, p.n_keypoints, p.obs_dim = (self.num_bodies, self.num_allegro_fingertips * self.num_arms, self.num_keypoints,
+                                                          self.num_obs)
         p.subtask = self.subtask_id
-        p.palm_body[0] = L.palm_body[0]
+        for a, h in enumerate(L.palm_body):
+            p.palm_body[a] = h
+        p.two_arm_x_ofs, p.two_arm_obj_x_ofs = 0.75, 1.1 / 2 - 0.2     # allegro_kuka_two_arms_regrasping.py:91, allegro_kuka_two_arms.py:1163-1164
         for i, t in enumerate(L.tip_body):
             p.tip_body[i] = t
         p.object_body = L.object_body
@@ -254,9 +277,9 @@ class AllegroKukaBase(VecTask):
                 p.tip_offset[t][c] = float(self.fingertip_offsets[t][c])
         lo, hi = self.arm_hand_dof_lower_limits.cpu(), self.arm_hand_dof_upper_limits.cpu()
         dflt = self.hand_arm_default_dof_pos.cpu()
-        for d in range(self.num_hand_arm_dofs):
+        for d in range(n_dofs):
             p.dof_lower[d], p.dof_upper[d], p.dof_default[d] = float(lo[d]), float(hi[d]), float(dflt[d])
-            p.dof_reset_noise[d] = self.reset_dof_pos_noise_arm if d < 7 else self.reset_dof_pos_noise_fingers
+            p.dof_reset_noise[d] = self.reset_dof_pos_noise_arm if d % self.num_hand_arm_dofs < 7 else self.reset_dof_pos_noise_fingers
         self._lib.ha_kuka_fill_derived(ctypes.byref(p))
         clamp = self.clamp_abs_observations if self.clamp_abs_observations > 0 else math.inf
         clamp = min(clamp, self.clip_obs)            # clamp_obs (:1174-1176) then the VecTask clip (vec_task.py:432)
@@ -365,11 +388,11 @@ class AllegroKukaBase(VecTask):
 
     @property
     def arm_hand_dof_pos(self):
-        return self.sim.dof_state.view(self.num_envs, -1, 2)[:, : self.num_hand_arm_dofs, 0]
+        return self.sim.dof_state.view(self.num_envs, -1, 2)[:, : self.num_hand_arm_dofs * self.num_arms, 0]
 
     @property
     def arm_hand_dof_vel(self):
-        return self.sim.dof_state.view(self.num_envs, -1, 2)[:, : self.num_hand_arm_dofs, 1]
+        return self.sim.dof_state.view(self.num_envs, -1, 2)[:, : self.num_hand_arm_dofs * self.num_arms, 1]
 
     # ---- env state side channel (allegro_kuka_base.py:472-493) ------------------------------------
     def get_env_state(self):
@@ -387,7 +410,7 @@ class AllegroKukaBase(VecTask):
     # ---- the hot path --------------------------------------------------------------------------
     def _rand_ptr(self):
         if self.ext_rand is not None:
-            stride = 25 + 2 * self.num_hand_arm_dofs       # HA_KUKA_RND_STRIDE
+            stride = (25 if self.num_arms == 1 else 34) + 2 * self.num_hand_arm_dofs * self.num_arms   # HA_KUKA_RND_STRIDE / HA_KUKA2_RND_STRIDE
             assert self.ext_rand.shape == (self.num_envs, stride) and self.ext_rand.dtype == torch.float32 and self.ext_rand.is_contiguous()
             self._params.use_fast_rng = 0
             return ctypes.c_void_p(self.ext_rand.data_ptr())
@@ -481,3 +504,15 @@ class AllegroKukaReorientation(AllegroKukaBase):
         if tol != self.success_tolerance:
             self.success_tolerance = tol
             self._write_dynamic()
+
+
+class AllegroKukaTwoArmsRegrasping(AllegroKukaReorientation):
+    """allegro_kuka_two_arms.py (``AllegroKukaTwoArmsBase``) + allegro_kuka_two_arms_regrasping.py:40-135: two Kuka-Allegro arms pass
+    the object between them; 46 DOFs all position-controlled, one keypoint (the object centre), 169-wide observation."""
+    subtask_id = C["HA_KUKA_REGRASPING"]
+    num_arms = 2
+    default_layout = KUKA2_LAYOUT
+    episode_term_keys, step_term_keys = EPISODE_TERM_KEYS_2ARMS, STEP_TERM_KEYS_2ARMS
+
+    def _object_keypoint_offsets(self):
+        return [[0, 0, 0]]

@@ -60,3 +60,28 @@ def load_hand_fixture(name: str):
             s[phase] = {k[len(pre):]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith(pre)}
         steps.append(s)
     return c, st, steps
+
+
+def kuka2_fixture_names() -> List[str]:
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "kuka2_*.npz")))
+
+
+def load_kuka2_fixture(name: str):
+    """-> (Kuka2Consts, input state dict, [per-step dict(actions, rnd, pre={...}, post={...}, extras={...})])"""
+    import json
+    from oracle import kuka2_oracle as k2
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    d = json.loads(str(z["meta/consts_json"]))
+    for k, v in list(d.items()):
+        if isinstance(v, list):
+            d[k] = tuple(tuple(x) if isinstance(x, list) else x for x in v)
+    c = k2.Kuka2Consts(**d)
+    st = {k.split("/", 1)[1]: torch.from_numpy(z[k].copy()) for k in z.files if k.startswith("in/")}
+    steps = []
+    for i in range(int(z["meta/steps"])):
+        s: Dict[str, object] = {"actions": torch.from_numpy(z[f"s{i}/actions"].copy()), "rnd": torch.from_numpy(z[f"s{i}/rnd"].copy())}
+        for phase in ("pre", "post", "extras"):
+            pre = f"s{i}/{phase}/"
+            s[phase] = {k[len(pre):]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith(pre)}
+        steps.append(s)
+    return c, st, steps
