@@ -101,7 +101,7 @@ size_t ha_hand_post_bytes_per_env_step(const HaHandParams* p) {
   if (dof) rd += 8 * D;
   if (full) rd += 4 * D + 24 * T;
   rd += 52 * T;
-  const size_t wr = 4 * ((size_t)p->obs_dim + (size_t)p->states_dim) + 4 + 24 + 4 + 4;   // rows, reward, 3 int64, successes, (timeout + pad)
+  const size_t wr = 4 * ((size_t)p->obs_dim + (size_t)p->states_dim) + 4 + 24 + 4;       // rows, reward, 3 int64, successes
   return rd + wr;
 }
 

@@ -96,7 +96,33 @@ def load_reference() -> Dict[str, types.ModuleType]:
     _loaded["ak2g"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms_regrasping")
     _loaded["sh"] = importlib.import_module("isaacgymenvs.tasks.shadow_hand")
     _loaded["ah"] = importlib.import_module("isaacgymenvs.tasks.allegro_hand")
+    _loaded["adrv"] = importlib.import_module("isaacgymenvs.tasks.dextreme.adr_vec_task")
+    _loaded["dx"] = _load_dextreme(root)
     return _loaded
+
+
+def _load_dextreme(root: str) -> types.ModuleType:
+    """``allegro_hand_dextreme.py`` executed from where it lies with TWO source-level patches, both needed only to run it on
+    CPU torch 2.x: ``:1630`` passes an int64 tensor as the condition of ``torch.where``, which torch >= 2 rejects (``!= 0`` is the
+    meaning old torch gave it); ``:969`` shifts the action queue with an overlapping slice assignment, which the CPU
+    backend refuses ("refer to a single memory location") -- ``.clone()`` of the source gives the shift the CUDA backend performs."""
+    path = os.path.join(root, "tasks", "dextreme", "allegro_hand_dextreme.py")
+    src = open(path).read()
+    old, new = "torch.where(goal_reached, hold_count_buf + 1", "torch.where(goal_reached != 0, hold_count_buf + 1"
+    assert src.count(old) == 1, "the reference changed: the documented torch.where patch no longer applies"
+    name = "isaacgymenvs.tasks.dextreme.allegro_hand_dextreme"
+    mod = types.ModuleType(name)
+    mod.__file__ = path
+    sys.modules[name] = mod
+    old2, new2 = "self.prev_actions_queue[:, :-1].detach()", "self.prev_actions_queue[:, :-1].clone()"
+    assert src.count(old2) == 1, "the reference changed: the documented queue-shift patch no longer applies"
+    patched = src.replace(old, new).replace(old2, new2)
+    shown = path + "<patched>"                                # torch.jit.script re-reads the source through linecache
+    import linecache
+    linecache.cache[shown] = (len(patched), None, patched.splitlines(True), shown)
+    mod.__file__ = shown
+    exec(compile(patched, shown, "exec"), mod.__dict__)
+    return mod
 
 
 class FakeGym:
@@ -477,4 +503,148 @@ def harvest_kuka2(env, st: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     cum = env.extras.get("episode_cumulative")
     if cum is not None:
         out["episode_cumulative"] = torch.stack([cum[k] for k in STEP_TERMS])
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# AllegroHandDextremeADR (tasks/dextreme/allegro_hand_dextreme.py, adr_vec_task.py)
+# ---------------------------------------------------------------------------------------------
+def make_reference_dextreme(st: Dict[str, torch.Tensor], c) -> object:
+    """A reference ``AllegroHandDextremeADR`` instance aliasing the tensors of ``st`` (``oracle/dextreme_state.py`` layout).
+    ``apply_randomizations`` (Isaac Gym property DR + host ADR bookkeeping) is replaced by a no-op: the per-env ADR tensors and
+    affine parameters of ``st`` play the role of what it sampled."""
+    from . import dextreme_oracle as dx
+    mods = load_reference()
+    env = object.__new__(mods["dx"].AllegroHandDextremeADR)
+    N, D = st["reset_buf"].shape[0], c.n_dofs
+    env.__dict__.update(
+        gym=FakeGym(), sim=None, device="cpu", rl_device="cpu", sim_device="cpu", num_environments=N, viewer=None, debug_viz=False,
+        headless=True, num_actions=D, num_hand_dofs=D, num_fingertips=c.n_tips, randomize=True, use_adr=True, randomization_params={},
+        up_axis_idx=2, dt=c.dt, control_freq_inv=c.control_freq_inv, use_relative_control=False,
+        use_capped_dof_control=c.use_capped_dof_control, max_dof_radians_per_second=c.max_dof_radians_per_second,
+        act_moving_average=c.act_moving_average, act_moving_average_scheduled_freq=500, act_moving_average_scheduled_steps=1000000,
+        act_moving_average_lower=0.15, act_moving_average_upper=0.2, last_step=0, enable_rna=False, apply_random_quat=c.apply_random_quat,
+        random_cube_pose_prob=c.random_cube_pose_prob, enable_random_obs=True, force_scale=c.force_scale,
+        force_decay_interval=c.force_decay_interval, max_episode_length=c.max_episode_length, dist_reward_scale=c.dist_reward_scale,
+        rot_reward_scale=c.rot_reward_scale, rot_eps=c.rot_eps, action_penalty_scale=c.action_penalty_scale,
+        action_delta_penalty_scale=c.action_delta_penalty_scale, success_tolerance=c.success_tolerance,
+        reach_goal_bonus=c.reach_goal_bonus, fall_dist=c.fall_dist, fall_penalty=c.fall_penalty,
+        max_consecutive_successes=c.max_consecutive_successes, num_success_hold_steps=c.num_success_hold_steps,
+        print_success_stat=False, vel_obs_scale=c.vel_obs_scale, force_torque_obs_scale=c.force_torque_obs_scale,
+        reset_position_noise=c.reset_position_noise, reset_position_noise_z=c.reset_position_noise_z,
+        reset_dof_pos_noise=c.reset_dof_pos_noise, reset_dof_vel_noise=c.reset_dof_vel_noise, extras={}, total_successes=0, total_resets=0,
+        clip_obs=c.clip_obs,
+    )
+    env.apply_randomizations = lambda *a, **k: None
+    env.frame = int(st["frame"])
+    env.av_factor = torch.tensor(c.av_factor, dtype=torch.float32)
+    env.force_decay = torch.tensor(c.force_decay, dtype=torch.float32)
+    env.force_prob_range = torch.tensor(c.force_prob_range, dtype=torch.float32)
+    env.goal_displacement_tensor = torch.tensor(c.goal_displacement, dtype=torch.float32)
+    env.x_unit_tensor = torch.tensor([1.0, 0.0, 0.0]).repeat(N, 1)
+    env.y_unit_tensor = torch.tensor([0.0, 1.0, 0.0]).repeat(N, 1)
+    env.actuated_dof_indices = torch.arange(D, dtype=torch.long)
+    env.fingertip_handles = torch.tensor(list(c.tip_bodies), dtype=torch.long)
+    env.palm_link_handle = (c.palm_body,)                                   # the reference stores a 1-tuple (:390, trailing comma)
+    env.object_rb_handles = torch.tensor([c.object_body], dtype=torch.long)
+    env.object_rb_masses = torch.tensor([c.object_mass], dtype=torch.float32)
+    env.all_env_ids = torch.arange(N, dtype=torch.long)
+    env.root_state_tensor = st["root_state"]
+    env.rigid_body_states = st["rigid_body_state"].view(N, -1, 13)
+    env.dof_state = st["dof_state"].view(N, -1, 2)[:, :D]
+    env.dof_pos = env.dof_state[..., 0]
+    env.dof_vel = env.dof_state[..., 1]
+    env.dof_force_tensor = st["dof_force"]
+    env.vec_sensor_tensor = st["sensors"]
+    env.hand_dof_lower_limits = st["dof_lower"]
+    env.hand_dof_upper_limits = st["dof_upper"]
+    env.hand_default_dof_pos = torch.zeros(D)
+    env.hand_dof_default_pos = st["dof_default"]
+    env.hand_dof_default_vel = torch.zeros(D)
+    env.num_bodies = env.rigid_body_states.shape[1]
+    for name in ("hand_indices", "object_indices", "goal_object_indices", "goal_states", "goal_init_state", "object_init_state",
+                 "rew_buf", "reset_buf", "reset_goal_buf", "progress_buf", "hold_count_buf", "apply_reset_buf", "successes",
+                 "consecutive_successes", "best_rotation_dist", "prev_targets", "cur_targets", "prev_prev_targets", "prev_actions",
+                 "prev_actions_queue", "rb_forces", "random_force_prob", "random_cube_poses", "object_pose", "object_pose_wrt_wrist",
+                 "obs_object_pose", "obs_object_pose_freq", "action_latency", "cube_pose_refresh_rate", "cube_pose_refresh_offset",
+                 "affine_actions_scaling", "affine_actions_additive", "affine_cube_pose_scaling", "affine_cube_pose_additive",
+                 "affine_dof_pos_scaling", "affine_dof_pos_additive", "cube_random_params", "hand_random_params", "gravity_vec"):
+        setattr(env, name, st[name])
+    env.adr_tensor_values = {k: st["adr_" + k] for k in dx.ADR_KEYS}
+    env.actions = st["actions"]
+    env.timeout_buf = st["timeout_buf"]
+    env.obs_dict = {k: torch.zeros(N, w) for k, w in dx.OBS_KEYS}
+    return env
+
+
+def dextreme_random_queues(st: Dict[str, torch.Tensor], c, rnd: torch.Tensor, prnd: torch.Tensor):
+    """Draw order of one Dextreme ``pre_physics_step`` and one ``post_physics_step`` for the tables ``HA_DEX_RND_*`` / ``HA_DEX_POST_RND_*``."""
+    from . import dextreme_oracle as dx
+    N, D = st["reset_buf"].shape[0], c.n_dofs
+    goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
+    ids = st["apply_reset_buf"].nonzero(as_tuple=False).flatten()
+    q: List[torch.Tensor] = []
+
+    def target(rows, base):
+        out = [rnd[rows, base:base + 4]]
+        if c.apply_random_quat:
+            out.append(rnd[rows, base + 4:base + 7])
+        return out
+
+    if len(goal_ids) > 0:
+        q += target(goal_ids, dx.RND_GOAL)
+    prob = st["random_force_prob"].clone()
+    if len(ids) > 0:
+        q.append(rnd[ids, dx.RND_RESET:dx.RND_RESET + 2 * D + 5])
+        q += target(ids, dx.RND_RESET_GOAL)
+        if c.apply_random_quat:
+            q.append(rnd[ids, dx.RND_RESET + 2 * D + 5:dx.RND_RESET + 2 * D + 8])
+        q.append(rnd[ids, dx.RND_FORCE_PROB])
+        pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
+        prob[ids] = torch.exp((torch.log(pr[0]) - torch.log(pr[1])) * rnd[ids, dx.RND_FORCE_PROB] + torch.log(pr[1]))
+    q += [rnd[:, dx.RND_ACTION_DELAY], rnd[:, dx.RND_ACTION_WHITE:dx.RND_ACTION_WHITE + D]]
+    if c.force_scale > 0.0:
+        q.append(rnd[:, dx.RND_FORCE_TEST])
+        hit = (rnd[:, dx.RND_FORCE_TEST] < prob).nonzero(as_tuple=False)
+        q.append(rnd[hit.squeeze(-1), dx.RND_FORCE_NORMAL:dx.RND_FORCE_NORMAL + 3].unsqueeze(1))
+    pq = [prnd[:, dx.PRND_POSE_WHITE:dx.PRND_POSE_WHITE + 7], prnd[:, dx.PRND_CUBE:dx.PRND_CUBE + 5]]
+    if c.apply_random_quat:
+        pq.append(prnd[:, dx.PRND_CUBE_QUAT:dx.PRND_CUBE_QUAT + 3])
+    pq += [prnd[:, dx.PRND_CUBE_MASK:dx.PRND_CUBE_MASK + 1], prnd[:, dx.PRND_DELAY], prnd[:, dx.PRND_DOF_WHITE:dx.PRND_DOF_WHITE + D]]
+    return q, pq
+
+
+def reference_dextreme_step(env, c, actions: torch.Tensor, rnd: torch.Tensor, prnd: torch.Tensor, st: Dict[str, torch.Tensor]) -> None:
+    from . import dextreme_oracle as dx
+    q_pre, q_post = dextreme_random_queues(st, c, rnd, prnd)
+    progress = torch.clamp((rnd[:, dx.RND_PROGRESS] * c.max_episode_length).long(), max=c.max_episode_length - 1)
+    old_randint = torch.randint
+    torch.randint = lambda *a, **k: progress.clone()       # the all-env reset's torch.randint(0, max_episode_length) (:848-849)
+    try:
+        with scripted_randoms(q_pre) as q:
+            env.pre_physics_step(actions)
+            assert len(q) == 0, f"{len(q)} scripted random tensors were not consumed (pre)"
+        with scripted_randoms(q_post) as q:
+            env.post_physics_step()
+            assert len(q) == 0, f"{len(q)} scripted random tensors were not consumed (post)"
+    finally:
+        torch.randint = old_randint
+    env.timeout_buf = (env.progress_buf >= env.max_episode_length - 1) & (env.reset_buf != 0)      # adr_vec_task.py:290
+
+
+def harvest_dextreme(env, st: Dict[str, torch.Tensor], c) -> Dict[str, torch.Tensor]:
+    from . import dextreme_oracle as dx
+    out = dict(st)
+    for name in ("rew_buf", "reset_buf", "reset_goal_buf", "progress_buf", "hold_count_buf", "apply_reset_buf", "successes",
+                 "consecutive_successes", "best_rotation_dist", "prev_targets", "cur_targets", "prev_prev_targets", "prev_actions",
+                 "prev_actions_queue", "rb_forces", "random_force_prob", "object_pose", "object_pose_wrt_wrist", "obs_object_pose",
+                 "obs_object_pose_freq", "timeout_buf", "actions", "dof_delta", "curr_rotation_dist", "random_cube_poses"):
+        if hasattr(env, name):
+            out[name] = getattr(env, name)
+    out["frame"] = torch.tensor(env.frame, dtype=torch.long)
+    if "episode_cumulative" in env.extras:
+        out["episode_cumulative"] = torch.stack([env.extras["episode_cumulative"][k].to(torch.float32) for k in dx.STEP_TERMS], dim=0)
+    out["obs"] = {k: env.obs_dict[k] for k, _ in dx.OBS_KEYS}
+    out["obs_rows"] = torch.cat([env.obs_dict[k] for k, _ in dx.OBS_KEYS], dim=-1)
+    out["obs_out"] = torch.clamp(out["obs_rows"], -c.clip_obs, c.clip_obs)
     return out

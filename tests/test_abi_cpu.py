@@ -62,6 +62,25 @@ def test_algorithmic_bytes_per_env_step(lib):
     assert lib.ha_kuka_bytes_per_env_step(ctypes.byref(p2)) == 2670
 
 
+def test_hand_algorithmic_bytes_per_env_step(lib):
+    """ShadowHand full 640 + 660 + 416 = 1716, full_state 856 + 876 + 416 = 2148, AllegroHand full_state 364 + 384 + 336 = 1084."""
+    C = _lib.CONSTS
+
+    def hand(shadow, D, A, T, obs_type, obs_dim):
+        p = _lib.HaHandParams()
+        p.is_shadow, p.n_dofs, p.n_actions, p.n_tips, p.obs_type, p.obs_dim, p.states_dim = shadow, D, A, T, obs_type, obs_dim, 0
+        return p
+
+    sh = hand(1, 24, 20, 5, C["HA_HAND_OBS_FULL"], 157)
+    assert lib.ha_hand_post_bytes_per_env_step(ctypes.byref(sh)) == 640 + 660
+    assert lib.ha_hand_pre_bytes_per_env_step(ctypes.byref(sh)) == 416
+    sh = hand(1, 24, 20, 5, C["HA_HAND_OBS_FULL_STATE"], 211)
+    assert lib.ha_hand_bytes_per_env_step(ctypes.byref(sh)) == 2148
+    ah = hand(0, 16, 16, 0, C["HA_HAND_OBS_FULL_STATE"], 88)
+    assert lib.ha_hand_post_bytes_per_env_step(ctypes.byref(ah)) == 364 + 384
+    assert lib.ha_hand_bytes_per_env_step(ctypes.byref(ah)) == 1084
+
+
 def test_stat_accumulator_initial_values(lib):
     C = _lib.CONSTS
     for i in range(C["HA_STATS_LEN"]):
