@@ -85,3 +85,28 @@ def load_kuka2_fixture(name: str):
             s[phase] = {k[len(pre):]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith(pre)}
         steps.append(s)
     return c, st, steps
+
+
+def dextreme_fixture_names() -> List[str]:
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "dextreme_*.npz")))
+
+
+def load_dextreme_fixture(name: str):
+    """-> (DexConsts, input state dict, [per-step dict(actions, rnd, prnd, pre={...}, post={...})])"""
+    import json
+    from oracle import dextreme_oracle as dx
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    d = json.loads(str(z["meta/consts_json"]))
+    for k, v in list(d.items()):
+        if isinstance(v, list):
+            d[k] = tuple(v)
+    c = dx.DexConsts(**d)
+    st = {k.split("/", 1)[1]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith("in/")}
+    steps = []
+    for i in range(int(z["meta/steps"])):
+        s: Dict[str, object] = {k: torch.from_numpy(z[f"s{i}/{k}"].copy()) for k in ("actions", "rnd", "prnd")}
+        for phase in ("pre", "post"):
+            pre = f"s{i}/{phase}/"
+            s[phase] = {k[len(pre):]: torch.from_numpy(np.asarray(z[k]).copy()) for k in z.files if k.startswith(pre)}
+        steps.append(s)
+    return c, st, steps
