@@ -442,6 +442,168 @@ int ha_hand_reset_idx(const HaHandParams* p, const HaHandBuffers* b, const float
 int ha_hand_post_step(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream);
 int ha_hand_observe(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream);
 
+/* =====================================================================================================
+ * DeXtreme: AllegroHandDextremeADR (config 5) -- per-step tensor path of
+ * isaacgymenvs/tasks/dextreme/allegro_hand_dextreme.py (pre_physics_step :912-949, apply_actions :955-1015 with the ADR
+ * apply_action_noise_latency :1430-1441, reset_idx :775-858, reset_target_pose :709-733, apply_random_forces :1017-1030,
+ * post_physics_step :1033-1048, compute_observations :606-692 + :1443-1489, compute_poses_wrt_wrist :533-588,
+ * get_random_cube_observation :739-771, compute_hand_reward :1598-1663) and the dict-observation step tail of
+ * adr_vec_task.py:289-325.  The host side of ADR (apply_randomizations: Isaac Gym property DR, range update, per-env
+ * resampling) stays in Python; its per-env results are the adr_* / affine_* / action_latency / cube_pose_refresh_* inputs.
+ * ===================================================================================================== */
+#define HA_DEX_DOFS 16
+#define HA_DEX_TIPS 4
+#define HA_DEX_OBS_DIM 285          /* the 20 dict entries of get_num_obs_dict (:168-199), concatenated in declaration order */
+#define HA_DEX_MAX_QUEUE 64
+#define HA_DEX_N_STEP_TERMS 8       /* dist, rot, action, action_delta, velocity, reach_goal, fall, timeout (:455-464) */
+
+enum {   /* column offsets of the dict entries inside an observation row */
+  HA_DEX_OBS_DOF_POS = 0, HA_DEX_OBS_DOF_POS_RANDOMIZED = 16, HA_DEX_OBS_DOF_VEL = 32, HA_DEX_OBS_DOF_FORCE = 48,
+  HA_DEX_OBS_OBJECT_VELS = 64, HA_DEX_OBS_LAST_ACTIONS = 70, HA_DEX_OBS_CUBE_RANDOM_PARAMS = 86, HA_DEX_OBS_HAND_RANDOM_PARAMS = 89,
+  HA_DEX_OBS_GRAVITY_VEC = 90, HA_DEX_OBS_FT_STATES = 93, HA_DEX_OBS_FT_FORCE_TORQUES = 145, HA_DEX_OBS_RB_FORCES = 169,
+  HA_DEX_OBS_ROT_DIST = 172, HA_DEX_OBS_STOCHASTIC_DELAY_PARAMS = 174, HA_DEX_OBS_AFFINE_PARAMS = 178, HA_DEX_OBS_OBJECT_POSE = 256,
+  HA_DEX_OBS_GOAL_POSE = 263, HA_DEX_OBS_GOAL_RELATIVE_ROT = 270, HA_DEX_OBS_OBJECT_POSE_CAM_RANDOMIZED = 274,
+  HA_DEX_OBS_GOAL_RELATIVE_ROT_CAM_RANDOMIZED = 281
+};
+enum {   /* pre-step random table [n_envs, HA_DEX_RND_STRIDE]: U(0,1), N(0,1) in the *_WHITE / *_NORMAL slots */
+  HA_DEX_RND_GOAL = 0,          /* 4 rand_floats + 3 quaternion uniforms (goal-only reset_target_pose) */
+  HA_DEX_RND_RESET_GOAL = 7,    /* the same 7 for reset_target_pose inside reset_idx */
+  HA_DEX_RND_RESET = 14,        /* 2*16+5 rand_floats + 3 quaternion uniforms */
+  HA_DEX_RND_FORCE_PROB = 54,
+  HA_DEX_RND_PROGRESS = 55,     /* progress_buf of an all-env reset: floor(u * max_episode_length) (:848-849) */
+  HA_DEX_RND_ACTION_DELAY = 56,
+  HA_DEX_RND_ACTION_WHITE = 57, /* 16 normals */
+  HA_DEX_RND_FORCE_TEST = 73,
+  HA_DEX_RND_FORCE_NORMAL = 74, /* 3 normals */
+  HA_DEX_RND_STRIDE = 77
+};
+enum {   /* post-step random table [n_envs, HA_DEX_POST_RND_STRIDE] */
+  HA_DEX_POST_RND_POSE_WHITE = 0,   /* 7 normals */
+  HA_DEX_POST_RND_CUBE = 7,         /* 5 rand_floats */
+  HA_DEX_POST_RND_CUBE_QUAT = 12,   /* 3 uniforms */
+  HA_DEX_POST_RND_CUBE_MASK = 15,
+  HA_DEX_POST_RND_DELAY = 16,
+  HA_DEX_POST_RND_DOF_WHITE = 17,   /* 16 normals */
+  HA_DEX_POST_RND_STRIDE = 33
+};
+enum {   /* HaDexBuffers.dynamic: int64 [HA_DEX_DYN_LEN], device resident, advanced by the kernels */
+  HA_DEX_DYN_RNG_SEED = 0, HA_DEX_DYN_RNG_STEP, HA_DEX_DYN_FRAME /* self.frame */, HA_DEX_DYN_QUEUE_HEAD /* ring slot of the newest action */,
+  HA_DEX_DYN_N_APPLY /* envs with apply_reset_buf set when the last pre step ended */, HA_DEX_DYN_APPLY_ACC /* scratch of that count */,
+  HA_DEX_DYN_LEN = 8
+};
+
+typedef struct HaDexParams {
+  int32_t abi_version;
+  int32_t n_envs;
+  int32_t dofs_per_env;     /* row width of dof_state (>= 16) */
+  int32_t n_bodies;
+  int32_t palm_body;        /* palm_link (:390) */
+  int32_t tip_body[HA_DEX_TIPS];
+  int32_t object_body;
+  int32_t max_episode_length;
+  int32_t max_consecutive_successes;
+  int32_t num_success_hold_steps;
+  int32_t queue_len;        /* actionLatencyMax + 1 */
+  int32_t use_capped_dof_control;
+  int32_t apply_random_quat;
+  int32_t use_fast_rng;
+  int32_t force_enabled;
+  int32_t root_regular, actors_per_env, object_slot, goal_slot;
+  float dof_lower[HA_DEX_DOFS], dof_upper[HA_DEX_DOFS];
+  float dof_range_rcp[HA_DEX_DOFS];   /* filled by ha_dex_fill_derived() */
+  float clip_obs;           /* clipObservations (adr_vec_task.py:319); <= 0: none */
+  float vel_obs_scale, force_torque_obs_scale;
+  float dist_reward_scale, rot_reward_scale, rot_eps, action_penalty_scale, action_delta_penalty_scale, success_tolerance;
+  float reach_goal_bonus, fall_dist, fall_penalty, av_factor;
+  float act_moving_average, one_minus_act_moving_average;   /* annealed on the host (:896-909) */
+  float max_dof_delta;      /* max_dof_radians_per_second * dt * control_freq_inv */
+  float force_decay_pow, force_gain[2], force_log_c0, force_log_c1;
+  float reset_position_noise, reset_position_noise_z, reset_dof_pos_noise, reset_dof_vel_noise;
+  float goal_displacement[3];
+  float random_cube_pose_prob;
+} HaDexParams;
+
+typedef struct HaDexBuffers {
+  /* simulator-owned (Isaac Gym layout) */
+  float* root_state;                /* [n_envs*actors_per_env, 13] */
+  const float* rigid_body_state;    /* [n_envs, n_bodies, 13] */
+  float* dof_state;                 /* [n_envs, dofs_per_env, 2] */
+  const float* dof_force;           /* [n_envs, 16] */
+  const float* force_sensors;       /* [n_envs, 24] */
+  const int32_t* object_actor;      /* [n_envs] */
+  const int32_t* goal_actor;
+  const int32_t* hand_actor;
+  /* task constants */
+  const float* object_init_state;   /* [n_envs, 13] */
+  const float* goal_init_state;     /* [n_envs, 13] */
+  /* per-env ADR state sampled by apply_randomizations (:1392-1416) */
+  const int64_t* action_latency;            /* [n_envs], < queue_len */
+  const int64_t* cube_pose_refresh_rate;    /* [n_envs], >= 1 */
+  const int64_t* cube_pose_refresh_offset;  /* [n_envs] */
+  const float* adr_action_delay_prob;       /* [n_envs] each: get_adr_tensor(...) */
+  const float* adr_affine_action_white;
+  const float* adr_affine_cube_pose_white;
+  const float* adr_cube_obs_delay_prob;
+  const float* adr_affine_dof_pos_white;
+  const float* adr_rna_alpha;               /* nullable unless rna_perturbation is passed */
+  const float* affine_actions_scaling;      /* [n_envs, 16] */
+  const float* affine_actions_additive;
+  const float* affine_cube_pose_scaling;    /* [n_envs, 7] */
+  const float* affine_cube_pose_additive;
+  const float* affine_dof_pos_scaling;      /* [n_envs, 16] */
+  const float* affine_dof_pos_additive;
+  const float* cube_random_params;          /* [n_envs, 3] */
+  const float* hand_random_params;          /* [n_envs, 1] */
+  const float* gravity_vec;                 /* [n_envs, 3] */
+  /* task state */
+  float* goal_states;               /* [n_envs, 13] */
+  float* obs_rows;                  /* [n_envs, HA_DEX_OBS_DIM]: every dict entry, clipped to +-clip_obs */
+  float* rew_buf;
+  int64_t* reset_buf;
+  int64_t* reset_goal_buf;
+  int64_t* progress_buf;
+  int64_t* hold_count_buf;
+  int64_t* apply_reset_buf;
+  uint8_t* timeout_buf;
+  float* successes;
+  float* consecutive_successes;     /* [1] */
+  float* best_rotation_dist;        /* [n_envs] */
+  float* prev_targets;              /* [n_envs, 16] */
+  float* cur_targets;
+  float* prev_prev_targets;
+  float* actions;                   /* [n_envs, 16] task-owned copy */
+  float* prev_actions;              /* [n_envs, 16] */
+  float* action_queue;              /* [queue_len, n_envs, 16] ring buffer; slot (head - k) mod queue_len = the action of k steps ago */
+  float* dof_delta;                 /* [n_envs, 16] */
+  float* rb_forces;                 /* [n_envs, n_bodies, 3] */
+  float* random_force_prob;         /* [n_envs] */
+  float* object_pose;               /* [n_envs, 7]: the object pose gathered by the last compute_observations (:613) */
+  float* obs_object_pose;           /* [n_envs, 7] */
+  float* obs_object_pose_freq;      /* [n_envs, 7] */
+  float* episode_cumulative;        /* [HA_DEX_N_STEP_TERMS, n_envs] */
+  /* outputs for the simulator's *_indexed setters */
+  int32_t* root_reset_indices;      /* [2*n_envs] */
+  int32_t* hand_reset_indices;      /* [n_envs] */
+  int32_t* reset_counts;            /* [4]: n_root, n_hand, n_reset_envs, n_randomized */
+  /* reductions (HA_HAND_STAT_* layout) */
+  float* stats;
+  int64_t* stat_accum;
+  uint32_t* tickets;                /* [8], zero-initialised once */
+  int64_t* dynamic;                 /* [HA_DEX_DYN_LEN] */
+} HaDexBuffers;
+
+size_t ha_sizeof_dex_params(void);
+size_t ha_sizeof_dex_buffers(void);
+void ha_dex_fill_derived(HaDexParams* p);
+size_t ha_dex_post_bytes_per_env_step(const HaDexParams* p);
+size_t ha_dex_pre_bytes_per_env_step(const HaDexParams* p);
+size_t ha_dex_bytes_per_env_step(const HaDexParams* p);
+/* rna_perturbation: nullable [n_envs, 16], the RNA network's DOF-space perturbation (:864-879) computed by the caller */
+int ha_dex_pre_step(const HaDexParams* p, const HaDexBuffers* b, const float* actions, const float* rna_perturbation,
+                    const float* ext_rand, ha_stream_t stream);
+int ha_dex_post_step(const HaDexParams* p, const HaDexBuffers* b, const float* ext_rand_post, ha_stream_t stream);
+int ha_dex_observe(const HaDexParams* p, const HaDexBuffers* b, const float* ext_rand_post, ha_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

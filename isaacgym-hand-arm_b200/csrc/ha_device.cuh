@@ -186,4 +186,8 @@ __device__ __forceinline__ float key_float(long long k) {
   return __int_as_float(b >= 0 ? b : (b ^ 0x7fffffff));
 }
 
+// column descriptor of the observation-row assembly (hand and DeXtreme post kernels)
+enum { kOpCopy = 0, kOpScale = 1, kOpUnscale = 2 };
+struct HandCol { int base, stride, op; float a, b, c; };   // value(e) = stage[base + e * stride]; scale: * a; unscale: lo = a, hi = b, 1/(hi-lo) = c
+
 }  // namespace ha

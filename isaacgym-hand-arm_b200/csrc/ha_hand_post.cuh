@@ -22,11 +22,9 @@
 namespace ha {
 
 enum { kHandPostFull = 0, kHandPostObserveOnly = 1 };
-enum { kOpCopy = 0, kOpScale = 1, kOpUnscale = 2 };
 constexpr int kHandThreads = 128;
 constexpr int kHandTile = 32;
 
-struct HandCol { int base, stride, op; float a, b, c; };   // value(e) = stage[base + e * stride]; scale: * a; unscale: lo = a, hi = b, 1/(hi-lo) = c
 
 struct HandStageOfs {   // float offsets into the stage (contiguous images first: they are filled by 16-byte copies)
   int dof, frc, sens, act, obj, goal, tip, qd, total;

@@ -1,5 +1,6 @@
 """Task registry (subset of ``isaacgymenvs/tasks/__init__.py:66-123`` that lies on the hot path)."""
 from .allegro_kuka import AllegroKukaBase, AllegroKukaReorientation, AllegroKukaTwoArmsRegrasping
+from .dextreme import AllegroHandDextremeADR
 from .hand import AllegroHand, ShadowHand
 
 
@@ -23,4 +24,4 @@ def resolve_allegro_kuka_two_arms(cfg, *args, **kwargs):
 
 isaacgym_task_map = {"AllegroKukaTwoArms": resolve_allegro_kuka_two_arms, "AllegroKukaTwoArmsLSTM": resolve_allegro_kuka_two_arms,
                      "AllegroKuka": resolve_allegro_kuka, "AllegroKukaLSTM": resolve_allegro_kuka, "ShadowHand": ShadowHand,
-                     "AllegroHand": AllegroHand}
+                     "AllegroHand": AllegroHand, "AllegroHandDextremeADR": AllegroHandDextremeADR}
