@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--layout", default="both", choices=["both", "isaacgym", "soa"],
                     help="simulator state layout: component-major planes (HA_STATE_SOA, the north star's SoA state; headline), "
                          "Isaac Gym AoS rows, or both (default: headline on soa, the AoS numbers ride along)")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the short runs of configs 1, 2, 4 and 5 that ride along at N=1")
     ap.add_argument("--l2-fetch", type=int, default=0, help="cudaLimitMaxL2FetchGranularity in bytes (0 = leave the driver default)")
     return ap.parse_args()
 
@@ -172,6 +173,102 @@ def build_blocks(args, device, layout):
     return tasks, actions
 
 
+# ---- the other configs of BASELINE.json (1 ShadowHand, 2 AllegroHand, 4 two-arm regrasping, 5 DeXtreme ADR): short runs that ride
+# along with the headline at N=1, same method (CUDA graph over round-robin env blocks, device events, per-kernel graphs) ----
+OTHER_CONFIGS = {
+    "cfg1_shadow_hand": dict(task="ShadowHand", envs=4096, actions=20),
+    "cfg2_allegro_hand": dict(task="AllegroHand", envs=16384, actions=16),
+    "cfg4_two_arms_regrasping": dict(task="AllegroKukaTwoArmsLSTM", envs=8192, actions=46),
+    "cfg5_dextreme_adr": dict(task="AllegroHandDextremeADR", envs=16384, actions=16),
+}
+
+
+def build_other(key, device, blocks, snapshots):
+    import ctypes
+    import handarm_b200.config as hcfg
+    from handarm_b200 import sim as hsim
+    from handarm_b200.tasks import allegro_kuka, dextreme, hand
+    spec = OTHER_CONFIGS[key]
+    n = spec["envs"]
+    tasks, actions = [], []
+    for b in range(blocks):
+        seed = 4321 + b
+        if key == "cfg4_two_arms_regrasping":
+            cfg = hcfg.load_task_config(spec["task"], num_envs=n, sim_device=device, subtask="regrasping")
+            sim = hsim.SyntheticSim(n, hsim.KUKA2_LAYOUT, device, seed=seed, snapshots=snapshots)
+            task = allegro_kuka.AllegroKukaTwoArmsRegrasping(cfg, device, device, 0, True, sim=sim, seed=seed)
+            sim.fill_kuka(goal_states=None)
+        elif key == "cfg5_dextreme_adr":
+            cfg = hcfg.load_task_config(spec["task"], num_envs=n, sim_device=device)
+            sim = hsim.SyntheticSim(n, dextreme.DEXTREME_LAYOUT, device, seed=seed, snapshots=snapshots)
+            task = dextreme.AllegroHandDextremeADR(cfg, device, device, 0, True, sim=sim, seed=seed)      # create_sim fills the snapshots
+        else:
+            shadow = key == "cfg1_shadow_hand"
+            cfg = hcfg.load_task_config(spec["task"], num_envs=n, sim_device=device)
+            layout = hsim.SHADOW_HAND_LAYOUT if shadow else hsim.ALLEGRO_HAND_LAYOUT
+            sim = hsim.SyntheticSim(n, layout, device, seed=seed, snapshots=snapshots)
+            task = (hand.ShadowHand if shadow else hand.AllegroHand)(cfg, device, device, 0, True, sim=sim, seed=seed)
+            sim.fill_hand(task.object_init_state[0, 0:3].tolist(), task.goal_states, task.dof_lower, task.dof_upper)
+        task.seed_rng(seed)
+        sim.record_calls = False
+        gen = torch.Generator().manual_seed(77 + b)
+        actions.append((2.0 * torch.rand(n, spec["actions"], generator=gen) - 1.0).to(device))
+        tasks.append(task)
+    t0 = tasks[0]
+    fam = "dex" if key == "cfg5_dextreme_adr" else ("kuka" if key == "cfg4_two_arms_regrasping" else "hand")
+    post_b = int(getattr(t0._lib, f"ha_{fam}_post_bytes_per_env_step")(ctypes.byref(t0._params)))
+    pre_b = int(getattr(t0._lib, f"ha_{fam}_pre_bytes_per_env_step")(ctypes.byref(t0._params)))
+    return tasks, actions, post_b, pre_b
+
+
+def measure_other(key, device, steps, blocks=4, snapshots=2):
+    hbm_gbs, _ = peaks()
+    tasks, actions, post_b, pre_b = build_other(key, device, blocks, snapshots)
+    n = OTHER_CONFIGS[key]["envs"]
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        for t, a in zip(tasks, actions):
+            for _ in range(3):
+                one_step(t, a)
+        stream.synchronize()
+        for t in tasks:
+            if hasattr(t, "frame_since_restart"):
+                t.frame_since_restart, t.last_curriculum_update = 0, 0
+
+        def graph_of(which):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream):
+                for _ in range(snapshots):
+                    for t, a in zip(tasks, actions):
+                        if which in ("step", "pre"):
+                            t.pre_physics_step(a)
+                        if which in ("step", "post"):
+                            t.sim.simulate()
+                            t.post_physics_step()
+            return g
+
+        per_graph = blocks * snapshots
+
+        def time_graph(g, reps):
+            for _ in range(3):
+                g.replay()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(stream)
+            for _ in range(reps):
+                g.replay()
+            a1.record(stream)
+            stream.synchronize()
+            return a0.elapsed_time(a1) * 1e3 / (reps * per_graph)
+
+        reps = max(4, steps // per_graph)
+        step_us = time_graph(graph_of("step"), reps)
+        post_us = time_graph(graph_of("post"), reps)
+        pre_us = time_graph(graph_of("pre"), reps)
+    return {"envs_per_gpu": n, "value": n / (step_us * 1e-6), "unit": UNIT, "ms_per_step": step_us * 1e-3, "steps": reps * per_graph,
+            "bytes_per_env": post_b + pre_b, "step_frac": n * (post_b + pre_b) / (step_us * 1e-6) / 1e9 / hbm_gbs,
+            "post_kernel_us": post_us, "post_frac": n * post_b / (post_us * 1e-6) / 1e9 / hbm_gbs, "pre_kernel_us": pre_us}
+
+
 def one_step(task, act):
     task.pre_physics_step(act)
     task.sim.simulate()
@@ -206,6 +303,13 @@ def run_ours(args):
             line["isaacgym_layout"]["roofline"] = {k: other["roofline"][k] for k in ("achieved", "frac", "kernel_us", "pre_kernel_us", "step_frac")}
             line["isaacgym_layout"]["note"] = ("same kernels on Isaac Gym's AoS tensors (root [N*A,13], rigid-body [N*B,13]): every 52-byte row "
                                                "costs whole 128-byte DRAM lines, 1.43 KB fetched per env for 0.61 KB used")
+    if rank == 0 and world == 1 and not args.no_other_configs:
+        import gc
+        line["other_configs"] = {}
+        for key in OTHER_CONFIGS:
+            gc.collect()
+            torch.cuda.empty_cache()
+            line["other_configs"][key] = measure_other(key, device, min(args.steps, 800))
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -190,4 +190,32 @@ __device__ __forceinline__ float key_float(long long k) {
 enum { kOpCopy = 0, kOpScale = 1, kOpUnscale = 2 };
 struct HandCol { int base, stride, op; float a, b, c; };   // value(e) = stage[base + e * stride]; scale: * a; unscale: lo = a, hi = b, 1/(hi-lo) = c
 
+// Row assembly, warp per env row: lane l owns columns l, l + 32, ... and keeps their descriptors in registers, so one row costs
+// ceil(W / 32) shared loads, ops and 128-byte coalesced stores per warp.  `rank` / `nwarps`: this warp's index among the warps taking part.
+template <int MAX_PER_LANE>
+__device__ __forceinline__ void assemble_rows(const float* stage, const HandCol* cols, float* __restrict__ out, const int W, const int nvalid,
+                                              const float clip, const int lane, const int rank, const int nwarps) {
+  HandCol c[MAX_PER_LANE];
+#pragma unroll
+  for (int k = 0; k < MAX_PER_LANE; ++k) {
+    const int j = lane + 32 * k;
+    c[k] = (j < W) ? cols[j] : HandCol{0, 0, kOpCopy, 0.f, 0.f, 0.f};
+  }
+  const bool do_clip = clip > 0.0f;
+  for (int e = rank; e < nvalid; e += nwarps) {
+    float* row = out + (size_t)e * W;
+#pragma unroll
+    for (int k = 0; k < MAX_PER_LANE; ++k) {
+      const int j = lane + 32 * k;
+      if (j < W) {
+        float v = stage[c[k].base + e * c[k].stride];
+        if (c[k].op == kOpScale) v = c[k].a * v;
+        else if (c[k].op == kOpUnscale) v = div_by_const(2.0f * v - c[k].b - c[k].a, c[k].b - c[k].a, c[k].c);   // torch_jit_utils.py:238-240
+        if (do_clip) v = fminf(fmaxf(v, -clip), clip);
+        row[j] = v;
+      }
+    }
+  }
+}
+
 }  // namespace ha

@@ -95,39 +95,6 @@ __device__ inline HandCol dex_col(const HaDexParams& p, const DexStageOfs& o, in
   return cmp(kCmpCamRel + k);
 }
 
-// hand_assemble on a subset of the CTA's threads (rank r of nthr)
-__device__ __forceinline__ void dex_assemble(const float* stage, const HandCol* cols, float* __restrict__ out, const int W, const int nvalid,
-                                             const float clip, const int r, const int nthr) {
-  const bool do_clip = clip > 0.0f;
-  const int total = nvalid * W, nvec = total >> 2;
-  const float inv_w = 1.0f / (float)W;
-  auto value = [&](int e, int j) {
-    const HandCol c = cols[j];
-    float v = stage[c.base + e * c.stride];
-    if (c.op == kOpScale) v = c.a * v;
-    else if (c.op == kOpUnscale) v = div_by_const(2.0f * v - c.b - c.a, c.b - c.a, c.c);
-    if (do_clip) v = fminf(fmaxf(v, -clip), clip);
-    return v;
-  };
-  for (int q = r; q < nvec; q += nthr) {
-    const int idx = 4 * q;
-    int e = (int)(((float)idx + 0.5f) * inv_w);
-    int j = idx - e * W;
-    float v[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      v[k] = value(e, j);
-      if (++j == W) { j = 0; ++e; }
-    }
-    reinterpret_cast<float4*>(out)[q] = make_float4(v[0], v[1], v[2], v[3]);
-  }
-  const int f = (nvec << 2) + r;
-  if (f < total) {
-    const int e = f / W;
-    out[f] = value(e, f - e * W);
-  }
-}
-
 __global__ void __launch_bounds__(kDexThreads)
 dex_post_kernel(const __grid_constant__ HaDexParams p, const __grid_constant__ HaDexBuffers b, const float* __restrict__ ext_rand, const int mode) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -296,7 +263,8 @@ dex_post_kernel(const __grid_constant__ HaDexParams p, const __grid_constant__ H
   // ---------------- assemble (warps 0, 2, 3) ----------------
   if (warp != 1) {
     const int r = (warp == 0) ? lane : tid - 32;                                // ranks 0..95
-    dex_assemble(stage, cols, b.obs_rows + (size_t)env0 * HA_DEX_OBS_DIM, HA_DEX_OBS_DIM, nvalid, p.clip_obs, r, kDexThreads - 32);
+    assemble_rows<(HA_DEX_OBS_DIM + 31) / 32>(stage, cols, b.obs_rows + (size_t)env0 * HA_DEX_OBS_DIM, HA_DEX_OBS_DIM, nvalid, p.clip_obs, lane,
+                                              warp == 0 ? 0 : warp - 1, 3);
     for (int j = r; j < nvalid * 7; j += kDexThreads - 32) {                    // the two pose latches
       b.obs_object_pose_freq[(size_t)env0 * 7 + j] = stage[o.freq + j];
       b.obs_object_pose[(size_t)env0 * 7 + j] = stage[o.cam + j];

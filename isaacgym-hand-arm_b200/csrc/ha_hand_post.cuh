@@ -13,8 +13,8 @@
 //   reward    warp 0, lane = env: quaternion difference (also an observation), compute_hand_reward, per-env
 //             stores, statistics partials; the global consecutive_successes average is finished by the last CTA
 //             from integer accumulators (order-independent);
-//   assemble  all threads walk the 32 x W tile flat (4 consecutive elements per thread), apply the column op
-//             and the +-clipObservations clip and write 128-bit coalesced stores straight to obs_buf.
+//   assemble  warp per env row, lane = column (mod 32) with the column descriptors in registers: apply the column op
+//             and the +-clipObservations clip and write 128-byte coalesced row segments straight to obs_buf.
 #pragma once
 #include "ha_device.cuh"
 #include "../../include/handarm_b200.h"
@@ -94,39 +94,6 @@ __device__ inline HandCol hand_col(const HaHandParams& p, const HandStageOfs& o,
     }
   }
   return copy(o.act + k, A);
-}
-
-// Write one [nvalid, W] tile of an observation-like buffer from the stage (all threads).
-__device__ __forceinline__ void hand_assemble(const float* stage, const HandCol* cols, float* __restrict__ out, const int W,
-                                              const int nvalid, const float clip, const int tid) {
-  const bool do_clip = clip > 0.0f;
-  const int total = nvalid * W, nvec = total >> 2;
-  const float inv_w = 1.0f / (float)W;
-  auto value = [&](int e, int j) {
-    const HandCol c = cols[j];
-    float v = stage[c.base + e * c.stride];
-    if (c.op == kOpScale) v = c.a * v;
-    else if (c.op == kOpUnscale) v = div_by_const(2.0f * v - c.b - c.a, c.b - c.a, c.c);   // unscale (torch_jit_utils.py:238-240)
-    if (do_clip) v = fminf(fmaxf(v, -clip), clip);
-    return v;
-  };
-  for (int q = tid; q < nvec; q += kHandThreads) {
-    const int idx = 4 * q;
-    int e = (int)(((float)idx + 0.5f) * inv_w);
-    int j = idx - e * W;
-    float v[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      v[k] = value(e, j);
-      if (++j == W) { j = 0; ++e; }
-    }
-    reinterpret_cast<float4*>(out)[q] = make_float4(v[0], v[1], v[2], v[3]);
-  }
-  const int f = (nvec << 2) + tid;                    // ragged last tile: up to 3 trailing floats
-  if (f < total) {
-    const int e = f / W;
-    out[f] = value(e, f - e * W);
-  }
 }
 
 __global__ void __launch_bounds__(kHandThreads)
@@ -259,8 +226,10 @@ hand_post_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__
   __syncthreads();                                                       // quat_diff is in the stage
 
   // ---------------- assemble ----------------
-  hand_assemble(stage, cols_obs, b.obs_buf + (size_t)env0 * p.obs_dim, p.obs_dim, nvalid, p.clip_obs, tid);
-  if (has_states) hand_assemble(stage, cols_st, b.states_buf + (size_t)env0 * p.states_dim, p.states_dim, nvalid, p.clip_obs, tid);
+  constexpr int kMaxPerLane = (HA_HAND_MAX_OBS + 31) / 32;
+  assemble_rows<kMaxPerLane>(stage, cols_obs, b.obs_buf + (size_t)env0 * p.obs_dim, p.obs_dim, nvalid, p.clip_obs, lane, warp, kHandThreads / 32);
+  if (has_states)
+    assemble_rows<kMaxPerLane>(stage, cols_st, b.states_buf + (size_t)env0 * p.states_dim, p.states_dim, nvalid, p.clip_obs, lane, warp, kHandThreads / 32);
 
   // ---------------- statistics + the global consecutive_successes average (warp 0) ----------------
   if (warp != 0 || mode != kHandPostFull) return;

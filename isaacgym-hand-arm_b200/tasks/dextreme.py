@@ -448,7 +448,7 @@ class AllegroHandDextremeADR(VecTask):
         self._require_engine()
         self._rebind_sim_state()
         _lib.check(self._lib.ha_dex_post_step(ctypes.byref(self._params), ctypes.byref(self._buffers), self._rand_ptrs()[1], self._stream()))
-        self.extras["consecutive_successes"] = self.consecutive_successes.mean()
+        self.extras["consecutive_successes"] = self.consecutive_successes[0]      # mean of the [1] tensor: a 0-dim view, no launch
         self.extras["true_objective"] = self.successes
         self.extras["episode_cumulative"] = {k: self._episode_cumulative[i] for i, k in enumerate(REWARD_KEYS)}
 

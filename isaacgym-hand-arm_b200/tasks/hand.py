@@ -311,7 +311,7 @@ class _HandTask(VecTask):
         self._require_engine()
         self._rebind_sim_state()
         _lib.check(self._lib.ha_hand_post_step(ctypes.byref(self._params), ctypes.byref(self._buffers), self._stream()))
-        self.extras["consecutive_successes"] = self.consecutive_successes.mean()
+        self.extras["consecutive_successes"] = self.consecutive_successes[0]      # mean of the [1] tensor: a 0-dim view, no launch
 
     def compute_observations(self):
         """compute_observations only (VecTask.reset())."""
