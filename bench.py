@@ -120,11 +120,12 @@ def cpu_port_rate(n_envs: int, steps: int, warmup: int = 2):
     st = ks.make_state(n_envs, seed=1, c=c, fresh=False)
     acts = [ks.make_actions(n_envs, s) for s in range(2)]
     rnds = [ks.make_rnd(n_envs, s) for s in range(2)]
-    if steps <= 0:
+    if steps <= 0:            # bounded sample: about 15 s of CPU work
+        ko.pre_step(st, c, acts[0], rnds[0]); ko.post_step(st, c)          # first call pays allocator / thread-pool start-up
         t0 = time.perf_counter()
-        ko.pre_step(st, c, acts[0], rnds[0]); ko.post_step(st, c)
+        ko.pre_step(st, c, acts[1], rnds[1]); ko.post_step(st, c)
         one = time.perf_counter() - t0
-        steps = max(3, min(200, int(12.0 / max(one, 1e-3))))
+        steps = max(3, min(2000, int(15.0 / max(one, 1e-3))))
     for i in range(warmup):
         ko.pre_step(st, c, acts[i % 2], rnds[i % 2]); ko.post_step(st, c)
     t0 = time.perf_counter()
@@ -317,6 +318,15 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def ncu_traffic(layout):
+    """dram__bytes_read.sum + dram__bytes_write.sum per K_post launch from the committed ncu --set full capture (profiles/traffic.json)."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")
+    try:
+        return json.load(open(path))["kuka_post_kernel"][layout]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def measure(args, layout, device, rank, world, local, headline=True):
     import torch.distributed as dist
     hbm_gbs, peak_src = peaks()
@@ -483,8 +493,8 @@ def measure(args, layout, device, rank, world, local, headline=True):
             "config": {"workload": WORKLOAD, "envs_per_gpu": N, "state_layout": layout, "env_blocks": B, "snapshots_per_block": S,
                        "l2": f"inputs larger than L2: {B} env blocks stepped round-robin, {B}x{N * (post_bytes + pre_bytes) / 1e6:.0f} MB "
                              "algorithmic bytes per round", "launch": f"CUDA graph of {per_graph} steps", "rng": "in-kernel Philox"},
-            "roofline": {"bound": "hbm", "kernel": "kuka_post_kernel<4>", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
-                         "frac": achieved / hbm_gbs, "traffic": None, "peak_source": peak_src, "kernel_us": post_avg,
+            "roofline": {"bound": "hbm", "kernel": f"kuka_post_kernel<K=4, SOA={int(layout == 'soa')}, NS=2>", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
+                         "frac": achieved / hbm_gbs, "traffic": ncu_traffic(layout), "peak_source": peak_src, "kernel_us": post_avg,
                          "bytes_per_env": post_bytes, "pre_kernel_us": pre_avg, "pre_bytes_per_env": pre_bytes,
                          "step_frac": step_frac, "kernel_timing": "CUDA events around graph replays of only-post / only-pre launches"},
             "value_l2_warm": warm_value,

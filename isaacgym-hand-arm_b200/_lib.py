@@ -16,7 +16,7 @@ from typing import Dict, List, Tuple
 _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 _REPO_DIR = os.path.dirname(_PKG_DIR)
 HEADER_PATH = os.path.join(_REPO_DIR, "include", "handarm_b200.h")
-LIB_PATH = os.path.join(_PKG_DIR, "libhandarm_b200.so")
+LIB_PATH = os.environ.get("HANDARM_B200_LIB") or os.path.join(_PKG_DIR, "libhandarm_b200.so")   # env: tuning hook for A/B builds
 
 
 class HandArmLibraryError(RuntimeError):

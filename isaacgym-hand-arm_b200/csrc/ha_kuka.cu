@@ -77,7 +77,10 @@ int post_grid_limit(int blocks_per_sm) {
   return override_grid > 0 ? override_grid : sm_count * blocks_per_sm;
 }
 
-constexpr int kPostNS = 2;   // cp.async stages per CTA (1: seven single-tile CTAs per SM; 2: four double-buffered CTAs)
+#ifndef HA_POST_NS
+#define HA_POST_NS 2
+#endif
+constexpr int kPostNS = HA_POST_NS;   // cp.async stages per CTA (1: seven single-tile CTAs per SM; 2: four double-buffered CTAs)
 
 template <int K, bool SOA>
 int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {

@@ -28,6 +28,23 @@
 #include "ha_device.cuh"
 #include "../../include/handarm_b200.h"
 
+// tuning switches (A/B builds): which transfers of K_post go through the bulk-copy engine (cp.async.bulk, SASS UBLKCP).
+// Measured on B200, 32768 envs, component planes (K_post us): none 13.4 | store 13.9 | images + store 13.8 | rows + images + store 15.0.
+// 128-byte rows are too small for the copy engine (57 descriptors per tile against 8 LDGSTS per thread), and a bulk store needs the
+// +-clamp moved from the store loop into the role warps, which lengthens the per-tile critical path by more than the store saves.
+#ifndef HA_BULK_ROWS
+#define HA_BULK_ROWS 0      // the 54 component-plane rows of a tile (128 bytes each)
+#endif
+#ifndef HA_BULK_IMAGES
+#define HA_BULK_IMAGES 0    // the contiguous keypoint / scale / DOF images
+#endif
+#ifndef HA_BULK_STORE
+#define HA_BULK_STORE 0     // the finished [32, OBS] observation tile
+#endif
+#ifndef HA_POST_NS1_CTAS
+#define HA_POST_NS1_CTAS 7   // resident single-stage CTAs per SM the register allocation is sized for
+#endif
+
 namespace ha {
 
 struct KukaLayout {            // obs slot offsets, allegro_kuka_base.py:1091-1172
@@ -95,7 +112,12 @@ struct KukaPostSmem {
   KukaPostStage<K> st[NS];
   float obs[kTile * kObs];            // row-major tile, leaves as one contiguous run
   float xch[8 * kTile];               // [q][e]: cur[0..3], kp_max, sum|vel| arm, sum|vel| hand
+  unsigned long long mbar[2];         // transaction barriers of the bulk-copied stages
 };
+// a tile whose inputs arrive by bulk copies: component planes, full tile, 16-byte aligned plane rows
+__device__ __forceinline__ bool kuka_post_bulk_tile(bool soa, int n_envs, int env0) {
+  return (HA_BULK_ROWS || HA_BULK_IMAGES) && soa && (n_envs & 3) == 0 && n_envs - env0 >= kTile;
+}
 static_assert(sizeof(KukaPostStage<4>) % 16 == 0 && sizeof(KukaPostStage<1>) % 16 == 0, "stage must keep 16-byte alignment");
 static_assert((kTile * 13 * 2 + kTile * 29 + kTile * 7) % 4 == 0, "kp image must be 16-byte aligned inside the stage");
 
@@ -174,9 +196,10 @@ __device__ __forceinline__ void kuka_post_stats(const HaKukaBuffers& b, const Ku
 // Issue the cp.async copies of one tile (all 128 threads).  Idle envs of a ragged last tile re-read the last valid env.
 template <int K, bool SOA>
 __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaKukaBuffers& b, KukaPostStage<K>& s, const int env0,
-                                                const int nvalid, const int tid) {
+                                                const int nvalid, const int tid, unsigned long long* bar) {
   using S = KukaPostStage<K>;
   const int last = nvalid - 1;
+  const bool bulk = kuka_post_bulk_tile(SOA, p.n_envs, env0);
   const size_t rbs = (size_t)p.n_bodies * 13;
   const float* rb0 = b.rigid_body_state + (size_t)env0 * rbs;
   if constexpr (SOA) {
@@ -191,7 +214,16 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
       return b.rigid_body_state + ((size_t)p.tip_body[t] * 13 + c) * n + env0;
     };
     auto row_dst = [&](int r) -> float* { return r < 13 ? s.palm + r * kTile : r < 26 ? s.obj + (r - 13) * kTile : s.tip + (r - 26) * kTile; };
-    if (nvalid == kTile && (p.n_envs & 3) == 0) {       // plane rows are 16-byte aligned: 8 x 16-byte copies per row
+    if (bulk) {
+      constexpr unsigned kBytes = (HA_BULK_ROWS ? kRows * kTile * 4 : 0) + (HA_BULK_IMAGES ? kTile * 3 * K * 4 + kTile * 3 * 4 + kTile * 2 * kD1 * 4 : 0);
+      if (tid == 0) mbar_arrive_expect_tx(bar, kBytes);
+    }
+    if (bulk && HA_BULK_ROWS) {                         // one 128-byte bulk copy per plane row, issued by the first warp
+      if (tid < 32) {
+        bulk_g2s(row_dst(tid), row_src(tid), kTile * 4, bar);
+        if (tid + 32 < kRows) bulk_g2s(row_dst(tid + 32), row_src(tid + 32), kTile * 4, bar);
+      }
+    } else if (nvalid == kTile && (p.n_envs & 3) == 0) {       // plane rows are 16-byte aligned: 8 x 16-byte copies per row
 #pragma unroll
       for (int i = 0; i < (kRows * 8 + kPostThreads - 1) / kPostThreads; ++i) {
         const int q = tid + kPostThreads * i;
@@ -251,7 +283,11 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
   const float* kp_src = b.object_keypoint_offsets + (size_t)env0 * 3 * K;
   const float* sc_src = b.object_scales + (size_t)env0 * 3;
   const float* dof_src = b.dof_state + (size_t)env0 * (2 * kD1);
-  if (nvalid == kTile) {   // contiguous tiles: 16-byte copies (tile bases are 16-byte aligned: env0 % 32 == 0)
+  if (bulk && HA_BULK_IMAGES) {   // the three contiguous images: one bulk copy each
+    if (tid == 32) bulk_g2s(s.kp, kp_src, kTile * 3 * K * 4, bar);
+    if (tid == 33) bulk_g2s(s.scales, sc_src, kTile * 3 * 4, bar);
+    if (tid == 34) bulk_g2s(s.dof, dof_src, kTile * 2 * kD1 * 4, bar);
+  } else if (nvalid == kTile) {   // contiguous tiles: 16-byte copies (tile bases are 16-byte aligned: env0 % 32 == 0)
     constexpr int kKpVec = kTile * 3 * K / 4, kScVec = kTile * 3 / 4, kDofVec = kTile * 2 * kD1 / 4;
     if (tid < kKpVec) cp_async16(reinterpret_cast<float4*>(s.kp) + tid, reinterpret_cast<const float4*>(kp_src) + tid);
     if (tid >= kPostThreads - kScVec) {
@@ -307,7 +343,7 @@ __device__ __forceinline__ void kuka_post_load_env(const HaKukaParams& p, const 
 }
 
 template <int K, bool SOA, int NS>
-__global__ void __launch_bounds__(kPostThreads, NS == 1 ? 7 : 4)
+__global__ void __launch_bounds__(kPostThreads, NS == 1 ? HA_POST_NS1_CTAS : 4)
 kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b, const int mode) {
   using SM = KukaPostSmem<K, NS>;
   using ST = KukaPostStage<K>;
@@ -333,8 +369,12 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     tobj_offset = b.dynamic->true_objective_offset;
   }
   KukaPostAcc acc;
+  if constexpr (SOA && (HA_BULK_ROWS || HA_BULK_IMAGES)) {
+    if (tid == 0) { mbar_init(&sm.mbar[0], 1); mbar_init(&sm.mbar[1], 1); mbar_fence_init(); }
+    __syncthreads();
+  }
 
-  if (tile < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[0], tile * kTile, min(kTile, n - tile * kTile), tid);
+  if (tile < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[0], tile * kTile, min(kTile, n - tile * kTile), tid, &sm.mbar[0]);
   cp_async_commit();
 
   for (int it = 0; tile < n_tiles; ++it, tile += stride) {
@@ -345,15 +385,20 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     const int env = env0 + min(lane, nvalid - 1);       // idle lanes of a ragged tile re-read a valid env; stores are predicated
     const int next = tile + stride;
     if constexpr (NS == 2) {   // next tile's copies go in flight before this tile is touched
-      if (next < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid);
+      if (next < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid, &sm.mbar[(it + 1) & 1]);
       cp_async_commit();
     }
     KukaPostEnvState r;
     if (warp == 3) kuka_post_load_env<OBS, L.reward>(p, b, env, mode, r);
+    if (HA_BULK_STORE && tid == 0) bulk_wait_read0();   // the previous tile's bulk store has read the obs tile
     cp_async_wait<NS - 1>();
+    if (kuka_post_bulk_tile(SOA, n, env0)) mbar_wait(&sm.mbar[NS == 2 ? (it & 1) : 0], NS == 2 ? (it >> 1) & 1 : it & 1);
     __syncthreads();                                    // B1: this tile's inputs are in shared memory
 
     float* o = sm.obs + lane * OBS;
+    const float clamp_c = p.clamp_abs_obs;                // clamp_obs (:1174-1176) / vec_task.py:432, applied where a value is produced
+    const bool do_clamp = clamp_c > 0.0f;
+    auto W = [&](int i, float v) { o[i] = (HA_BULK_STORE && do_clamp) ? fminf(fmaxf(v, -clamp_c), clamp_c) : v; };   // else: clamped by the store loop
     float obj_z = 0.f;
     // staged rows: [e][13] / [e][29] images of the AoS rows, or component-major [c][32] planes (SOA)
     auto PALM = [&](int c) { return SOA ? S.palm[c * kTile + lane] : S.palm[lane * 13 + c]; };
@@ -363,16 +408,16 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       // palm_center_pos = palm_pos + quat_rotate(palm_rot, palm_offset)   (:1013-1017); fingertips (:1033-1052)
       const f3 pc = f3{PALM(0), PALM(1), PALM(2)} + quat_rotate(f4{PALM(3), PALM(4), PALM(5), PALM(6)}, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
       const f3 obj_pos = {OBJ(0), OBJ(1), OBJ(2)};
-      o[L.palm_pos + 0] = pc.x; o[L.palm_pos + 1] = pc.y; o[L.palm_pos + 2] = pc.z;
+      W(L.palm_pos + 0, pc.x); W(L.palm_pos + 1, pc.y); W(L.palm_pos + 2, pc.z);
 #pragma unroll
       for (int t = 0; t < kT1; ++t) {
         const f3 to = f3{TIP(t, 0), TIP(t, 1), TIP(t, 2)} +
                       quat_rotate(f4{TIP(t, 3), TIP(t, 4), TIP(t, 5), TIP(t, 6)}, f3{p.tip_offset[t][0], p.tip_offset[t][1], p.tip_offset[t][2]});
         const f3 rel_obj = to - obj_pos, rel_palm = to - pc;
         sm.xch[t * kTile + lane] = norm3(rel_obj);
-        o[L.tip_rel_palm + 3 * t + 0] = rel_palm.x;
-        o[L.tip_rel_palm + 3 * t + 1] = rel_palm.y;
-        o[L.tip_rel_palm + 3 * t + 2] = rel_palm.z;
+        W(L.tip_rel_palm + 3 * t + 0, rel_palm.x);
+        W(L.tip_rel_palm + 3 * t + 1, rel_palm.y);
+        W(L.tip_rel_palm + 3 * t + 2, rel_palm.z);
       }
     } else if (warp == 1) {
       // keypoints (:1057-1073)
@@ -398,12 +443,12 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
         const f3 rel_goal = okp - gkp, rel_palm = okp - pc;
         const float dist = norm3(rel_goal);
         kp_max = (k == 0) ? dist : fmaxf(kp_max, dist);
-        o[L.kp_rel_palm + 3 * k + 0] = rel_palm.x;
-        o[L.kp_rel_palm + 3 * k + 1] = rel_palm.y;
-        o[L.kp_rel_palm + 3 * k + 2] = rel_palm.z;
-        o[L.kp_rel_goal + 3 * k + 0] = rel_goal.x;
-        o[L.kp_rel_goal + 3 * k + 1] = rel_goal.y;
-        o[L.kp_rel_goal + 3 * k + 2] = rel_goal.z;
+        W(L.kp_rel_palm + 3 * k + 0, rel_palm.x);
+        W(L.kp_rel_palm + 3 * k + 1, rel_palm.y);
+        W(L.kp_rel_palm + 3 * k + 2, rel_palm.z);
+        W(L.kp_rel_goal + 3 * k + 0, rel_goal.x);
+        W(L.kp_rel_goal + 3 * k + 1, rel_goal.y);
+        W(L.kp_rel_goal + 3 * k + 2, rel_goal.z);
       }
       sm.xch[4 * kTile + lane] = kp_max;
     } else if (warp == 2) {
@@ -414,8 +459,8 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       for (int d = 0; d < kD1; ++d) {
         const float2 pv = dl[d];
         const float lo = p.dof_lower[d], hi = p.dof_upper[d];
-        o[L.dof_pos + d] = div_by_const(2.0f * pv.x - hi - lo, hi - lo, p.dof_range_rcp[d]);
-        o[L.dof_vel + d] = pv.y;
+        W(L.dof_pos + d, div_by_const(2.0f * pv.x - hi - lo, hi - lo, p.dof_range_rcp[d]));
+        W(L.dof_vel + d, pv.y);
         if (d < 7) sa += fabsf(pv.y); else sh += fabsf(pv.y);
       }
       sm.xch[5 * kTile + lane] = sa;
@@ -424,9 +469,9 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       // palm rot + vel (:1112-1117), object rot + vel (:1120), object scales (:1143)
       obj_z = OBJ(2);
 #pragma unroll
-      for (int c = 0; c < 10; ++c) { o[L.palm_rot_vel + c] = PALM(3 + c); o[L.obj_rot_vel + c] = OBJ(3 + c); }
+      for (int c = 0; c < 10; ++c) { W(L.palm_rot_vel + c, PALM(3 + c)); W(L.obj_rot_vel + c, OBJ(3 + c)); }
 #pragma unroll
-      for (int c = 0; c < 3; ++c) o[L.scales + c] = S.scales[lane * 3 + c];
+      for (int c = 0; c < 3; ++c) W(L.scales + c, S.scales[lane * 3 + c]);
     }
     __syncthreads();                                    // B2: distances, kp_max and |vel| sums are visible to warp 3
 
@@ -444,14 +489,14 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       float ckp = (r.ckp < 0.0f) ? kp_max : r.ckp;
       const long long progress = r.progress + (mode == kPostFull ? 1 : 0);   // progress_buf += 1 (:1429)
       // observation slots that see pre-update state (ordering: SURVEY 8a)
-      o[L.closest_kp] = ckp;
+      W(L.closest_kp, ckp);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) o[L.closest_tip + i] = ctip[i];
-      o[L.lifted] = r.lifted ? 1.0f : 0.0f;
-      o[L.progress] = logf((float)progress / 10.0f + 1.0f);
-      o[L.successes] = logf(r.succ + 1.0f);
+      for (int i = 0; i < 4; ++i) W(L.closest_tip + i, ctip[i]);
+      W(L.lifted, r.lifted ? 1.0f : 0.0f);
+      W(L.progress, logf((float)progress / 10.0f + 1.0f));
+      W(L.successes, logf(r.succ + 1.0f));
       if (mode == kPostObserveOnly) {
-        o[L.reward] = r.old_rew_obs;
+        W(L.reward, r.old_rew_obs);
         if (valid) {
           b.closest_keypoint_max_dist[env] = ckp;
           b.furthest_hand_dist[env] = furthest;
@@ -516,7 +561,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
         }
         const float true_obj = succ * tobj_scale + tobj_offset;
         const bool timeout_flag = timed_out && (resets != 0);          // vec_task.py:424
-        o[L.reward] = reward * 0.01f;                                  // (:1437-1439)
+        W(L.reward, reward * 0.01f);                                  // (:1437-1439)
         if (valid) {
           // per-env outputs (lane = env: coalesced)
           b.rew_buf[env] = reward;
@@ -550,16 +595,23 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
         }
       }
     }
+    const bool bulk_store = HA_BULK_STORE && (nvalid == kTile);   // 14976 contiguous bytes, 16-byte aligned on both sides
+    if (bulk_store) fence_proxy_async_smem();           // the tile's generic-proxy writes, before the async proxy reads them
     __syncthreads();                                    // B3: the observation tile is complete
-    // on its last tile the state warp goes straight to the statistics (fence + atomics round trips) while the
-    // other three warps store the tile
+    // on its last tile the state warp goes straight to the statistics (fence + atomics round trips)
     const bool stats_now = (next >= n_tiles) && (mode == kPostFull);
-    if (stats_now && warp == 3) {
+    if (bulk_store) {
+      if (tid == 0) {                                   // the whole [32, OBS] tile leaves as one bulk copy
+        bulk_s2g(b.obs_buf + (size_t)env0 * OBS, sm.obs, kTile * OBS * 4);
+        bulk_commit();
+      }
+      if (stats_now && warp == 3) kuka_post_stats(b, acc, lane);
+    } else if (stats_now && warp == 3) {
       kuka_post_stats(b, acc, lane);
     } else {
-      // obs tile: clamp (:1174-1176 clamp_obs, vec_task.py:432 clip) and store as one contiguous run
-      const float c = p.clamp_abs_obs;
-      const bool do_clamp = c > 0.0f;
+      // obs tile: clamp (unless the roles already did) and store as one contiguous run of 128-bit words
+      const bool clamp_here = do_clamp && !HA_BULK_STORE;
+      const float c = clamp_c;
       float4* dst = reinterpret_cast<float4*>(b.obs_buf + (size_t)env0 * OBS);   // 16-byte aligned: env0 % 32 == 0
       const float4* src = reinterpret_cast<const float4*>(sm.obs);
       const int total = nvalid * OBS, nvec = total >> 2;
@@ -567,7 +619,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
 #pragma unroll 2
       for (int q = sid; q < nvec; q += nst) {
         float4 v = src[q];
-        if (do_clamp) {
+        if (clamp_here) {
           v.x = fminf(fmaxf(v.x, -c), c); v.y = fminf(fmaxf(v.y, -c), c);
           v.z = fminf(fmaxf(v.z, -c), c); v.w = fminf(fmaxf(v.w, -c), c);
         }
@@ -576,19 +628,20 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       const int f = (nvec << 2) + sid;                  // ragged last tile: up to 3 trailing floats
       if (f < total) {
         float v = sm.obs[f];
-        if (do_clamp) v = fminf(fmaxf(v, -c), c);
+        if (clamp_here) v = fminf(fmaxf(v, -c), c);
         b.obs_buf[(size_t)env0 * OBS + f] = v;
       }
     }
     if constexpr (NS == 1) {
       if (next < n_tiles) {
         __syncthreads();                                // every warp is done with the stage and the obs tile
-        kuka_post_issue<K, SOA>(p, b, sm.st[0], next * kTile, min(kTile, n - next * kTile), tid);
+        kuka_post_issue<K, SOA>(p, b, sm.st[0], next * kTile, min(kTile, n - next * kTile), tid, &sm.mbar[0]);
       }
       cp_async_commit();
     }
   }
   cp_async_wait<0>();
+  if (HA_BULK_STORE && tid == 0) bulk_wait_read0();     // shared memory must outlive the last bulk store's reads
   if (blockIdx.x >= n_tiles && warp == 3 && mode == kPostFull) kuka_post_stats(b, acc, lane);   // CTA without a tile still owes its ticket
 }
 
