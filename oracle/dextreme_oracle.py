@@ -413,3 +413,89 @@ def post_step(st: Dict[str, Tensor], c: DexConsts, prnd: Tensor) -> None:
     st["prev_targets"][:, :D] = st["cur_targets"][:, :D]
     st["timeout_buf"] = (st["progress_buf"] >= c.max_episode_length - 1) & (st["reset_buf"] != 0)
     st["obs_out"] = torch.clamp(st["obs_rows"], -c.clip_obs, c.clip_obs)
+
+
+# ---------------------------------------------------------------------------------------------
+# per-env ADR resampling on reset (the tensor half of apply_randomizations)
+# ---------------------------------------------------------------------------------------------
+# Tensorised ADR parameters of cfg/task/AllegroHandDextremeADR.yaml in declaration order, with their index among ALL adr params
+# (13 physics parameters patched into Isaac Gym's DR ranges come first) -- adr_modes counts over all of them.
+ADR_TENSOR_KEYS = ["cube_obs_delay_prob", "cube_pose_refresh_rate", "action_delay_prob", "action_latency", "affine_action_scaling",
+                   "affine_action_additive", "affine_action_white", "affine_cube_pose_scaling", "affine_cube_pose_additive",
+                   "affine_cube_pose_white", "affine_dof_pos_scaling", "affine_dof_pos_additive", "affine_dof_pos_white", "rna_alpha"]
+ADR_N_BUILTIN = 13
+ADR_N_PARAMS = ADR_N_BUILTIN + len(ADR_TENSOR_KEYS)
+# random table of the resampling [n_envs, ARND_STRIDE]
+ARND_WORKER = 0        # worker type draw
+ARND_MODE = 1          # stands in for torch.randint(0, 2 * n_params): floor(u * 2 * n_params)
+ARND_PARAM = 2         # one uniform per tensorised parameter (16 slots reserved)
+ARND_LATENCY = 18
+ARND_RATE = 19
+ARND_OFFSET = 20
+ARND_AFFINE = 21       # 16 + 16 + 7 + 7 + 16 + 16 normals
+ARND_STRIDE = 99
+ADR_ROLLOUT, ADR_BOUNDARY = 0, 1
+
+
+@dataclasses.dataclass
+class AdrTable:
+    """Current ADR ranges (host state of adr_update) of the tensorised parameters."""
+    ranges: Dict[str, Tuple[float, float]]
+    next_limits: Dict[str, Tuple[float, float]]
+    boundary_fraction: float = 0.4
+    extended_boundary_sample: bool = False
+
+
+def default_adr_table(widen: float = 0.0) -> AdrTable:
+    """init_range of the YAML (``widen`` > 0 opens every range a little so that all branches produce distinct values)."""
+    init = {"cube_obs_delay_prob": (0.0, 0.05), "cube_pose_refresh_rate": (1.0, 1.0), "action_delay_prob": (0.0, 0.05),
+            "action_latency": (0.0, 0.0), "affine_action_scaling": (0.0, 0.0), "affine_action_additive": (0.0, 0.04),
+            "affine_action_white": (0.0, 0.04), "affine_cube_pose_scaling": (0.0, 0.0), "affine_cube_pose_additive": (0.0, 0.04),
+            "affine_cube_pose_white": (0.0, 0.04), "affine_dof_pos_scaling": (0.0, 0.0), "affine_dof_pos_additive": (0.0, 0.04),
+            "affine_dof_pos_white": (0.0, 0.04), "rna_alpha": (0.0, 0.0)}
+    if widen > 0.0:
+        init = {k: (lo, hi + widen * (10.0 if k in ("cube_pose_refresh_rate", "action_latency") else 1.0)) for k, (lo, hi) in init.items()}
+    nxt = {k: (max(lo - 0.01, 0.0), hi + 0.01) for k, (lo, hi) in init.items()}
+    return AdrTable(ranges=init, next_limits=nxt)
+
+
+def adr_resample(st: Dict[str, Tensor], c: DexConsts, table: AdrTable, mask: Tensor, arnd: Tensor) -> None:
+    """recycle_envs (adr_vec_task.py:740-758) + sample_adr_tensor of every tensorised parameter (:666-730, as the tail of adr_update
+    :915-917 calls it) + the Dextreme-specific resampling of allegro_hand_dextreme.py:1392-1416, for the envs in ``mask``."""
+    ids = mask.nonzero(as_tuple=False).squeeze(-1)
+    if len(ids) == 0:
+        return
+    D = c.n_dofs
+    # recycle_envs
+    new_types = torch.zeros(len(ids), dtype=torch.long)
+    r = arnd[ids, ARND_WORKER]
+    new_types[r < table.boundary_fraction] = ADR_ROLLOUT
+    new_types[r >= table.boundary_fraction] = ADR_BOUNDARY
+    st["worker_types"][ids] = new_types
+    st["adr_modes"][ids] = torch.clamp((arnd[ids, ARND_MODE] * (2 * ADR_N_PARAMS)).long(), max=2 * ADR_N_PARAMS - 1)
+    # sample_adr_tensor
+    sample_mask = torch.zeros(mask.shape[0], dtype=torch.bool)
+    sample_mask[ids] = True
+    for t, name in enumerate(ADR_TENSOR_KEYS):
+        n = ADR_N_BUILTIN + t
+        lo, hi = table.ranges[name]
+        nlo, nhi = table.next_limits[name]
+        low = (st["worker_types"] == ADR_BOUNDARY) & (st["adr_modes"] == 2 * n) & sample_mask
+        high = (st["worker_types"] == ADR_BOUNDARY) & (st["adr_modes"] == 2 * n + 1) & sample_mask
+        rollout = (~low) & (~high) & sample_mask
+        result = torch.zeros(len(ids), dtype=torch.float32)
+        result[rollout[ids]] = arnd[rollout, ARND_PARAM + t] * (hi - lo) + lo
+        result[low[ids]] = nlo if table.extended_boundary_sample else lo
+        result[high[ids]] = nhi if table.extended_boundary_sample else hi
+        st["adr_" + name][ids] = result
+    # allegro_hand_dextreme.py:1398-1416
+    st["action_latency"][ids] = (st["adr_action_latency"][ids] + (-(arnd[ids, ARND_LATENCY] - 0.5))).round().long()
+    st["cube_pose_refresh_rate"][ids] = (st["adr_cube_pose_refresh_rate"][ids] + (-(arnd[ids, ARND_RATE] - 0.5))).round().long()
+    st["cube_pose_refresh_offset"][mask] = (arnd[ids, ARND_OFFSET] * st["cube_pose_refresh_rate"][ids].view(-1).float() - 0.5).round().long()
+    o = ARND_AFFINE
+    for key, adr, dim, one in (("affine_actions_scaling", "affine_action_scaling", D, 1.), ("affine_actions_additive", "affine_action_additive", D, 0.),
+                               ("affine_cube_pose_scaling", "affine_cube_pose_scaling", 7, 1.), ("affine_cube_pose_additive", "affine_cube_pose_additive", 7, 0.),
+                               ("affine_dof_pos_scaling", "affine_dof_pos_scaling", D, 1.), ("affine_dof_pos_additive", "affine_dof_pos_additive", D, 0.)):
+        noise = arnd[ids, o:o + dim] * gaussian_stdev(st["adr_" + adr][ids])
+        st[key][ids] = (1. + noise) if one else noise
+        o += dim

@@ -10,7 +10,7 @@ from typing import Dict
 
 import torch
 
-from .dextreme_oracle import (ADR_KEYS, OBS_DIM, PRND_CUBE_MASK, PRND_DELAY, PRND_DOF_WHITE, PRND_POSE_WHITE, PRND_STRIDE, RND_ACTION_WHITE,
+from .dextreme_oracle import (ADR_KEYS, ADR_N_PARAMS, ADR_TENSOR_KEYS, ARND_AFFINE, ARND_STRIDE, OBS_DIM, PRND_CUBE_MASK, PRND_DELAY, PRND_DOF_WHITE, PRND_POSE_WHITE, PRND_STRIDE, RND_ACTION_WHITE,
                               RND_FORCE_NORMAL, RND_STRIDE, DexConsts)
 from .hand_state import ALLEGRO_LOWER, ALLEGRO_UPPER, _unit_quat
 
@@ -75,6 +75,11 @@ def make_state(n: int, seed: int, c: DexConsts, fresh: int = 0, actors: int = 3)
         v[U(n) < 0.2] = 0.0                              # the v > 0 gate of sample_gaussian_adr
         st["adr_" + k] = v
     st["adr_rna_alpha"] = 0.5 * U(n)
+    for k in ADR_TENSOR_KEYS:                            # the remaining tensorised ADR parameters (only resampling reads them)
+        if "adr_" + k not in st:
+            st["adr_" + k] = 0.2 * U(n)
+    st["worker_types"] = (U(n) < 0.6).long()
+    st["adr_modes"] = torch.randint(0, 2 * ADR_N_PARAMS, (n,), generator=gen)
     st["affine_actions_scaling"] = 1.0 + 0.05 * G(n, D)
     st["affine_actions_additive"] = 0.05 * G(n, D)
     st["affine_cube_pose_scaling"] = 1.0 + 0.05 * G(n, 7)
@@ -163,4 +168,12 @@ def make_prnd(n: int, seed: int, c: DexConsts) -> torch.Tensor:
     rnd = torch.rand(n, PRND_STRIDE, generator=gen)
     rnd[:, PRND_POSE_WHITE:PRND_POSE_WHITE + 7] = torch.randn(n, 7, generator=gen)
     rnd[:, PRND_DOF_WHITE:PRND_DOF_WHITE + c.n_dofs] = torch.randn(n, c.n_dofs, generator=gen)
+    return rnd.contiguous()
+
+
+def make_arnd(n: int, seed: int, c: DexConsts) -> torch.Tensor:
+    """ADR-resampling table [n, ARND_STRIDE]: uniforms, N(0,1) in the affine slots."""
+    gen = torch.Generator().manual_seed(seed + 15485863)
+    rnd = torch.rand(n, ARND_STRIDE, generator=gen)
+    rnd[:, ARND_AFFINE:] = torch.randn(n, ARND_STRIDE - ARND_AFFINE, generator=gen)
     return rnd.contiguous()

@@ -241,12 +241,13 @@ def scripted_randoms(queue: List[torch.Tensor]):
     for key in patched:
         saved[key] = mods[key].torch_rand_float
         mods[key].torch_rand_float = fake_rand_float
-    old_rand, old_randn = torch.rand, torch.randn
+    old_rand, old_randn, old_rand_like = torch.rand, torch.randn, torch.rand_like
     torch.rand, torch.randn = fake_rand, fake_rand
+    torch.rand_like = lambda t, **kw: pop(t.shape)
     try:
         yield q
     finally:
-        torch.rand, torch.randn = old_rand, old_randn
+        torch.rand, torch.randn, torch.rand_like = old_rand, old_randn, old_rand_like
         for key in patched:
             mods[key].torch_rand_float = saved[key]
 
@@ -648,3 +649,63 @@ def harvest_dextreme(env, st: Dict[str, torch.Tensor], c) -> Dict[str, torch.Ten
     out["obs_rows"] = torch.cat([env.obs_dict[k] for k, _ in dx.OBS_KEYS], dim=-1)
     out["obs_out"] = torch.clamp(out["obs_rows"], -c.clip_obs, c.clip_obs)
     return out
+
+
+ADR_BUILTIN_KEYS = ["hand_damping", "hand_stiffness", "hand_joint_friction", "hand_armature", "hand_effort", "hand_lower", "hand_upper",
+                    "hand_mass", "hand_friction_fingertips", "hand_restitution", "object_mass", "object_friction", "object_restitution"]
+
+
+def attach_reference_adr(env, st: Dict[str, torch.Tensor], table) -> None:
+    """ADRVecTask state (adr_vec_task.py:489-560) for ``recycle_envs`` / ``sample_adr_tensor`` / the Dextreme resampling."""
+    from . import dextreme_oracle as dx
+    params = {k: {"range": [0.5, 2.0], "range_path": "x", "delta": 0.01} for k in ADR_BUILTIN_KEYS}
+    for k in dx.ADR_TENSOR_KEYS:
+        params[k] = {"range": list(table.ranges[k]), "next_limits": list(table.next_limits[k]), "delta": 0.01}
+    env.adr_params = params
+    env.adr_params_keys = list(params.keys())
+    env.num_adr_params = len(params)
+    assert env.num_adr_params == dx.ADR_N_PARAMS
+    env.adr_extended_boundary_sample = table.extended_boundary_sample
+    env.worker_adr_boundary_fraction = table.boundary_fraction
+    env.worker_types, env.adr_modes = st["worker_types"], st["adr_modes"]
+    env.adr_tensor_values = {k: st["adr_" + k] for k in dx.ADR_TENSOR_KEYS}
+    env.__dict__.pop("apply_randomizations", None)           # the class method (with the patched super) is what runs
+
+
+def reference_adr_resample(env, c, table, mask: torch.Tensor, arnd: torch.Tensor, st: Dict[str, torch.Tensor]) -> None:
+    """Runs the reference's ``recycle_envs`` + ``sample_adr_tensor`` (as the tail of ``adr_update`` does) and then
+    ``AllegroHandDextremeADR.apply_randomizations``' own resampling (:1396-1416); only the Isaac Gym half of
+    ``ADRVecTask.apply_randomizations`` is replaced."""
+    from . import dextreme_oracle as dx
+    mods = load_reference()
+    ids = mask.nonzero(as_tuple=False).squeeze(-1)
+    P = dx.ADR_N_PARAMS
+    types = torch.where(arnd[ids, dx.ARND_WORKER] < table.boundary_fraction, 0, 1)
+    modes = torch.clamp((arnd[ids, dx.ARND_MODE] * (2 * P)).long(), max=2 * P - 1)
+    q: List[torch.Tensor] = [arnd[ids, dx.ARND_WORKER]]
+    for t, _ in enumerate(dx.ADR_TENSOR_KEYS):
+        n = dx.ADR_N_BUILTIN + t
+        boundary = (types == 1) & ((modes == 2 * n) | (modes == 2 * n + 1))
+        q.append(arnd[ids[~boundary], dx.ARND_PARAM + t])
+    q += [arnd[ids, dx.ARND_LATENCY], arnd[ids, dx.ARND_RATE], arnd[ids, dx.ARND_OFFSET]]
+    o = dx.ARND_AFFINE
+    for dim in (c.n_dofs, c.n_dofs, 7, 7, c.n_dofs, c.n_dofs):
+        q.append(arnd[ids, o:o + dim])
+        o += dim
+
+    def tensor_half(self, dr_params, randomize_buf, adr_objective=None, randomisation_callback=None):
+        rows = torch.nonzero(randomize_buf, as_tuple=False).squeeze(-1)
+        self.recycle_envs(rows)
+        for k in self.adr_tensor_values:
+            self.sample_adr_tensor(k, rows)
+
+    cls = mods["adrv"].ADRVecTask
+    saved, old_randint = cls.apply_randomizations, torch.randint
+    cls.apply_randomizations = tensor_half
+    torch.randint = lambda *a, **k: modes.clone()
+    try:
+        with scripted_randoms(q) as rest:
+            type(env).apply_randomizations(env, {}, mask)
+            assert len(rest) == 0, f"{len(rest)} scripted random tensors were not consumed (adr)"
+    finally:
+        cls.apply_randomizations, torch.randint = saved, old_randint

@@ -54,3 +54,32 @@ def test_dextreme_restatement_is_bit_exact(n, fresh):
 def test_dextreme_variants():
     run(130, 3, dx.DexConsts(use_capped_dof_control=True, apply_random_quat=False, num_success_hold_steps=1, fall_penalty=-50.0,
                              force_scale=0.0, act_moving_average=0.15), 0)
+
+
+ADR_OUT = ["worker_types", "adr_modes", "action_latency", "cube_pose_refresh_rate", "cube_pose_refresh_offset", "affine_actions_scaling",
+           "affine_actions_additive", "affine_cube_pose_scaling", "affine_cube_pose_additive", "affine_dof_pos_scaling",
+           "affine_dof_pos_additive"] + ["adr_" + k for k in dx.ADR_TENSOR_KEYS]
+
+
+@pytest.mark.parametrize("extended", [False, True])
+@pytest.mark.parametrize("which", ["pending", "all"])
+def test_adr_resampling_is_bit_exact(which, extended):
+    """recycle_envs + sample_adr_tensor + the Dextreme resampling of apply_randomizations against the reference's own methods."""
+    c, n = dx.DexConsts(), 400
+    st = ds.make_state(n, 77, c, fresh=0)
+    st["reset_buf"] = (torch.rand(n, generator=torch.Generator().manual_seed(5)) < 0.5).long()
+    st["apply_reset_buf"] = st["apply_reset_buf"] * st["reset_buf"]
+    ref_st = copy.deepcopy(st)
+    table = dx.default_adr_table(widen=0.3)
+    table.extended_boundary_sample = extended
+    mask = torch.ones(n, dtype=torch.bool) if which == "all" else (st["reset_buf"] & ~st["apply_reset_buf"]).bool()
+    assert 50 < int(mask.sum())
+    arnd = ds.make_arnd(n, 77, c)
+    env = rl.make_reference_dextreme(ref_st, c)
+    rl.attach_reference_adr(env, ref_st, table)
+    rl.reference_adr_resample(env, c, table, mask, arnd, ref_st)
+    dx.adr_resample(st, c, table, mask, arnd)
+    for k in ADR_OUT:
+        assert torch.equal(st[k], ref_st[k]), f"{k}: max |d| = {(st[k].double() - ref_st[k].double()).abs().max().item():.3e}"
+    boundary = (st["worker_types"][mask] == 1)
+    assert 0.3 < boundary.float().mean() < 0.9       # both worker kinds were drawn
