@@ -536,22 +536,22 @@ typedef struct HaDexBuffers {
   /* task constants */
   const float* object_init_state;   /* [n_envs, 13] */
   const float* goal_init_state;     /* [n_envs, 13] */
-  /* per-env ADR state sampled by apply_randomizations (:1392-1416) */
-  const int64_t* action_latency;            /* [n_envs], < queue_len */
-  const int64_t* cube_pose_refresh_rate;    /* [n_envs], >= 1 */
-  const int64_t* cube_pose_refresh_offset;  /* [n_envs] */
+  /* per-env ADR state sampled by apply_randomizations (:1392-1416): read by the step kernels, written by ha_dex_adr_resample */
+  int64_t* action_latency;            /* [n_envs], < queue_len */
+  int64_t* cube_pose_refresh_rate;    /* [n_envs], >= 1 */
+  int64_t* cube_pose_refresh_offset;  /* [n_envs] */
   const float* adr_action_delay_prob;       /* [n_envs] each: get_adr_tensor(...) */
   const float* adr_affine_action_white;
   const float* adr_affine_cube_pose_white;
   const float* adr_cube_obs_delay_prob;
   const float* adr_affine_dof_pos_white;
   const float* adr_rna_alpha;               /* nullable unless rna_perturbation is passed */
-  const float* affine_actions_scaling;      /* [n_envs, 16] */
-  const float* affine_actions_additive;
-  const float* affine_cube_pose_scaling;    /* [n_envs, 7] */
-  const float* affine_cube_pose_additive;
-  const float* affine_dof_pos_scaling;      /* [n_envs, 16] */
-  const float* affine_dof_pos_additive;
+  float* affine_actions_scaling;      /* [n_envs, 16] */
+  float* affine_actions_additive;
+  float* affine_cube_pose_scaling;    /* [n_envs, 7] */
+  float* affine_cube_pose_additive;
+  float* affine_dof_pos_scaling;      /* [n_envs, 16] */
+  float* affine_dof_pos_additive;
   const float* cube_random_params;          /* [n_envs, 3] */
   const float* hand_random_params;          /* [n_envs, 1] */
   const float* gravity_vec;                 /* [n_envs, 3] */
@@ -591,6 +591,45 @@ typedef struct HaDexBuffers {
   uint32_t* tickets;                /* [8], zero-initialised once */
   int64_t* dynamic;                 /* [HA_DEX_DYN_LEN] */
 } HaDexBuffers;
+
+/* ---- per-env ADR resampling on reset: recycle_envs (adr_vec_task.py:740-758), sample_adr_tensor (:666-730) for every tensorised
+ * parameter, and the Dextreme-specific draws of allegro_hand_dextreme.py:1392-1416, for the envs in reset_buf & ~apply_reset_buf (the
+ * mask pre_physics_step hands to apply_randomizations, :930-937).  Launch it BEFORE ha_dex_pre_step of the same step.  The ADR range
+ * update itself (adr_update: host deques, thresholds) stays on the host and only refreshes this table. ---- */
+#define HA_DEX_ADR_MAX_PARAMS 16
+enum {
+  HA_DEX_ADR_RND_WORKER = 0,
+  HA_DEX_ADR_RND_MODE = 1,       /* adr_modes: floor(u * 2 * n_params_total) */
+  HA_DEX_ADR_RND_PARAM = 2,      /* one uniform per tensorised parameter */
+  HA_DEX_ADR_RND_LATENCY = 18,
+  HA_DEX_ADR_RND_RATE = 19,
+  HA_DEX_ADR_RND_OFFSET = 20,
+  HA_DEX_ADR_RND_AFFINE = 21,    /* 16 + 16 + 7 + 7 + 16 + 16 normals */
+  HA_DEX_ADR_RND_STRIDE = 99
+};
+typedef struct HaDexAdrTable {
+  int32_t n_params_total;                       /* num_adr_params: adr_modes ranges over 2 * n_params_total */
+  int32_t n_tensor;                             /* tensorised parameters (<= HA_DEX_ADR_MAX_PARAMS), in adr_tensor_values order */
+  int32_t param_index[HA_DEX_ADR_MAX_PARAMS];   /* index of each among all ADR parameters */
+  float lo[HA_DEX_ADR_MAX_PARAMS];
+  float span[HA_DEX_ADR_MAX_PARAMS];            /* float(hi - lo), the difference taken in double like the reference's Python floats */
+  float low_value[HA_DEX_ADR_MAX_PARAMS];       /* what a boundary worker evaluating the lower end gets: range[0], or next_limits[0] */
+  float high_value[HA_DEX_ADR_MAX_PARAMS];
+  float boundary_fraction;                      /* worker_adr_boundary_fraction */
+  int32_t idx_action_latency;                   /* positions (0 .. n_tensor-1) of the parameters the Dextreme draws read */
+  int32_t idx_cube_pose_refresh_rate;
+  int32_t idx_affine[6];                        /* action scaling / additive, cube pose scaling / additive, dof pos scaling / additive */
+  int32_t all_envs;                             /* first_randomization: every env is resampled */
+} HaDexAdrTable;
+typedef struct HaDexAdrBuffers {
+  float* values[HA_DEX_ADR_MAX_PARAMS];         /* adr_tensor_values[k], [n_envs] each */
+  int64_t* worker_types;                        /* [n_envs] RolloutWorkerModes */
+  int64_t* adr_modes;                           /* [n_envs] */
+} HaDexAdrBuffers;
+size_t ha_sizeof_dex_adr_table(void);
+size_t ha_sizeof_dex_adr_buffers(void);
+int ha_dex_adr_resample(const HaDexParams* p, const HaDexBuffers* b, const HaDexAdrTable* t, const HaDexAdrBuffers* ab, const float* ext_rand,
+                        ha_stream_t stream);
 
 size_t ha_sizeof_dex_params(void);
 size_t ha_sizeof_dex_buffers(void);

@@ -112,6 +112,8 @@ HaHandBuffers = STRUCTS["HaHandBuffers"]
 HaHandDynamic = STRUCTS["HaHandDynamic"]
 HaDexParams = STRUCTS["HaDexParams"]
 HaDexBuffers = STRUCTS["HaDexBuffers"]
+HaDexAdrTable = STRUCTS["HaDexAdrTable"]
+HaDexAdrBuffers = STRUCTS["HaDexAdrBuffers"]
 
 _lib = None
 
@@ -170,15 +172,17 @@ def load():
     for fn in ("ha_hand_bytes_per_env_step", "ha_hand_post_bytes_per_env_step", "ha_hand_pre_bytes_per_env_step"):
         getattr(lib, fn).argtypes = [ctypes.c_void_p]
     # DeXtreme family
-    for fn in ("ha_sizeof_dex_params", "ha_sizeof_dex_buffers", "ha_dex_bytes_per_env_step", "ha_dex_post_bytes_per_env_step",
+    for fn in ("ha_sizeof_dex_params", "ha_sizeof_dex_buffers", "ha_sizeof_dex_adr_table", "ha_sizeof_dex_adr_buffers", "ha_dex_bytes_per_env_step", "ha_dex_post_bytes_per_env_step",
                "ha_dex_pre_bytes_per_env_step"):
         getattr(lib, fn).restype = ctypes.c_size_t
-    for cls, fn in ((HaDexParams, lib.ha_sizeof_dex_params), (HaDexBuffers, lib.ha_sizeof_dex_buffers)):
+    for cls, fn in ((HaDexParams, lib.ha_sizeof_dex_params), (HaDexBuffers, lib.ha_sizeof_dex_buffers),
+                    (HaDexAdrTable, lib.ha_sizeof_dex_adr_table), (HaDexAdrBuffers, lib.ha_sizeof_dex_adr_buffers)):
         if ctypes.sizeof(cls) != fn():
             raise HandArmLibraryError(f"struct {cls.__name__}: ctypes size {ctypes.sizeof(cls)} != C size {fn()}")
     lib.ha_dex_pre_step.argtypes = [ctypes.c_void_p] * 6
     lib.ha_dex_post_step.argtypes = [ctypes.c_void_p] * 4
     lib.ha_dex_observe.argtypes = [ctypes.c_void_p] * 4
+    lib.ha_dex_adr_resample.argtypes = [ctypes.c_void_p] * 6
     lib.ha_dex_fill_derived.argtypes = [ctypes.c_void_p]
     lib.ha_dex_fill_derived.restype = None
     for fn in ("ha_dex_bytes_per_env_step", "ha_dex_post_bytes_per_env_step", "ha_dex_pre_bytes_per_env_step"):

@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/handarm_b200.h"
+#include "ha_dex_adr.cuh"
 #include "ha_dex_post.cuh"
 #include "ha_dex_pre.cuh"
 #include "ha_host.h"
@@ -73,6 +74,28 @@ extern "C" {
 
 size_t ha_sizeof_dex_params(void) { return sizeof(HaDexParams); }
 size_t ha_sizeof_dex_buffers(void) { return sizeof(HaDexBuffers); }
+size_t ha_sizeof_dex_adr_table(void) { return sizeof(HaDexAdrTable); }
+size_t ha_sizeof_dex_adr_buffers(void) { return sizeof(HaDexAdrBuffers); }
+
+int ha_dex_adr_resample(const HaDexParams* p, const HaDexBuffers* b, const HaDexAdrTable* t, const HaDexAdrBuffers* ab, const float* ext_rand,
+                        ha_stream_t stream) {
+  int rc = validate_dex(p, b);
+  if (rc) return rc;
+  HA_REQUIRE(t != nullptr && ab != nullptr, "null ADR table / buffers");
+  HA_REQUIRE(t->n_tensor >= 0 && t->n_tensor <= HA_DEX_ADR_MAX_PARAMS, "n_tensor %d out of range", t->n_tensor);
+  HA_REQUIRE(t->n_params_total >= t->n_tensor && t->n_params_total > 0, "n_params_total %d < n_tensor %d", t->n_params_total, t->n_tensor);
+  for (int k = 0; k < t->n_tensor; ++k) {
+    HA_REQUIRE(ab->values[k] != nullptr, "HaDexAdrBuffers.values[%d] is null", k);
+    HA_REQUIRE(t->param_index[k] >= 0 && t->param_index[k] < t->n_params_total, "param_index[%d] out of range", k);
+  }
+  HA_REQUIRE(ab->worker_types != nullptr && ab->adr_modes != nullptr, "worker_types / adr_modes is null");
+  HA_REQUIRE(t->idx_action_latency >= 0 && t->idx_action_latency < t->n_tensor && t->idx_cube_pose_refresh_rate >= 0 &&
+                 t->idx_cube_pose_refresh_rate < t->n_tensor, "action_latency / cube_pose_refresh_rate positions out of range");
+  for (int a = 0; a < 6; ++a) HA_REQUIRE(t->idx_affine[a] >= 0 && t->idx_affine[a] < t->n_tensor, "idx_affine[%d] out of range", a);
+  HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
+  const int grid = (p->n_envs + ha::kDexThreads - 1) / ha::kDexThreads;
+  return ha::check_cuda(ha::launch(ha::dex_adr_kernel, grid, ha::kDexThreads, 0, (cudaStream_t)stream, *p, *b, *t, *ab, ext_rand), "dex_adr_kernel launch");
+}
 
 void ha_dex_fill_derived(HaDexParams* p) {
   if (!p) return;

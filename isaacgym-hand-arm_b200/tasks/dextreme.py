@@ -12,9 +12,11 @@ Layout choices (B200-first):
 * the action queue (``prev_actions_queue`` ``[N, L, 16]`` shifted every step, ``:969``) is a slot-major ring buffer
   ``[L, N, 16]``; ``prev_actions_queue`` is offered as a read-only reconstruction for callers that want the reference view.
 
-Host-side ADR (``ADRVecTask.apply_randomizations``: Isaac Gym property randomisation, range update, per-env resampling) is control
-logic outside the kernels: the per-env ADR tensors / affine parameters it samples are plain attributes here (initialised from the
-YAML ``init_range``), and ``apply_randomizations`` is a hook a caller may assign.
+ADR: the per-env half of ``apply_randomizations`` -- ``recycle_envs``, ``sample_adr_tensor`` for every tensorised parameter and the
+Dextreme draws (action latency, cube-pose refresh rate / offset, six affine tensors; ``:1392-1416``) -- is one more kernel
+(``ha_dex_adr_resample``), launched ahead of K_pre on the envs in ``reset_buf & ~apply_reset_buf`` without reading the mask back.
+The range update (``adr_update``: host deques and thresholds) and the Isaac Gym property randomisation are host control logic
+outside the path: ``adr_params[name]["range"]`` is plain host state a caller updates, ``refresh_adr_table()`` pushes it.
 """
 from __future__ import annotations
 
@@ -33,6 +35,8 @@ DEXTREME_LAYOUT = ActorLayout(actors_per_env=3, bodies_per_env=19, dofs_per_env=
                               palm_body=(0,), tip_body=(4, 8, 12, 16), object_body=17)
 REWARD_KEYS = ["dist_rew", "rot_rew", "action_penalty", "action_delta_penalty", "velocity_penalty", "reach_goal_rew", "fall_rew", "timeout_rew"]
 ADR_HOT_KEYS = ["action_delay_prob", "affine_action_white", "affine_cube_pose_white", "cube_obs_delay_prob", "affine_dof_pos_white", "rna_alpha"]
+AFFINE_ADR_KEYS = ["affine_action_scaling", "affine_action_additive", "affine_cube_pose_scaling", "affine_cube_pose_additive",
+                   "affine_dof_pos_scaling", "affine_dof_pos_additive"]
 
 
 class AllegroHandDextremeADR(VecTask):
@@ -56,6 +60,17 @@ class AllegroHandDextremeADR(VecTask):
         adr = cfg["task"].get("adr", {})
         self.use_adr = bool(adr.get("use_adr", False))
         self.adr_params = adr.get("params", {})
+        self.worker_adr_boundary_fraction = adr.get("worker_adr_boundary_fraction", 0.4)
+        self.adr_extended_boundary_sample = bool(adr.get("adr_extended_boundary_sample", False))
+        for k, prm in self.adr_params.items():                               # adr_vec_task.py:530-545
+            prm["range"] = list(prm["init_range"])
+            prm.setdefault("limits", [None, None])
+            if prm.get("type", "uniform") != "uniform":
+                raise NotImplementedError(f"ADR parameter {k}: only uniform tensorised parameters are built")
+        self.adr_params_keys = list(self.adr_params.keys())
+        self.adr_tensor_keys = [k for k in self.adr_params_keys if "range_path" not in self.adr_params[k]]
+        self.num_adr_params = len(self.adr_params)
+        self.first_randomization = True
         super().__init__(cfg, rl_device, sim_device, graphics_device_id, headless, virtual_screen_capture, force_render)
         self.dt = self.sim_params_dt
         if self.reset_time > 0.0:
@@ -185,7 +200,11 @@ class AllegroHandDextremeADR(VecTask):
         self.affine_cube_pose_additive = torch.zeros(N, 7, **f)
         self.affine_dof_pos_scaling = torch.ones(N, 16, **f)
         self.affine_dof_pos_additive = torch.zeros(N, 16, **f)
-        self.adr_tensor_values: Dict[str, torch.Tensor] = {k: self._adr_init(k, gen) for k in ADR_HOT_KEYS}
+        keys = list(dict.fromkeys(self.adr_tensor_keys + ADR_HOT_KEYS))
+        self.adr_tensor_values: Dict[str, torch.Tensor] = {k: self._adr_init(k, gen) for k in keys}
+        self.worker_types = torch.zeros(N, **i64)
+        self.adr_modes = torch.zeros(N, **i64)
+        self.ext_rand_adr: Optional[torch.Tensor] = None               # parity mode: [N, HA_DEX_ADR_RND_STRIDE] raw draws
         self.all_env_ids = torch.arange(N, **i64)
         self.prev_targets = torch.zeros((N, 16), **f)
         self.cur_targets = torch.zeros((N, 16), **f)
@@ -234,6 +253,7 @@ class AllegroHandDextremeADR(VecTask):
         self.ext_rand: Optional[torch.Tensor] = None                   # parity mode: [N, HA_DEX_RND_STRIDE] raw draws (pre)
         self.ext_rand_post: Optional[torch.Tensor] = None              # parity mode: [N, HA_DEX_POST_RND_STRIDE] raw draws (post)
         self.rna_perturbation: Optional[torch.Tensor] = None           # [N, 16] DOF-space output of the RNA network, if a caller runs one
+        self.adr_resample_on_step = True                               # launch the per-env ADR resampling ahead of every K_pre
 
     # ---- C-ABI structs -----------------------------------------------------------------------
     def _build_abi(self):
@@ -286,6 +306,33 @@ class AllegroHandDextremeADR(VecTask):
         self._set_moving_average(self.act_moving_average)
         self._buffers = _lib.HaDexBuffers()
         self._bind_buffers()
+        self._adr_table = self._adr_buffers = None
+        if self.use_adr and all(k in self.adr_tensor_keys for k in ["action_latency", "cube_pose_refresh_rate"] + AFFINE_ADR_KEYS):
+            ab = _lib.HaDexAdrBuffers()
+            for i, k in enumerate(self.adr_tensor_keys):
+                ab.values[i] = self.adr_tensor_values[k].data_ptr()
+            ab.worker_types, ab.adr_modes = self.worker_types.data_ptr(), self.adr_modes.data_ptr()
+            self._adr_buffers = ab
+            self.refresh_adr_table()
+
+    def refresh_adr_table(self):
+        """Push the host-side ADR ranges (``adr_params[k]["range"]`` / ``["next_limits"]``) into the table the resampling kernel reads."""
+        t = _lib.HaDexAdrTable()
+        keys = self.adr_tensor_keys
+        assert len(keys) <= C["HA_DEX_ADR_MAX_PARAMS"]
+        t.n_params_total, t.n_tensor = self.num_adr_params, len(keys)
+        for i, k in enumerate(keys):
+            prm = self.adr_params[k]
+            lo, hi = (float(v) for v in prm["range"])
+            nlo, nhi = (float(v) for v in prm.get("next_limits") or (lo, hi))
+            t.param_index[i] = self.adr_params_keys.index(k)
+            t.lo[i], t.span[i] = lo, hi - lo
+            t.low_value[i], t.high_value[i] = (nlo, nhi) if self.adr_extended_boundary_sample else (lo, hi)
+        t.boundary_fraction = self.worker_adr_boundary_fraction
+        t.idx_action_latency, t.idx_cube_pose_refresh_rate = keys.index("action_latency"), keys.index("cube_pose_refresh_rate")
+        for a, k in enumerate(AFFINE_ADR_KEYS):
+            t.idx_affine[a] = keys.index(k)
+        self._adr_table = t
 
     def _set_moving_average(self, value: float):
         self.act_moving_average = value
@@ -400,8 +447,22 @@ class AllegroHandDextremeADR(VecTask):
         return self.get_adr_tensor("rna_alpha").view(-1, 1)
 
     def apply_randomizations(self, dr_params=None, randomize_buf=None, adr_objective=None, randomisation_callback=None):
-        """Host-side ADR hook (adr_vec_task.py:920-1100, allegro_hand_dextreme.py:1392-1416): control logic outside the kernels."""
-        return None
+        """The per-env tensor half of ADR ``apply_randomizations`` (adr_vec_task.py:740-758, :666-730 via :915-917;
+        allegro_hand_dextreme.py:1392-1416) as one launch on the envs in ``reset_buf & ~apply_reset_buf`` (every env on the first
+        call, like ``first_randomization``).  ``randomize_buf`` is accepted for signature parity; the kernel derives the same mask."""
+        if self._adr_table is None:
+            return
+        self._require_engine()
+        self._adr_table.all_envs = 1 if self.first_randomization else 0
+        self.first_randomization = False
+        if self.ext_rand_adr is not None:
+            r = self.ext_rand_adr
+            assert r.shape == (self.num_envs, C["HA_DEX_ADR_RND_STRIDE"]) and r.dtype == torch.float32 and r.is_contiguous()
+            self._params.use_fast_rng, ptr = 0, ctypes.c_void_p(r.data_ptr())
+        else:
+            self._params.use_fast_rng, ptr = 1, ctypes.c_void_p(0)
+        _lib.check(self._lib.ha_dex_adr_resample(ctypes.byref(self._params), ctypes.byref(self._buffers), ctypes.byref(self._adr_table),
+                                                 ctypes.byref(self._adr_buffers), ptr, self._stream()))
 
     # ---- the hot path --------------------------------------------------------------------------
     def _rand_ptrs(self):
@@ -430,6 +491,8 @@ class AllegroHandDextremeADR(VecTask):
         if actions.dtype != torch.float32 or not actions.is_contiguous():
             actions = actions.float().contiguous()
         self._rebind_sim_state()
+        if self.randomize and self.use_adr and self.adr_resample_on_step:
+            self.apply_randomizations(self.randomization_params, None, adr_objective=self.successes)      # (:926-937), mask derived in-kernel
         rna = self.rna_perturbation
         rna_ptr = ctypes.c_void_p(rna.data_ptr()) if rna is not None else ctypes.c_void_p(0)
         _lib.check(self._lib.ha_dex_pre_step(ctypes.byref(self._params), ctypes.byref(self._buffers), ctypes.c_void_p(actions.data_ptr()),
