@@ -111,6 +111,17 @@ struct Rng {
                                   make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
     return make_float2(u32_to_unit(r.x), u32_to_unit(r.y));
   }
+  // four standard normals from ONE counter block (two Box-Muller pairs); `block` must be unique per (env, use)
+  __device__ __forceinline__ float4 normal4(int env, uint32_t block) const {
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)env, 0x40000000u | block, (uint32_t)step, (uint32_t)(step >> 32)),
+                                  make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    const float two_pi = 6.2831854820251465f;
+    const float r0 = sqrtf(-2.0f * __logf(1.0f - u32_to_unit(r.x))), r1 = sqrtf(-2.0f * __logf(1.0f - u32_to_unit(r.z)));
+    float s0, c0, s1, c1;
+    __sincosf(two_pi * u32_to_unit(r.y), &s0, &c0);
+    __sincosf(two_pi * u32_to_unit(r.w), &s1, &c1);
+    return make_float4(r0 * c0, r0 * s0, r1 * c1, r1 * s1);
+  }
   // standard normal for (env, slot): Box-Muller over an independent counter block
   __device__ __forceinline__ float normal(int env, int slot) const {
     const uint4 r = philox4x32_10(make_uint4((uint32_t)env, 0x80000000u | (uint32_t)(slot >> 1), (uint32_t)step, (uint32_t)(step >> 32)),

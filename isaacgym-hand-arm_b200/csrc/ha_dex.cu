@@ -47,6 +47,9 @@ int validate_dex(const HaDexParams* p, const HaDexBuffers* b) {
   HA_REQUIRE_ALIGNED16(b->cube_random_params);
   HA_REQUIRE_ALIGNED16(b->hand_random_params);
   HA_REQUIRE_ALIGNED16(b->gravity_vec);
+  HA_REQUIRE_ALIGNED16(b->prev_actions);
+  HA_REQUIRE_ALIGNED16(b->action_queue);
+  HA_REQUIRE_ALIGNED16(b->dof_delta);
   HA_REQUIRE_ALIGNED16(b->obs_object_pose);
   HA_REQUIRE_ALIGNED16(b->obs_object_pose_freq);
   if (p->root_regular)
@@ -131,6 +134,8 @@ int ha_dex_pre_step(const HaDexParams* p, const HaDexBuffers* b, const float* ac
   int rc = validate_dex(p, b);
   if (rc) return rc;
   HA_REQUIRE(actions != nullptr, "actions is null");
+  HA_REQUIRE_ALIGNED16(actions);
+  if (rna_perturbation) HA_REQUIRE_ALIGNED16(rna_perturbation);
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   HA_REQUIRE(rna_perturbation == nullptr || b->adr_rna_alpha != nullptr, "adr_rna_alpha is required with rna_perturbation");
   const int grid = (p->n_envs + ha::kDexTile - 1) / ha::kDexTile;

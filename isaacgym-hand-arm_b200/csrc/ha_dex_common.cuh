@@ -22,6 +22,22 @@ struct DexRand {
   __device__ __forceinline__ float nrm(int env, int slot) const {
     return ext ? __ldg(ext + (size_t)env * stride + slot) : rng.normal(env, space + slot);
   }
+  // normals of slots slot .. slot+3: the table's four entries, or one Philox block in fast mode
+  __device__ __forceinline__ float4 nrm4(int env, int slot) const {
+    if (ext) {
+      const float* r = ext + (size_t)env * stride + slot;
+      return make_float4(__ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3));
+    }
+    return rng.normal4(env, (uint32_t)(space + slot));
+  }
+  // uniforms of slots slot .. slot+3
+  __device__ __forceinline__ float4 u4(int env, int slot) const {
+    if (ext) {
+      const float* r = ext + (size_t)env * stride + slot;
+      return make_float4(__ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3));
+    }
+    return rng.uniform4(env, 0x20000000 | (space + slot));
+  }
 };
 
 // sample_gaussian_adr (:1383-1387): stdev = exp(v^2) - 1 where v > 0, else 0

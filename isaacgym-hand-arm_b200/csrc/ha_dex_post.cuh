@@ -11,7 +11,7 @@
 //   compute   warp 0, lane = env: wrist-relative poses (closed-form rigid inverse), relative rotations, the ADR pose
 //             pipeline (affine + white noise, random pose injection, refresh-rate and delay latches);
 //             warp 1, lane = env: rotation / position distances, per-env reward state;
-//             warps 2-3: half-warp per env, lane = DOF: randomised DOF positions and the three 16-term sums of the reward;
+//             warps 2-3: four lanes per env, four DOFs per lane: randomised DOF positions and the three 16-term sums of the reward;
 //   reward    warp 1 finishes compute_hand_reward and the statistics while
 //   assemble  warps 0, 2, 3 walk the 32 x 285 tile flat through a column-descriptor table, apply scale / unscale / clip
 //             and write 128-bit coalesced stores; the latches and prev_targets leave through the same flat path.
@@ -201,13 +201,14 @@ dex_post_kernel(const __grid_constant__ HaDexParams p, const __grid_constant__ H
     const float sd = dex_stdev(r_pose_white);
     const float* ps = stage + o.a_ps + lane * 7;
     const float* pa = stage + o.a_pa + lane * 7;
-    float rf[5];
-#pragma unroll
-    for (int c = 0; c < 5; ++c) rf[c] = 2.0f * R.u(env, HA_DEX_POST_RND_CUBE + c) + -1.0f;
-    const f4 rq = dex_new_rot(p.apply_random_quat, rf[3], rf[4], R.u(env, HA_DEX_POST_RND_CUBE_QUAT), R.u(env, HA_DEX_POST_RND_CUBE_QUAT + 1),
-                              R.u(env, HA_DEX_POST_RND_CUBE_QUAT + 2));
-    const bool inject = R.u(env, HA_DEX_POST_RND_CUBE_MASK) < p.random_cube_pose_prob;
-    const bool delayed = R.u(env, HA_DEX_POST_RND_DELAY) < r_obs_delay;
+    // the ten uniforms (slots 7..16) and seven normals (slots 0..6) of this env: five counter blocks in fast mode
+    const float4 ua = R.u4(env, HA_DEX_POST_RND_CUBE), ub = R.u4(env, HA_DEX_POST_RND_CUBE + 4), uc = R.u4(env, HA_DEX_POST_RND_CUBE + 8);
+    const float4 na = R.nrm4(env, HA_DEX_POST_RND_POSE_WHITE), nb = R.nrm4(env, HA_DEX_POST_RND_POSE_WHITE + 4);
+    const float pose_white[7] = {na.x, na.y, na.z, na.w, nb.x, nb.y, nb.z};
+    const float rf[5] = {2.0f * ua.x + -1.0f, 2.0f * ua.y + -1.0f, 2.0f * ua.z + -1.0f, 2.0f * ua.w + -1.0f, 2.0f * ub.x + -1.0f};
+    const f4 rq = dex_new_rot(p.apply_random_quat, rf[3], rf[4], ub.y, ub.z, ub.w);
+    const bool inject = uc.x < p.random_cube_pose_prob;
+    const bool delayed = uc.y < r_obs_delay;
     const float* init = b.object_init_state + (size_t)env * 13;
     const float rnd_pose[7] = {__ldg(init + 0) + 0.5f * rf[0], __ldg(init + 1) + 0.5f * rf[1], __ldg(init + 2) + 0.5f * rf[2], rq.x, rq.y, rq.z, rq.w};
     float* fr = stage + o.freq + lane * 7;
@@ -215,7 +216,7 @@ dex_post_kernel(const __grid_constant__ HaDexParams p, const __grid_constant__ H
     float camq[4];
 #pragma unroll
     for (int c = 0; c < 7; ++c) {
-      const float noisy = ps[c] * op.v[c] + pa[c] + R.nrm(env, HA_DEX_POST_RND_POSE_WHITE + c) * sd;
+      const float noisy = ps[c] * op.v[c] + pa[c] + pose_white[c] * sd;
       const float seen = inject ? rnd_pose[c] : noisy;
       const float f = update_freq ? seen : fr[c];
       const float v = delayed ? cm[c] : f;
@@ -239,23 +240,29 @@ dex_post_kernel(const __grid_constant__ HaDexParams p, const __grid_constant__ H
     r_best = r_best < 0.0f ? rot_dist : r_best;                                 // lazy init (:685)
     cmp[kCmpRotDist + 0] = rot_dist; cmp[kCmpRotDist + 1] = r_best;
   } else {
-    // warps 2-3: half-warp per env, lane & 15 = DOF; 2 envs per warp pass
-    const int d = lane & 15, half = lane >> 4;
-    const float lo = p.dof_lower[d], hi = p.dof_upper[d], rcp = p.dof_range_rcp[d];
-    for (int e = (warp - 2) * 2 + half; e < kDexTile; e += 4) {
+    // warps 2-3: four lanes per env, four DOFs per lane (one Philox block gives the lane's four normals); 8 envs per warp pass
+    const int q = lane & 3, sub = lane >> 2, d0 = 4 * q;
+    for (int e = (warp - 2) * 8 + sub; e < kDexTile; e += 16) {
       const int ee = env0 + min(e, last);
-      const int at = e * 16 + d;
-      const float dof_pos = stage[o.dof + e * 32 + 2 * d], dof_vel = stage[o.dof + e * 32 + 2 * d + 1];
       const float sd = dex_stdev(__ldg(b.adr_affine_dof_pos_white + ee));
-      const float rz = stage[o.a_ds + at] * dof_pos + stage[o.a_da + at] + R.nrm(ee, HA_DEX_POST_RND_DOF_WHITE + d) * sd;
-      stage[o.cmp + e * kDexCmp + kCmpDofRand + d] = div_by_const(2.0f * rz - hi - lo, hi - lo, rcp);
-      const float a = stage[o.act + at], dt = stage[o.cur + at] - stage[o.prev + at], vv = dof_vel / (5.0f - 1.0f);
-      float s_a = a * a, s_d = dt * dt, s_v = vv * vv;
+      const float4 wn4 = R.nrm4(ee, HA_DEX_POST_RND_DOF_WHITE + d0);
+      const float wn[4] = {wn4.x, wn4.y, wn4.z, wn4.w};
+      float s_a = 0.f, s_d = 0.f, s_v = 0.f;
 #pragma unroll
-      for (int m = 8; m > 0; m >>= 1) {
+      for (int c = 0; c < 4; ++c) {
+        const int d = d0 + c, at = e * 16 + d;
+        const float lo = p.dof_lower[d], hi = p.dof_upper[d];
+        const float dof_pos = stage[o.dof + e * 32 + 2 * d], dof_vel = stage[o.dof + e * 32 + 2 * d + 1];
+        const float rz = stage[o.a_ds + at] * dof_pos + stage[o.a_da + at] + wn[c] * sd;
+        stage[o.cmp + e * kDexCmp + kCmpDofRand + d] = div_by_const(2.0f * rz - hi - lo, hi - lo, p.dof_range_rcp[d]);
+        const float a = stage[o.act + at], dt = stage[o.cur + at] - stage[o.prev + at], vv = dof_vel / (5.0f - 1.0f);
+        s_a += a * a; s_d += dt * dt; s_v += vv * vv;
+      }
+#pragma unroll
+      for (int m = 2; m > 0; m >>= 1) {
         s_a += __shfl_xor_sync(FULL, s_a, m); s_d += __shfl_xor_sync(FULL, s_d, m); s_v += __shfl_xor_sync(FULL, s_v, m);
       }
-      if (d == 0) { stage[o.sums + e * 3 + 0] = s_a; stage[o.sums + e * 3 + 1] = s_d; stage[o.sums + e * 3 + 2] = s_v; }
+      if (q == 0) { stage[o.sums + e * 3 + 0] = s_a; stage[o.sums + e * 3 + 1] = s_d; stage[o.sums + e * 3 + 2] = s_v; }
     }
   }
   __syncthreads();

@@ -97,48 +97,69 @@ dex_pre_kernel(const __grid_constant__ HaDexParams p, const __grid_constant__ Ha
   __syncthreads();
 
   // ---------------- all threads: action queue, latency / delay / noise, DOF targets (:955-1015, :1430-1441) ----------------
-  {
+  if (tid < nvalid * 4) {                                                      // thread = 4 consecutive DOFs of one env (128-bit accesses)
     const bool copy_actions = (actions != b.actions);
-    const int total = nvalid * D;
-    const size_t slot_stride = (size_t)n * D;
-    const unsigned m_delay = s.m_delay;
-    for (int idx = tid; idx < total; idx += kDexThreads) {
-      const int e = idx >> 4, d = idx & 15;
-      const size_t g = (size_t)env0 * D + idx;                                 // element (env, d) of an [N,16] buffer
-      const bool is_rst = (m_rst >> e) & 1u, fresh = (m_fresh >> e) & 1u;
-      const float lo = p.dof_lower[d], hi = p.dof_upper[d];
-      const float act = __ldg(actions + g);
-      float unscaled = 0.0f;
-      if (fresh) {                                                             // queue and prev_actions restart from the current pose
-        const float dp = is_rst ? s.pos[e][d] : b.dof_state[2 * ((size_t)(env0 + e) * Dp + d)];
-        unscaled = div_by_const(2.0f * dp - hi - lo, hi - lo, p.dof_range_rcp[d]);
-        for (int k = 0; k < L; ++k)
-          if (k != head) b.action_queue[(size_t)k * slot_stride + g] = unscaled;
+    const size_t slot4 = (size_t)n * D / 4;                                    // float4 elements per queue slot
+    const int e = tid >> 2, d0 = (tid & 3) * 4;
+    const size_t g4 = (size_t)env0 * (D / 4) + tid;                            // float4 index into an [N,16] buffer
+    const bool is_rst = (m_rst >> e) & 1u, fresh = (m_fresh >> e) & 1u, delayed = (s.m_delay >> e) & 1u;
+    auto ld4 = [](const float* base, size_t i4) { return __ldg(reinterpret_cast<const float4*>(base) + i4); };
+    auto st4 = [](float* base, size_t i4, float4 v) { reinterpret_cast<float4*>(base)[i4] = v; };
+    float4* queue = reinterpret_cast<float4*>(b.action_queue);
+    const float4 act = ld4(actions, g4);
+    float lo[4], hi[4], rcp[4], av[4], prev[4], out[4], dd[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { lo[c] = p.dof_lower[d0 + c]; hi[c] = p.dof_upper[d0 + c]; rcp[c] = p.dof_range_rcp[d0 + c]; }
+    float4 unscaled = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (fresh) {                                                               // queue and prev_actions restart from the current pose
+      float u[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float dp = is_rst ? s.pos[e][d0 + c] : b.dof_state[2 * ((size_t)(env0 + e) * Dp + d0 + c)];
+        u[c] = div_by_const(2.0f * dp - hi[c] - lo[c], hi[c] - lo[c], rcp[c]);
       }
-      b.action_queue[(size_t)head * slot_stride + g] = act;                    // prev_actions_queue[:, 0] = actions
-      const int lat = s.lat[e];
-      float a;
-      if ((m_delay >> e) & 1u) a = fresh ? unscaled : b.prev_actions[g];
-      else if (lat == 0) a = act;
-      else if (fresh) a = unscaled;
-      else { int k = head - lat; k += (k < 0) ? L : 0; a = b.action_queue[(size_t)k * slot_stride + g]; }
-      const float white = R.nrm(env0 + e, HA_DEX_RND_ACTION_WHITE + d) * s.stdev[e];
-      a = __ldg(b.affine_actions_scaling + g) * a + __ldg(b.affine_actions_additive + g) + white;
-      if (rna) {                                                               // rna_alpha blend (:887-890)
-        const float al = s.alpha[e];
-        const float pert = div_by_const(2.0f * __ldg(rna + g) - hi - lo, hi - lo, p.dof_range_rcp[d]);
-        a = al * pert + (1.0f - al) * a;
-      }
-      const float prev = is_rst ? s.pos[e][d] : b.prev_targets[g];
-      float x = scale_to(a, lo, hi);
-      if (p.use_capped_dof_control) x = prev + fminf(fmaxf(x - prev, -p.max_dof_delta), p.max_dof_delta);
-      x = p.act_moving_average * x + p.one_minus_act_moving_average * prev;
-      x = clamp_to(x, lo, hi);
-      b.cur_targets[g] = x;
-      b.dof_delta[g] = x - prev;
-      b.prev_actions[g] = act;
-      if (copy_actions) b.actions[g] = act;
+      unscaled = make_float4(u[0], u[1], u[2], u[3]);
+      for (int k = 0; k < L; ++k)
+        if (k != head) queue[(size_t)k * slot4 + g4] = unscaled;
     }
+    queue[(size_t)head * slot4 + g4] = act;                                    // prev_actions_queue[:, 0] = actions
+    const int lat = s.lat[e];
+    float4 a4;
+    if (delayed) a4 = fresh ? unscaled : *(reinterpret_cast<const float4*>(b.prev_actions) + g4);
+    else if (lat == 0) a4 = act;
+    else if (fresh) a4 = unscaled;
+    else { int k = head - lat; k += (k < 0) ? L : 0; a4 = queue[(size_t)k * slot4 + g4]; }
+    const float4 wn = R.nrm4(env0 + e, HA_DEX_RND_ACTION_WHITE + d0);
+    const float4 sc = ld4(b.affine_actions_scaling, g4), ad = ld4(b.affine_actions_additive, g4);
+    const float sd = s.stdev[e];
+    av[0] = sc.x * a4.x + ad.x + wn.x * sd; av[1] = sc.y * a4.y + ad.y + wn.y * sd;
+    av[2] = sc.z * a4.z + ad.z + wn.z * sd; av[3] = sc.w * a4.w + ad.w + wn.w * sd;
+    if (rna) {                                                                 // rna_alpha blend (:887-890)
+      const float al = s.alpha[e];
+      const float4 rp = ld4(rna, g4);
+      const float r[4] = {rp.x, rp.y, rp.z, rp.w};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) av[c] = al * div_by_const(2.0f * r[c] - hi[c] - lo[c], hi[c] - lo[c], rcp[c]) + (1.0f - al) * av[c];
+    }
+    if (is_rst) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) prev[c] = s.pos[e][d0 + c];
+    } else {
+      const float4 pv = *(reinterpret_cast<const float4*>(b.prev_targets) + g4);
+      prev[0] = pv.x; prev[1] = pv.y; prev[2] = pv.z; prev[3] = pv.w;
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float x = scale_to(av[c], lo[c], hi[c]);
+      if (p.use_capped_dof_control) x = prev[c] + fminf(fmaxf(x - prev[c], -p.max_dof_delta), p.max_dof_delta);
+      x = p.act_moving_average * x + p.one_minus_act_moving_average * prev[c];
+      out[c] = clamp_to(x, lo[c], hi[c]);
+      dd[c] = out[c] - prev[c];
+    }
+    st4(b.cur_targets, g4, make_float4(out[0], out[1], out[2], out[3]));
+    st4(b.dof_delta, g4, make_float4(dd[0], dd[1], dd[2], dd[3]));
+    st4(b.prev_actions, g4, act);
+    if (copy_actions) st4(b.actions, g4, act);
   }
 
   // ---------------- warp 1: random forces on the object body (:1017-1030) ----------------

@@ -30,6 +30,7 @@
 
 // tuning switches (A/B builds): which transfers of K_post go through the bulk-copy engine (cp.async.bulk, SASS UBLKCP).
 // Measured on B200, 32768 envs, component planes (K_post us): none 13.4 | store 13.9 | images + store 13.8 | rows + images + store 15.0.
+// Also measured: hoisting the plane-row decoding of the cp.async issue into a per-thread copy plan (12 more live registers) 13.0 -> 14.1.
 // 128-byte rows are too small for the copy engine (57 descriptors per tile against 8 LDGSTS per thread), and a bulk store needs the
 // +-clamp moved from the store loop into the role warps, which lengthens the per-tile critical path by more than the store saves.
 #ifndef HA_BULK_ROWS
