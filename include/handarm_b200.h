@@ -643,6 +643,30 @@ int ha_dex_pre_step(const HaDexParams* p, const HaDexBuffers* b, const float* ac
 int ha_dex_post_step(const HaDexParams* p, const HaDexBuffers* b, const float* ext_rand_post, ha_stream_t stream);
 int ha_dex_observe(const HaDexParams* p, const HaDexBuffers* b, const float* ext_rand_post, ha_stream_t stream);
 
+/* =====================================================================================================
+ * Observation / action noise of domain randomisation: the closures VecTask.apply_randomizations builds (vec_task.py:684-754) and
+ * VecTask.step applies to the actions before pre_physics_step (:398-400) and to obs_buf after post_physics_step (:427-429):
+ *   gaussian: noise = (corr * var_corr + mu_corr) + N(0,1) * var + mu        uniform: noise = (corr * (hi_c - lo_c) + lo_c) + U(0,1) * (hi - lo) + lo
+ *   out = x + noise (additive) | x * noise (scaling);   corr = the persistent N(0,1) tensor drawn on the closure's first use.
+ * One streaming pass: x, corr read once, out written once (12 B / element), white noise from in-kernel Philox (or a table in parity mode).
+ * ===================================================================================================== */
+enum { HA_NOISE_GAUSSIAN = 0, HA_NOISE_UNIFORM = 1 };
+enum { HA_NOISE_ADDITIVE = 0, HA_NOISE_SCALING = 1 };
+typedef struct HaNoiseParams {
+  int32_t abi_version;
+  int32_t distribution;   /* HA_NOISE_GAUSSIAN / HA_NOISE_UNIFORM */
+  int32_t operation;      /* HA_NOISE_ADDITIVE / HA_NOISE_SCALING */
+  int32_t use_fast_rng;
+  float corr_scale, corr_shift;     /* var_corr, mu_corr | hi_corr - lo_corr, lo_corr */
+  float white_scale, white_shift;   /* var, mu | hi - lo, lo */
+  float clip;                       /* > 0: clamp the result to +-clip (vec_task.py:432 follows the observation noise) */
+  uint64_t rng_seed, rng_step;
+} HaNoiseParams;
+size_t ha_sizeof_noise_params(void);
+/* x, corr, out: [count] floats (out may alias x); ext_white: nullable [count] raw draws (parity mode) */
+int ha_dr_noise_apply(const HaNoiseParams* p, const float* x, const float* corr, float* out, size_t count, const float* ext_white,
+                      ha_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

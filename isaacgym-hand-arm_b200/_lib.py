@@ -114,6 +114,7 @@ HaDexParams = STRUCTS["HaDexParams"]
 HaDexBuffers = STRUCTS["HaDexBuffers"]
 HaDexAdrTable = STRUCTS["HaDexAdrTable"]
 HaDexAdrBuffers = STRUCTS["HaDexAdrBuffers"]
+HaNoiseParams = STRUCTS["HaNoiseParams"]
 
 _lib = None
 
@@ -187,6 +188,12 @@ def load():
     lib.ha_dex_fill_derived.restype = None
     for fn in ("ha_dex_bytes_per_env_step", "ha_dex_post_bytes_per_env_step", "ha_dex_pre_bytes_per_env_step"):
         getattr(lib, fn).argtypes = [ctypes.c_void_p]
+    # DR noise
+    lib.ha_sizeof_noise_params.restype = ctypes.c_size_t
+    if ctypes.sizeof(HaNoiseParams) != lib.ha_sizeof_noise_params():
+        raise HandArmLibraryError(f"struct HaNoiseParams: ctypes size {ctypes.sizeof(HaNoiseParams)} != C size {lib.ha_sizeof_noise_params()}")
+    lib.ha_dr_noise_apply.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
+                                      ctypes.c_void_p]
     _lib = lib
     return lib
 

@@ -196,6 +196,18 @@ class VecTask(Env):
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict, self.rew_buf.to(self.rl_device), self.reset_buf.to(self.rl_device), self.extras
 
+    def apply_randomizations(self, dr_params):
+        """The non-physical half of ``vec_task.py:646-754``: (re)builds the observation / action noise closures that ``step``
+        applies.  Physics-property randomisation (``:756-876``) drives the Isaac Gym API and is outside the path."""
+        from .dr_noise import build_noise_closures
+        rand_freq = dr_params.get("frequency", 1)
+        self.last_step = self.control_steps                      # gym.get_frame_count(sim)
+        do_nonenv_randomize = self.first_randomization or (self.last_step - self.last_rand_step) >= rand_freq
+        if do_nonenv_randomize:
+            self.last_rand_step = self.last_step
+            self.dr_randomizations.update(build_noise_closures(dr_params, self.last_step, seed=getattr(self, "_seed", 0)))
+        self.first_randomization = False
+
     def zero_actions(self) -> torch.Tensor:
         return torch.zeros([self.num_envs, self.num_actions], dtype=torch.float32, device=self.rl_device)
 
