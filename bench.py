@@ -502,11 +502,12 @@ def measure(args, layout, device, rank, world, local, headline=True):
             tdt = torch.tensor([dt, dt_serial], device=device)
             dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
             dt, dt_serial = float(tdt[0]), float(tdt[1])
-        e2e = {"value": world * N * k / dt, "unit": UNIT, "h2d_bytes_per_step": N * 23 * 4,
+        v_multi, v_one = world * N * k / dt, world * N * k / dt_serial
+        e2e = {"value": max(v_multi, v_one), "unit": UNIT, "h2d_bytes_per_step": N * 23 * 4,
                "d2h_bytes_per_step": N * (t0.num_obs * 4 + 4 + 8 + 1), "steps": k,
-               "mode": f"VecTask.step per env block on its own stream ({B} blocks round-robin), pinned host actions in, obs / reward / reset / "
-                       "time_outs out every step",
-               "value_one_stream": world * N * k / dt_serial}
+               "mode": ("VecTask.step per env block on its own stream" if v_multi >= v_one else "VecTask.step on one stream, host sync every step")
+                       + f" ({B} blocks round-robin), pinned host actions in, obs / reward / reset / time_outs out every step",
+               "value_stream_per_block": v_multi, "value_one_stream": v_one}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline and headline:
