@@ -521,6 +521,7 @@ typedef struct HaDexParams {
   float reset_position_noise, reset_position_noise_z, reset_dof_pos_noise, reset_dof_vel_noise;
   float goal_displacement[3];
   float random_cube_pose_prob;
+  int32_t n_view_cols[2];   /* widths of the two concatenated views K_post also emits (0: off), see HaDexBuffers.view_* */
 } HaDexParams;
 
 typedef struct HaDexBuffers {
@@ -590,6 +591,11 @@ typedef struct HaDexBuffers {
   int64_t* stat_accum;
   uint32_t* tickets;                /* [8], zero-initialised once */
   int64_t* dynamic;                 /* [HA_DEX_DYN_LEN] */
+  /* optional concatenated views for the rl_games adapter (ComplexObsRLGPUEnv._generate_obs, rlgames_utils.py:341-399: torch.cat of the
+     policy inputs -> "obs", of the critic inputs -> "states"): view v is [n_envs, n_view_cols[v]] with column j = obs_rows column
+     view_cols[v][j]; written by K_post from the same staged tile, so the two cats per step disappear.  nullable when the width is 0 */
+  const int32_t* view_cols[2];
+  float* view_rows[2];
 } HaDexBuffers;
 
 /* ---- per-env ADR resampling on reset: recycle_envs (adr_vec_task.py:740-758), sample_adr_tensor (:666-730) for every tensorised

@@ -238,14 +238,15 @@ struct HandCol { int base, stride, op; float a, b, c; };   // value(e) = stage[b
 
 // Row assembly, warp per env row: lane l owns columns l, l + 32, ... and keeps their descriptors in registers, so one row costs
 // ceil(W / 32) shared loads, ops and 128-byte coalesced stores per warp.  `rank` / `nwarps`: this warp's index among the warps taking part.
+// `map` (nullable): column j of the output is column map[j] of the descriptor table (a permuted / subset view of the row).
 template <int MAX_PER_LANE>
 __device__ __forceinline__ void assemble_rows(const float* stage, const HandCol* cols, float* __restrict__ out, const int W, const int nvalid,
-                                              const float clip, const int lane, const int rank, const int nwarps) {
+                                              const float clip, const int lane, const int rank, const int nwarps, const int* map = nullptr) {
   HandCol c[MAX_PER_LANE];
 #pragma unroll
   for (int k = 0; k < MAX_PER_LANE; ++k) {
     const int j = lane + 32 * k;
-    c[k] = (j < W) ? cols[j] : HandCol{0, 0, kOpCopy, 0.f, 0.f, 0.f};
+    c[k] = (j < W) ? cols[map ? __ldg(map + j) : j] : HandCol{0, 0, kOpCopy, 0.f, 0.f, 0.f};
   }
   const bool do_clip = clip > 0.0f;
   for (int e = rank; e < nvalid; e += nwarps) {

@@ -55,6 +55,10 @@ int validate_dex(const HaDexParams* p, const HaDexBuffers* b) {
   if (p->root_regular)
     HA_REQUIRE(p->actors_per_env > 0 && p->object_slot >= 0 && p->object_slot < p->actors_per_env && p->goal_slot >= 0 &&
                    p->goal_slot < p->actors_per_env, "root_regular needs 0 <= object_slot, goal_slot < actors_per_env");
+  for (int v = 0; v < 2; ++v) {
+    HA_REQUIRE(p->n_view_cols[v] >= 0 && p->n_view_cols[v] <= HA_DEX_OBS_DIM, "n_view_cols[%d] = %d out of range", v, p->n_view_cols[v]);
+    HA_REQUIRE(p->n_view_cols[v] == 0 || (b->view_cols[v] != nullptr && b->view_rows[v] != nullptr), "view %d: view_cols / view_rows is null", v);
+  }
   return HA_OK;
 }
 

@@ -272,6 +272,11 @@ dex_post_kernel(const __grid_constant__ HaDexParams p, const __grid_constant__ H
     const int r = (warp == 0) ? lane : tid - 32;                                // ranks 0..95
     assemble_rows<(HA_DEX_OBS_DIM + 31) / 32>(stage, cols, b.obs_rows + (size_t)env0 * HA_DEX_OBS_DIM, HA_DEX_OBS_DIM, nvalid, p.clip_obs, lane,
                                               warp == 0 ? 0 : warp - 1, 3);
+#pragma unroll
+    for (int v = 0; v < 2; ++v)                                                  // concatenated policy / critic views (rl_games adapter)
+      if (p.n_view_cols[v] > 0)
+        assemble_rows<(HA_DEX_OBS_DIM + 31) / 32>(stage, cols, b.view_rows[v] + (size_t)env0 * p.n_view_cols[v], p.n_view_cols[v], nvalid,
+                                                  p.clip_obs, lane, warp == 0 ? 0 : warp - 1, 3, b.view_cols[v]);
     for (int j = r; j < nvalid * 7; j += kDexThreads - 32) {                    // the two pose latches
       b.obs_object_pose_freq[(size_t)env0 * 7 + j] = stage[o.freq + j];
       b.obs_object_pose[(size_t)env0 * 7 + j] = stage[o.cam + j];

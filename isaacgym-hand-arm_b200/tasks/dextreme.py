@@ -253,6 +253,7 @@ class AllegroHandDextremeADR(VecTask):
         self.ext_rand: Optional[torch.Tensor] = None                   # parity mode: [N, HA_DEX_RND_STRIDE] raw draws (pre)
         self.ext_rand_post: Optional[torch.Tensor] = None              # parity mode: [N, HA_DEX_POST_RND_STRIDE] raw draws (post)
         self.rna_perturbation: Optional[torch.Tensor] = None           # [N, 16] DOF-space output of the RNA network, if a caller runs one
+        self.obs_views: Dict[str, torch.Tensor] = {}                   # concatenated views emitted by K_post (set_obs_views)
         self.adr_resample_on_step = True                               # launch the per-env ADR resampling ahead of every K_pre
 
     # ---- C-ABI structs -----------------------------------------------------------------------
@@ -519,6 +520,28 @@ class AllegroHandDextremeADR(VecTask):
         self._require_engine()
         self._rebind_sim_state()
         _lib.check(self._lib.ha_dex_observe(ctypes.byref(self._params), ctypes.byref(self._buffers), self._rand_ptrs()[1], self._stream()))
+
+    def set_obs_views(self, obs_spec: Dict[str, Dict]) -> None:
+        """Have K_post also emit the concatenated tensors the rl_games adapter asks for (``obs_spec`` as ``train.py:162-167`` builds it:
+        ``{"obs": {"names": [...], "concat": True, ...}, "states": {...}}``), so ``ComplexObsRLGPUEnv._generate_obs``
+        (``rlgames_utils.py:341-399``) needs no ``torch.cat``."""
+        self._require_engine()
+        ofs, o = {}, 0
+        for k, w in self.num_obs_dict.items():
+            ofs[k] = (o, w)
+            o += w
+        self.obs_views: Dict[str, torch.Tensor] = {}
+        self._view_maps = []
+        for v, key in enumerate(("obs", "states")):
+            names = obs_spec.get(key, {}).get("names", []) if obs_spec.get(key, {}).get("concat", True) else []
+            cols = [c for n in names for c in range(ofs[n][0], ofs[n][0] + ofs[n][1])]
+            self._params.n_view_cols[v] = len(cols)
+            if cols:
+                m = torch.tensor(cols, dtype=torch.int32, device=self.device)
+                rows = torch.zeros((self.num_envs, len(cols)), dtype=torch.float, device=self.device)
+                self._view_maps.append(m)
+                self.obs_views[key] = rows
+                self._buffers.view_cols[v], self._buffers.view_rows[v] = m.data_ptr(), rows.data_ptr()
 
     def _obs_dict_out(self) -> Dict[str, torch.Tensor]:
         return {k: v.to(self.rl_device) for k, v in self.obs_dict_views.items()}
