@@ -1,8 +1,15 @@
-"""Task-config loader for the unmodified Hydra YAML tree under ``cfg/``.
+"""Task-config loader: Hydra-style composition of the task nodes into the dict a task constructor reads.
 
 The reference composes its configs with Hydra + OmegaConf (``isaacgymenvs/__init__.py:9-57``,
 ``cfg/config.yaml``).  Neither is installed here, so this module implements the small subset the
-five hot-path task configs use:
+five hot-path task configs use.  The nodes come from one of two places:
+
+* by default ``cfg/task_tables.json`` -- the parsed VALUES of the reference's config nodes (keys, ``defaults`` lists,
+  interpolation strings; transcribed by ``tools/transcribe_cfg.py``, the YAML files themselves are not shipped);
+* when ``HANDARM_CFG_DIR`` (or ``set_cfg_dir``) names a Hydra tree -- e.g. a user's own, possibly edited,
+  ``isaacgymenvs/cfg`` -- the unmodified YAML files under it.
+
+Supported Hydra / OmegaConf features:
 
 * ``defaults:`` composition inside ``cfg/task`` (``- AllegroKuka`` pulls a sibling file,
   ``- env: reorientation`` merges ``cfg/task/env/reorientation.yaml`` under the ``env`` key,
@@ -17,13 +24,24 @@ constructors (``rlgames_utils.py:113-121``).
 from __future__ import annotations
 
 import copy
+import json
 import os
 import re
 from typing import Any, Dict, List, Optional
 
 import yaml
 
-CFG_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cfg")
+TABLE_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cfg", "task_tables.json")
+_cfg_dir: Optional[str] = os.environ.get("HANDARM_CFG_DIR") or None
+_table: Optional[dict] = None
+
+
+def set_cfg_dir(path: Optional[str]) -> None:
+    """Read the nodes from the Hydra YAML tree at ``path`` (``.../isaacgymenvs/cfg``); ``None`` returns to the built-in table."""
+    global _cfg_dir
+    if path is not None and not os.path.isfile(os.path.join(path, "config.yaml")):
+        raise FileNotFoundError(f"{path!r} is not a Hydra config tree (no config.yaml)")
+    _cfg_dir = path
 
 
 def _merge(dst: dict, src: dict) -> dict:
@@ -35,15 +53,27 @@ def _merge(dst: dict, src: dict) -> dict:
     return dst
 
 
-def _load_yaml(path: str) -> dict:
-    with open(path) as f:
-        return yaml.safe_load(f) or {}
+def _load_node(rel: str) -> dict:
+    """One config node by its path relative to the tree root without extension (``task/AllegroKuka``, ``task/env/throw``)."""
+    global _table
+    if _cfg_dir is not None:
+        path = os.path.join(_cfg_dir, rel + ".yaml")
+        if not os.path.isfile(path):
+            raise KeyError(f"no config node {rel!r} under {_cfg_dir}")
+        with open(path) as f:
+            return yaml.safe_load(f) or {}
+    if _table is None:
+        with open(TABLE_PATH) as f:
+            _table = json.load(f)["nodes"]
+    if rel not in _table:
+        raise KeyError(f"no config node {rel!r} in {os.path.basename(TABLE_PATH)} (known: {sorted(_table)})")
+    return copy.deepcopy(_table[rel])
 
 
 def _compose_task(name: str, subdir: str = "task", overrides: Optional[Dict[str, str]] = None) -> dict:
     """Hydra-style composition of ``cfg/<subdir>/<name>.yaml`` honouring its ``defaults`` list."""
     overrides = overrides or {}
-    raw = _load_yaml(os.path.join(CFG_DIR, subdir, name + ".yaml"))
+    raw = _load_node(subdir + "/" + name)
     defaults = raw.pop("defaults", None)
     if not defaults:
         return raw
@@ -58,7 +88,7 @@ def _compose_task(name: str, subdir: str = "task", overrides: Optional[Dict[str,
         elif isinstance(item, dict):
             (group, choice), = item.items()
             choice = overrides.get(group, choice)
-            sub = _compose_task(choice, os.path.join(subdir, group))
+            sub = _compose_task(choice, subdir + "/" + group)
             _merge(out.setdefault(group, {}), sub)
         else:
             raise ValueError(f"unsupported defaults entry {item!r} in {name}.yaml")
@@ -166,7 +196,7 @@ def load_task_config(task: str, num_envs: Optional[int] = None, sim_device: str 
     ``overrides`` is a flat ``{"env.episodeLength": 300}`` style mapping applied before
     interpolation, like Hydra command-line overrides ``task.env.episodeLength=300``.
     """
-    root = _load_yaml(os.path.join(CFG_DIR, "config.yaml"))
+    root = _load_node("config")
     root.pop("defaults", None)
     root.pop("hydra", None)
     root["num_envs"] = "" if num_envs is None else int(num_envs)
@@ -184,4 +214,7 @@ def load_task_config(task: str, num_envs: Optional[int] = None, sim_device: str 
 
 
 def available_tasks() -> List[str]:
-    return sorted(os.path.splitext(f)[0] for f in os.listdir(os.path.join(CFG_DIR, "task")) if f.endswith(".yaml"))
+    if _cfg_dir is not None:
+        return sorted(os.path.splitext(f)[0] for f in os.listdir(os.path.join(_cfg_dir, "task")) if f.endswith(".yaml"))
+    _load_node("config")
+    return sorted(k[len("task/"):] for k in _table if k.startswith("task/") and k.count("/") == 1)

@@ -43,3 +43,30 @@ def test_overrides_and_other_hot_path_tasks_load():
 def test_task_registry_dispatch():
     from handarm_b200.tasks import isaacgym_task_map
     assert "AllegroKuka" in isaacgym_task_map and "AllegroKukaLSTM" in isaacgym_task_map
+
+
+def test_table_matches_reference_tree():
+    """The shipped value table resolves to the same dicts as the reference's own YAML tree (checked where that tree exists)."""
+    import os
+    import pytest
+    ref = "/root/reference/isaacgymenvs/cfg"
+    if not os.path.isdir(ref):
+        pytest.skip("reference checkout not present")
+    cases = [(t, None) for t in hcfg.available_tasks()] + [("AllegroKuka", s) for s in ("regrasping", "throw")] + \
+            [("AllegroKukaTwoArmsLSTM", "regrasping")]
+    from_table = {c: hcfg.load_task_config(c[0], num_envs=77, subtask=c[1]) for c in cases}
+    hcfg.set_cfg_dir(ref)
+    try:
+        assert set(hcfg.available_tasks()) >= {c[0] for c in cases}
+        for c in cases:
+            assert hcfg.load_task_config(c[0], num_envs=77, subtask=c[1]) == from_table[c], c
+    finally:
+        hcfg.set_cfg_dir(None)
+
+
+def test_unknown_node_is_loud():
+    import pytest
+    with pytest.raises(KeyError):
+        hcfg.load_task_config("NoSuchTask")
+    with pytest.raises(FileNotFoundError):
+        hcfg.set_cfg_dir("/nonexistent")
