@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define HA_ABI_VERSION 3
+#define HA_ABI_VERSION 4
 
 #define HA_OK 0
 #define HA_ERR_INVALID (-1)   /* bad argument / unsupported dimension */
@@ -236,14 +236,22 @@ typedef struct HaKukaBuffers {
   int32_t* reset_counts;        /* [4]: n_root, n_hand, n_reset_envs, n_goal_resets */
   /* ---- reductions ---- */
   float* stats;                 /* [HA_STATS_LEN], see HA_KUKA_STAT_* */
-  int64_t* stat_accum;          /* [HA_STATS_LEN] fixed-point accumulators; initialise once with ha_kuka_stat_accum_init(i):
+  int64_t* stat_accum;          /* fixed-point statistics scratch.
+                                   single arm: [HA_KUKA_N_PARTIAL_STATS][HA_KUKA_STAT_SLOTS], one slot per CTA of the last
+                                   ha_kuka_post_step (plain stores; initialise every slot of row i once with ha_kuka_stat_accum_init(i)), folded into stats[] by the next
+                                   ha_kuka_pre_step / ha_kuka_reset_idx or by ha_kuka_stats_finalize;
+                                   two arms: [HA_STATS_LEN] accumulators, initialise once with ha_kuka_stat_accum_init(i):
                                    0 for sums, INT32_MIN for the two MAX slots (the kernel re-arms them itself) */
   uint32_t* tickets;            /* [8], zero-initialised once by the caller */
   /* ---- dynamic scalars ---- */
   HaKukaDynamic* dynamic;       /* device */
 } HaKukaBuffers;
 
-/* stats[] written by ha_kuka_post_step (sums over this GPU's env block) */
+/* per-CTA statistic slots of the single-arm post kernel (its persistent grid never exceeds this) */
+#define HA_KUKA_STAT_SLOTS 768
+
+/* stats[] of the last ha_kuka_post_step (sums over this GPU's env block).  Two arms: written by the post step itself.
+ * Single arm: valid after the next ha_kuka_pre_step / ha_kuka_reset_idx or after ha_kuka_stats_finalize. */
 enum {
   HA_KUKA_STAT_N = 0,            /* n_envs */
   HA_KUKA_STAT_SUM_REWARD,
@@ -300,6 +308,11 @@ int ha_kuka_post_step(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t
 /* compute_observations only (VecTask.reset(), vec_task.py:459-474): fills
  * obs_buf from the current state without touching reward / reset state. */
 int ha_kuka_observe(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream);
+
+/* Folds the per-CTA statistic slots of the last single-arm ha_kuka_post_step into stats[] (the extras means of
+ * allegro_kuka_base.py:903-910).  One small launch, idempotent; the next ha_kuka_pre_step / ha_kuka_reset_idx does the
+ * same implicitly, so a step loop never needs it.  Two arms: no-op (stats[] is written by the post step itself). */
+int ha_kuka_stats_finalize(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream);
 
 
 /* ------------------------------------------------------------------------ */

@@ -150,6 +150,7 @@ def load():
     lib.ha_kuka_pre_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_post_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_observe.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_kuka_stats_finalize.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_reset_idx.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_kuka_obs_dim.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.ha_kuka_fill_derived.argtypes = [ctypes.c_void_p]

@@ -98,7 +98,8 @@ int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStr
   }
   // persistent CTAs: one wave of resident CTAs walks the 32-env tiles
   const int n_tiles = (p->n_envs + ha::kTile - 1) / ha::kTile;
-  const int limit = post_grid_limit(blocks_per_sm);
+  int limit = post_grid_limit(blocks_per_sm);
+  if (limit > HA_KUKA_STAT_SLOTS) limit = HA_KUKA_STAT_SLOTS;        // one statistics slot per CTA
   const int grid = n_tiles < limit ? n_tiles : limit;
   return ha::check_cuda(ha::launch(ha::kuka_post_kernel<K, SOA, kPostNS>, grid, ha::kPostThreads, sizeof(S), st, *p, *b, mode),
                         "kuka_post_kernel launch");
@@ -209,6 +210,13 @@ int ha_kuka_post_step(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t
 
 int ha_kuka_observe(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream) {
   return post_dispatch(p, b, ha::kPostObserveOnly, stream);
+}
+
+int ha_kuka_stats_finalize(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream) {
+  int rc = validate_kuka(p, b);
+  if (rc) return rc;
+  if (p->n_arms == 2) return HA_OK;
+  return ha::check_cuda(ha::launch(ha::kuka_stats_finalize_kernel, (int)ha::kNPart, ha::kThreads, 0, (cudaStream_t)stream, *b, p->n_envs), "kuka_stats_finalize_kernel launch");
 }
 
 }  // extern "C"

@@ -22,8 +22,13 @@
 //   store    the 32 x obs_dim tile leaves shared memory as one contiguous run of
 //            128-bit stores issued by all four warps.
 // Episode statistics: per-lane 64-bit fixed-point partials, reduced once per CTA with
-// integer shuffles and integer atomics, so every sum is order-independent and
-// bit-reproducible for any grid size; the last CTA converts them to floats.
+// integer shuffles, so every sum is order-independent and bit-reproducible for any
+// grid size.  Single arm: each CTA leaves its ten partials in its own slot of
+// stat_accum with plain stores (no atomics, no ticket, nothing the kernel's tail waits
+// for: the atomics + ticket + last-CTA epilogue cost 2.8 us of a 13.1 us launch on B200);
+// the slots are folded into stats[] by the next launch of the step loop (K_pre, CTA 0)
+// or on demand by ha_kuka_stats_finalize.  Two arms (non-persistent grid): integer
+// atomics + last-CTA ticket inside the launch (kuka_post_stats).
 #pragma once
 #include "ha_device.cuh"
 #include "../../include/handarm_b200.h"
@@ -192,6 +197,87 @@ __device__ __forceinline__ void kuka_post_stats(const HaKukaBuffers& b, const Ku
     // fast-mode RNG: one counter tick per step
     b.dynamic->rng_step = b.dynamic->rng_step + 1;
   }
+}
+
+// ---- deferred statistics (single arm) ------------------------------------------------------------------------------------
+// stat_accum is [HA_KUKA_N_PARTIAL_STATS][HA_KUKA_STAT_SLOTS] int64: slot = CTA of the last full post step; the slots beyond the
+// post kernel's grid keep the identity the host wrote once (ha_kuka_stat_accum_init).
+__device__ __forceinline__ void kuka_post_store_partials(const HaKukaBuffers& b, const KukaPostAcc& a, const int lane) {
+  const long long s_rew = warp_sum_ll(a.rew), s_pe = warp_sum_ll(a.prev_ep), s_to = warp_sum_ll(a.tobj);
+  const int s_n = warp_sum_i(a.n), s_rs = warp_sum_i(a.resets), s_su = warp_sum_i(a.success), s_tm = warp_sum_i(a.timeout),
+            s_li = warp_sum_i(a.lifted);
+  const float v_mx = warp_max(a.mx), v_mn = warp_max(a.neg_mn);
+  long long val = 0;
+  switch (lane) {
+    case HA_KUKA_STAT_N: val = s_n; break;
+    case HA_KUKA_STAT_SUM_REWARD: val = s_rew; break;
+    case HA_KUKA_STAT_SUM_RESETS: val = s_rs; break;
+    case HA_KUKA_STAT_SUM_SUCCESS_EVENTS: val = s_su; break;
+    case HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES: val = s_pe; break;
+    case HA_KUKA_STAT_SUM_TRUE_OBJECTIVE: val = s_to; break;
+    case HA_KUKA_STAT_MAX_TRUE_OBJECTIVE: val = float_key(v_mx); break;
+    case HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE: val = float_key(v_mn); break;
+    case HA_KUKA_STAT_SUM_TIMEOUTS: val = s_tm; break;
+    case HA_KUKA_STAT_SUM_LIFTED: val = s_li; break;
+    default: break;
+  }
+  if (lane < kNPart) reinterpret_cast<long long*>(b.stat_accum)[(size_t)lane * HA_KUKA_STAT_SLOTS + blockIdx.x] = val;
+}
+
+// Folding the per-CTA slots into stats[]: statistic s is folded by CTA s of the folding launch (K_pre's first kNPart CTAs, or the
+// kNPart CTAs of kuka_stats_finalize_kernel), kThreads threads each.  Every thread has its kFoldPerThread slot loads in flight at
+// once (one L2 round trip), slots no post CTA wrote hold the identity (host-initialised), so the fold is idempotent and needs no
+// slot count.  Three phases so that K_pre can overlap the loads with its own tile loads and reuse its CTA barrier.
+constexpr int kFoldPerThread = HA_KUKA_STAT_SLOTS / kThreads;
+static_assert(HA_KUKA_STAT_SLOTS % kThreads == 0, "slot count must be a multiple of the folding CTA");
+struct KukaStatFold { long long v[kFoldPerThread]; };
+
+__device__ __forceinline__ void kuka_fold_load(const HaKukaBuffers& b, const int stat, const int tid, KukaStatFold& f) {
+  const long long* part = reinterpret_cast<const long long*>(b.stat_accum) + (size_t)stat * HA_KUKA_STAT_SLOTS;
+#pragma unroll
+  for (int i = 0; i < kFoldPerThread; ++i) f.v[i] = part[tid + kThreads * i];
+}
+// warp-level fold; lane 0 of every warp leaves its value in red[warp] (shared memory, kThreads / 32 entries)
+__device__ __forceinline__ void kuka_fold_warp(const KukaStatFold& f, const int stat, const int tid, long long* red) {
+  const bool is_max = stat_is_max(stat);
+  long long v = f.v[0];
+#pragma unroll
+  for (int i = 1; i < kFoldPerThread; ++i) v = is_max ? (f.v[i] > v ? f.v[i] : v) : v + f.v[i];
+#pragma unroll
+  for (int ofs = 16; ofs > 0; ofs >>= 1) {
+    const long long o = __shfl_xor_sync(0xffffffffu, v, ofs);
+    v = is_max ? (o > v ? o : v) : v + o;
+  }
+  if ((tid & 31) == 0) red[tid >> 5] = v;
+}
+// after a CTA barrier: one thread writes stats[stat] and the value derived from it for extras (allegro_kuka_base.py:903-910)
+__device__ __forceinline__ void kuka_fold_finish(const HaKukaBuffers& b, const int stat, const int n_envs, const long long* red) {
+  const bool is_max = stat_is_max(stat);
+  long long v = red[0];
+#pragma unroll
+  for (int w = 1; w < kThreads / 32; ++w) v = is_max ? (red[w] > v ? red[w] : v) : v + red[w];
+  if (is_max) {
+    if (v == kStatMaxInit) return;                      // no post step has run yet
+    const float x = key_float(v);
+    b.stats[stat] = x;
+    if (stat == HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE) b.stats[HA_KUKA_STAT_MIN_TRUE_OBJECTIVE] = -x;
+    return;
+  }
+  const float x = (float)((double)v / (double)stat_scale(stat));
+  b.stats[stat] = x;
+  const float inv_n = 1.0f / (float)n_envs;             // HA_KUKA_STAT_N counts every env of the block
+  if (stat == HA_KUKA_STAT_SUM_REWARD) b.stats[HA_KUKA_STAT_MEAN_REWARD] = x * inv_n;
+  if (stat == HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES) b.stats[HA_KUKA_STAT_MEAN_PREV_EP_SUCCESSES] = x * inv_n;
+  if (stat == HA_KUKA_STAT_SUM_TRUE_OBJECTIVE) b.stats[HA_KUKA_STAT_MEAN_TRUE_OBJECTIVE] = x * inv_n;
+}
+
+__global__ void __launch_bounds__(kThreads) kuka_stats_finalize_kernel(const __grid_constant__ HaKukaBuffers b, const int n_envs) {
+  __shared__ long long red[kThreads / 32];
+  KukaStatFold f;
+  kuka_fold_load(b, blockIdx.x, threadIdx.x, f);
+  kuka_fold_warp(f, blockIdx.x, threadIdx.x, red);
+  __syncthreads();
+  if (threadIdx.x == 0) kuka_fold_finish(b, blockIdx.x, n_envs, red);
 }
 
 // Issue the cp.async copies of one tile (all 128 threads).  Idle envs of a ragged last tile re-read the last valid env.
@@ -368,6 +454,12 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     keypoint_tol = b.dynamic->keypoint_success_tolerance;
     tobj_scale = b.dynamic->true_objective_scale;
     tobj_offset = b.dynamic->true_objective_offset;
+  }
+  if (blockIdx.x == 0 && tid == 0 && mode == kPostFull) {
+    // step bookkeeping that needs no ordering against the rest of the launch: the reset / index counters of the pre-step are
+    // consumed by now (cleared for the next pre-step), the fast-mode RNG ticks once per step
+    b.reset_counts[0] = 0; b.reset_counts[1] = 0; b.reset_counts[2] = 0; b.reset_counts[3] = 0;
+    b.dynamic->rng_step = b.dynamic->rng_step + 1;
   }
   KukaPostAcc acc;
   if constexpr (SOA && (HA_BULK_ROWS || HA_BULK_IMAGES)) {
@@ -599,16 +691,11 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     const bool bulk_store = HA_BULK_STORE && (nvalid == kTile);   // 14976 contiguous bytes, 16-byte aligned on both sides
     if (bulk_store) fence_proxy_async_smem();           // the tile's generic-proxy writes, before the async proxy reads them
     __syncthreads();                                    // B3: the observation tile is complete
-    // on its last tile the state warp goes straight to the statistics (fence + atomics round trips)
-    const bool stats_now = (next >= n_tiles) && (mode == kPostFull);
     if (bulk_store) {
       if (tid == 0) {                                   // the whole [32, OBS] tile leaves as one bulk copy
         bulk_s2g(b.obs_buf + (size_t)env0 * OBS, sm.obs, kTile * OBS * 4);
         bulk_commit();
       }
-      if (stats_now && warp == 3) kuka_post_stats(b, acc, lane);
-    } else if (stats_now && warp == 3) {
-      kuka_post_stats(b, acc, lane);
     } else {
       // obs tile: clamp (unless the roles already did) and store as one contiguous run of 128-bit words
       const bool clamp_here = do_clamp && !HA_BULK_STORE;
@@ -616,7 +703,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       float4* dst = reinterpret_cast<float4*>(b.obs_buf + (size_t)env0 * OBS);   // 16-byte aligned: env0 % 32 == 0
       const float4* src = reinterpret_cast<const float4*>(sm.obs);
       const int total = nvalid * OBS, nvec = total >> 2;
-      const int sid = warp * 32 + lane, nst = stats_now ? kPostThreads - 32 : kPostThreads;
+      const int sid = warp * 32 + lane, nst = kPostThreads;
 #pragma unroll 2
       for (int q = sid; q < nvec; q += nst) {
         float4 v = src[q];
@@ -643,7 +730,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   }
   cp_async_wait<0>();
   if (HA_BULK_STORE && tid == 0) bulk_wait_read0();     // shared memory must outlive the last bulk store's reads
-  if (blockIdx.x >= n_tiles && warp == 3 && mode == kPostFull) kuka_post_stats(b, acc, lane);   // CTA without a tile still owes its ticket
+  if (warp == 3 && mode == kPostFull) kuka_post_store_partials(b, acc, lane);   // every CTA of the grid fills its slot
 }
 
 }  // namespace ha

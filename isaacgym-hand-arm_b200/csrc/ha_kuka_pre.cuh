@@ -20,6 +20,7 @@
 #pragma once
 #include "ha_device.cuh"
 #include "../../include/handarm_b200.h"
+#include "ha_kuka_post.cuh"   // kuka_stats_finalize_cta
 
 namespace ha {
 
@@ -53,6 +54,7 @@ __device__ __forceinline__ float force_prob_from(const HaKukaParams& p, float u)
 struct KukaPreSmem {
   float lo[24], hi[24], dflt[24], noise[24];
   float pos[kEnvsPerCta][24];      // re-randomised DOF positions of the tile's reset envs (row = env in tile)
+  long long fold[kThreads / 32];   // statistics fold of the CTAs below kNPart (kuka_fold_*)
 };
 
 // reset_idx DOF re-randomisation of one env by one warp, lane = dof (:1271-1290).
@@ -225,6 +227,10 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
 
   pdl_launch_dependents();
   pdl_wait();
+  // ---- CTAs 0 .. kNPart-1 also fold one statistic of the previous post step each (loads in flight with the tile's) ----
+  const bool fold = blockIdx.x < kNPart;                // uniform over the CTA
+  KukaStatFold sf;
+  if (fold) kuka_fold_load(b, blockIdx.x, tid, sf);
   // ---- issue the tile's vector loads first: they do not depend on the masks ----
   const size_t base = (size_t)env0 * D;
   const int total = nvalid * D, nvec = total >> 2;     // tile base is 16-byte aligned (env0 % 32 == 0)
@@ -271,7 +277,9 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   // warp 0: everything the scalar reset needs goes in flight now and is consumed at the very end
   KukaResetPrefetch pf;
   if (warp == 0 && tile_resets) kuka_reset_prefetch(p, b, R, env, lane, rst, grst, pf);
+  if (fold) kuka_fold_warp(sf, blockIdx.x, tid, s.fold);
   __syncthreads();
+  if (fold && tid == kThreads - 1) kuka_fold_finish(b, blockIdx.x, n, s.fold);
   if (m_rst != 0u) {
     // DOF re-randomisation of the tile's reset envs, one warp per env (round robin), lane = dof
     unsigned m = m_rst;

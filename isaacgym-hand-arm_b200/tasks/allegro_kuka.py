@@ -236,7 +236,8 @@ class AllegroKukaBase(VecTask):
         self.root_reset_indices = torch.zeros(2 * N, dtype=torch.int32, device=dev)
         self.hand_reset_indices = torch.zeros(N * self.num_arms, dtype=torch.int32, device=dev)
         self.reset_counts = torch.zeros(4, dtype=torch.int32, device=dev)
-        self.stats = torch.zeros(C["HA_STATS_LEN"], **f)
+        self._stats = torch.zeros(C["HA_STATS_LEN"], **f)
+        self._stats_pending = False
         self._tickets = torch.zeros(8, dtype=torch.int32, device=dev)
         self._object_actor_i32 = self.object_indices.to(torch.int32)
         self._goal_actor_i32 = self.goal_object_indices.to(torch.int32)
@@ -316,8 +317,12 @@ class AllegroKukaBase(VecTask):
         self._params = p
         self._observe_params = _lib.HaKukaParams.from_buffer_copy(p)
         self._observe_params.clamp_abs_obs = 0.0    # VecTask.reset() clips on the host side copy only
-        self._stat_accum = torch.tensor([int(self._lib.ha_kuka_stat_accum_init(i)) for i in range(C["HA_STATS_LEN"])],
-                                        dtype=torch.int64, device=self.device)
+        if self.num_arms == 1:   # one slot of partials per CTA of the post kernel, folded by the next pre step / finalize_stats()
+            init = torch.tensor([int(self._lib.ha_kuka_stat_accum_init(i)) for i in range(C["HA_KUKA_N_PARTIAL_STATS"])], dtype=torch.int64)
+            self._stat_accum = init[:, None].repeat(1, C["HA_KUKA_STAT_SLOTS"]).contiguous().to(self.device)
+        else:
+            self._stat_accum = torch.tensor([int(self._lib.ha_kuka_stat_accum_init(i)) for i in range(C["HA_STATS_LEN"])],
+                                            dtype=torch.int64, device=self.device)
         self._buffers = _lib.HaKukaBuffers()
         self._bind_buffers()
         self._write_dynamic()
@@ -339,7 +344,7 @@ class AllegroKukaBase(VecTask):
             rewards_episode=self._rewards_episode, episode_cumulative=self._episode_cumulative, prev_targets=self.prev_targets,
             cur_targets=self.cur_targets, actions=self.actions, rb_forces=self.rb_forces, random_force_prob=self.random_force_prob,
             root_reset_indices=self.root_reset_indices, hand_reset_indices=self.hand_reset_indices, reset_counts=self.reset_counts,
-            stats=self.stats, stat_accum=self._stat_accum, tickets=self._tickets, dynamic=self._dynamic)
+            stats=self._stats, stat_accum=self._stat_accum, tickets=self._tickets, dynamic=self._dynamic)
         for name, t in self._bound.items():
             assert t.is_contiguous(), name
             setattr(b, name, t.data_ptr())
@@ -426,6 +431,7 @@ class AllegroKukaBase(VecTask):
         rnd = self._rand_ptr()
         _lib.check(self._lib.ha_kuka_pre_step(ctypes.byref(self._params), ctypes.byref(self._buffers), ctypes.c_void_p(actions.data_ptr()),
                                               rnd, self._stream()))
+        self._stats_pending = False       # CTA 0 of the pre kernel folded the previous step's statistic slots
         # what the reference hands to PhysX after this point (recorded, not executed):
         sim = self.sim
         if sim.record_calls:
@@ -453,7 +459,9 @@ class AllegroKukaBase(VecTask):
         self._extra_curriculum()
         self._rebind_sim_state()
         _lib.check(self._lib.ha_kuka_post_step(ctypes.byref(self._params), ctypes.byref(self._buffers), self._stream()))
-        ex, st = self.extras, self.stats
+        self._stats_pending = self.num_arms == 1
+        # 0-dim views of the statistics vector: filled in place by the next pre step or by finalize_stats() / the `stats` property
+        ex, st = self.extras, self._stats
         ex["successes"] = st[C["HA_KUKA_STAT_MEAN_PREV_EP_SUCCESSES"]]
         ex["true_objective"] = self.true_objective
         ex["true_objective_mean"] = st[C["HA_KUKA_STAT_MEAN_TRUE_OBJECTIVE"]]
@@ -462,6 +470,19 @@ class AllegroKukaBase(VecTask):
         ex["rewards_episode"] = self.rewards_episode
         ex["episode_cumulative"] = self.episode_cumulative
         ex["scalars"] = {"success_tolerance": self.success_tolerance}
+
+    def finalize_stats(self) -> None:
+        """Single arm: fold the post kernel's per-CTA statistic slots into the statistics vector now (one small launch)
+        instead of at the head of the next ``pre_physics_step``.  Two arms / nothing pending: no-op."""
+        if self._stats_pending:
+            _lib.check(self._lib.ha_kuka_stats_finalize(ctypes.byref(self._params), ctypes.byref(self._buffers), self._stream()))
+            self._stats_pending = False
+
+    @property
+    def stats(self) -> torch.Tensor:
+        """Episode statistics of the last post step ([HA_STATS_LEN] float32, ``HA_KUKA_STAT_*``)."""
+        self.finalize_stats()
+        return self._stats
 
     def compute_observations(self):
         """allegro_kuka_base.py:991-1089 only (used by VecTask.reset()): obs + lazy init, no reward."""
@@ -478,6 +499,7 @@ class AllegroKukaBase(VecTask):
         self.reset_buf[env_ids] = 1
         self._rebind_sim_state()
         _lib.check(self._lib.ha_kuka_reset_idx(ctypes.byref(self._params), ctypes.byref(self._buffers), self._rand_ptr(), self._stream()))
+        self._stats_pending = False
         saved[env_ids] = 0
         self.reset_buf.copy_(saved)
         self.extras["scalars"] = {"success_tolerance": self.success_tolerance}
