@@ -49,6 +49,7 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   if (b->finger_rew_coeffs) HA_REQUIRE_ALIGNED16(b->finger_rew_coeffs);
   HA_REQUIRE_ALIGNED16(b->object_keypoint_offsets);
   HA_REQUIRE_ALIGNED16(b->object_scales);
+  if (A == 1) HA_REQUIRE_ALIGNED16(b->goal_states);
   HA_REQUIRE_ALIGNED16(b->prev_targets);
   HA_REQUIRE_ALIGNED16(b->cur_targets);
   HA_REQUIRE_ALIGNED16(b->actions);

@@ -47,6 +47,12 @@
 #ifndef HA_BULK_STORE
 #define HA_BULK_STORE 0     // the finished [32, OBS] observation tile
 #endif
+#ifndef HA_LATE_PREFETCH
+#define HA_LATE_PREFETCH 0  // 1: issue the next tile's copies only after this tile's inputs have landed (measured: 11.3 vs 11.0 us, worse)
+#endif
+#ifndef HA_EARLY_STORE
+#define HA_EARLY_STORE 1    // observation words without late columns leave before the reward chain has finished
+#endif
 #ifndef HA_POST_NS1_CTAS
 #define HA_POST_NS1_CTAS 7   // resident single-stage CTAs per SM the register allocation is sized for
 #endif
@@ -106,7 +112,7 @@ struct KukaPostStage {
   float palm[kTile * 13];                          // [e][13]  pos3 quat4 linvel3 angvel3
   float obj[kTile * 13];                           // [e][13]
   float tip[kTile * kTipW];                        // [e][t * 7 + c]  pos3 quat4
-  float goal[kTile * 7];                           // [e][7]
+  float goal[kTile * 13];                          // [e][13] contiguous image of goal_states rows (pos3 quat4 used)
   float kp[kTile * 3 * K];                         // contiguous image of object_keypoint_offsets[env0 .. env0+31]
   float scales[kTile * 3];                         // contiguous image
   float dof[kTile * 2 * kD1];                      // contiguous image of dof_state (pos, vel pairs)
@@ -119,13 +125,14 @@ struct KukaPostSmem {
   float obs[kTile * kObs];            // row-major tile, leaves as one contiguous run
   float xch[8 * kTile];               // [q][e]: cur[0..3], kp_max, sum|vel| arm, sum|vel| hand
   unsigned long long mbar[2];         // transaction barriers of the bulk-copied stages
+  const float* rowp[13 + 13 + kT1 * 7];   // component planes: source of staged row r at env 0 (palm 0..12, object 13..25, tips 26..53)
 };
 // a tile whose inputs arrive by bulk copies: component planes, full tile, 16-byte aligned plane rows
 __device__ __forceinline__ bool kuka_post_bulk_tile(bool soa, int n_envs, int env0) {
   return (HA_BULK_ROWS || HA_BULK_IMAGES) && soa && (n_envs & 3) == 0 && n_envs - env0 >= kTile;
 }
 static_assert(sizeof(KukaPostStage<4>) % 16 == 0 && sizeof(KukaPostStage<1>) % 16 == 0, "stage must keep 16-byte alignment");
-static_assert((kTile * 13 * 2 + kTile * 29 + kTile * 7) % 4 == 0, "kp image must be 16-byte aligned inside the stage");
+static_assert((kTile * 13 * 2 + kTile * 29 + kTile * 13) % 4 == 0, "kp image must be 16-byte aligned inside the stage");
 
 // per-lane statistic partials carried across the tiles of a persistent CTA (warp 3 only)
 struct KukaPostAcc {
@@ -283,7 +290,7 @@ __global__ void __launch_bounds__(kThreads) kuka_stats_finalize_kernel(const __g
 // Issue the cp.async copies of one tile (all 128 threads).  Idle envs of a ragged last tile re-read the last valid env.
 template <int K, bool SOA>
 __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaKukaBuffers& b, KukaPostStage<K>& s, const int env0,
-                                                const int nvalid, const int tid, unsigned long long* bar) {
+                                                const int nvalid, const int tid, unsigned long long* bar, const float* const* rowp) {
   using S = KukaPostStage<K>;
   const int last = nvalid - 1;
   const bool bulk = kuka_post_bulk_tile(SOA, p.n_envs, env0);
@@ -311,13 +318,12 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
         if (tid + 32 < kRows) bulk_g2s(row_dst(tid + 32), row_src(tid + 32), kTile * 4, bar);
       }
     } else if (nvalid == kTile && (p.n_envs & 3) == 0) {       // plane rows are 16-byte aligned: 8 x 16-byte copies per row
+      // staged rows are contiguous (palm, obj, tip images follow each other: row r at 32 * r floats), sources come from the CTA's table
+      static_assert(offsetof(S, obj) == 13 * kTile * 4 && offsetof(S, tip) == 26 * kTile * 4, "row images must be contiguous");
 #pragma unroll
       for (int i = 0; i < (kRows * 8 + kPostThreads - 1) / kPostThreads; ++i) {
         const int q = tid + kPostThreads * i;
-        if (q < kRows * 8) {
-          const int r = q >> 3, ch = q & 7;
-          cp_async16(row_dst(r) + 4 * ch, row_src(r) + 4 * ch);
-        }
+        if (q < kRows * 8) cp_async16(s.palm + 4 * q, rowp[q >> 3] + env0 + 4 * (q & 7));
       }
     } else {
       for (int q = tid; q < kRows * kTile; q += kPostThreads) {
@@ -357,14 +363,12 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
     }
   }
   }   // !SOA
-  {   // goal pose rows (7 of 13 floats)
-#pragma unroll
-    for (int i = 0; i < (kTile * 7 + kPostThreads - 1) / kPostThreads; ++i) {
-      const int j = tid + kPostThreads * i;
-      if (j < kTile * 7) {
-        const int e = j / 7, c = j - 7 * e;
-        cp_async4(s.goal + j, b.goal_states + (size_t)(env0 + min(e, last)) * 13 + c);
-      }
+  if (nvalid == kTile) {   // goal rows: the tile's 32 x 13 floats are one contiguous, 16-byte aligned run (whole lines are fetched anyway)
+    if (tid < kTile * 13 / 4) cp_async16(s.goal + 4 * tid, b.goal_states + (size_t)env0 * 13 + 4 * tid);
+  } else {                 // ragged last tile: pose columns only
+    for (int j = tid; j < kTile * 7; j += kPostThreads) {
+      const int e = j / 7, c = j - 7 * e;
+      cp_async4(s.goal + e * 13 + c, b.goal_states + (size_t)(env0 + min(e, last)) * 13 + c);
     }
   }
   const float* kp_src = b.object_keypoint_offsets + (size_t)env0 * 3 * K;
@@ -462,12 +466,24 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     b.dynamic->rng_step = b.dynamic->rng_step + 1;
   }
   KukaPostAcc acc;
-  if constexpr (SOA && (HA_BULK_ROWS || HA_BULK_IMAGES)) {
-    if (tid == 0) { mbar_init(&sm.mbar[0], 1); mbar_init(&sm.mbar[1], 1); mbar_fence_init(); }
+  if constexpr (SOA) {
+    if (HA_BULK_ROWS || HA_BULK_IMAGES) {
+      if (tid == 0) { mbar_init(&sm.mbar[0], 1); mbar_init(&sm.mbar[1], 1); mbar_fence_init(); }
+    }
+    // plane-row sources of the staged rows, decoded once per CTA (the per-tile issue then costs one shared load per copy)
+    if (tid < 13 + 13 + kT1 * 7) {
+      const size_t nn = (size_t)n;
+      const int r = tid;
+      const float* src;
+      if (r < 13) src = b.rigid_body_state + ((size_t)p.palm_body[0] * 13 + r) * nn;
+      else if (r < 26) src = b.root_state + ((size_t)p.object_slot * 13 + (r - 13)) * nn;
+      else { const int rr = r - 26, t = rr / 7, c = rr - 7 * t; src = b.rigid_body_state + ((size_t)p.tip_body[t] * 13 + c) * nn; }
+      sm.rowp[r] = src;
+    }
     __syncthreads();
   }
 
-  if (tile < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[0], tile * kTile, min(kTile, n - tile * kTile), tid, &sm.mbar[0]);
+  if (tile < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[0], tile * kTile, min(kTile, n - tile * kTile), tid, &sm.mbar[0], sm.rowp);
   cp_async_commit();
 
   for (int it = 0; tile < n_tiles; ++it, tile += stride) {
@@ -477,16 +493,22 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     const bool valid = lane < nvalid;
     const int env = env0 + min(lane, nvalid - 1);       // idle lanes of a ragged tile re-read a valid env; stores are predicated
     const int next = tile + stride;
-    if constexpr (NS == 2) {   // next tile's copies go in flight before this tile is touched
-      if (next < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid, &sm.mbar[(it + 1) & 1]);
+    if constexpr (NS == 2 && !HA_LATE_PREFETCH) {   // next tile's copies go in flight before this tile is touched
+      if (next < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid, &sm.mbar[(it + 1) & 1], sm.rowp);
       cp_async_commit();
     }
     KukaPostEnvState r;
     if (warp == 3) kuka_post_load_env<OBS, L.reward>(p, b, env, mode, r);
     if (HA_BULK_STORE && tid == 0) bulk_wait_read0();   // the previous tile's bulk store has read the obs tile
-    cp_async_wait<NS - 1>();
+    cp_async_wait<(NS == 2 && !HA_LATE_PREFETCH) ? 1 : 0>();
     if (kuka_post_bulk_tile(SOA, n, env0)) mbar_wait(&sm.mbar[NS == 2 ? (it & 1) : 0], NS == 2 ? (it >> 1) & 1 : it & 1);
     __syncthreads();                                    // B1: this tile's inputs are in shared memory
+    if constexpr (NS == 2 && HA_LATE_PREFETCH) {
+      // The next tile's reads start now, so they share the memory system with this tile's stores instead of with this tile's own
+      // reads: issued up front, both stages of every CTA land together (the whole input, ~3.5 us) and only then do the stores start.
+      if (next < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[(it + 1) & 1], next * kTile, min(kTile, n - next * kTile), tid, &sm.mbar[(it + 1) & 1], sm.rowp);
+      cp_async_commit();
+    }
 
     float* o = sm.obs + lane * OBS;
     const float clamp_c = p.clamp_abs_obs;                // clamp_obs (:1174-1176) / vec_task.py:432, applied where a value is produced
@@ -514,7 +536,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       }
     } else if (warp == 1) {
       // keypoints (:1057-1073)
-      const float* gl = S.goal + lane * 7;
+      const float* gl = S.goal + lane * 13;
       const f3 pc = f3{PALM(0), PALM(1), PALM(2)} + quat_rotate(f4{PALM(3), PALM(4), PALM(5), PALM(6)}, f3{p.palm_offset[0], p.palm_offset[1], p.palm_offset[2]});
       const f3 obj_pos = {OBJ(0), OBJ(1), OBJ(2)}, goal_pos = {gl[0], gl[1], gl[2]};
       const f4 obj_rot = {OBJ(3), OBJ(4), OBJ(5), OBJ(6)}, goal_rot = {gl[3], gl[4], gl[5], gl[6]};
@@ -567,6 +589,33 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       for (int c = 0; c < 3; ++c) W(L.scales + c, S.scales[lane * 3 + c]);
     }
     __syncthreads();                                    // B2: distances, kp_max and |vel| sums are visible to warp 3
+
+    // Observation tile store, split in two: every 128-bit word that holds none of the columns the state warp still has to write
+    // (closest_kp .. reward, the last 9 of a row) is complete now and leaves through the three other warps while the state warp
+    // runs the reward chain; the 3 remaining words per row follow after B3.
+    constexpr int kLate0 = HA_EARLY_STORE ? L.closest_kp - 3 : 0;              // first column offset of a word that overlaps the late columns
+    const bool clamp_here = do_clamp && !HA_BULK_STORE;
+    float4* obs_dst = reinterpret_cast<float4*>(b.obs_buf + (size_t)env0 * OBS);   // 16-byte aligned: env0 % 32 == 0
+    const float4* obs_src = reinterpret_cast<const float4*>(sm.obs);
+    const int obs_total = nvalid * OBS, obs_nvec = obs_total >> 2;
+    auto store_word = [&](int q) {
+      float4 v = obs_src[q];
+      if (clamp_here) {
+        v.x = fminf(fmaxf(v.x, -clamp_c), clamp_c); v.y = fminf(fmaxf(v.y, -clamp_c), clamp_c);
+        v.z = fminf(fmaxf(v.z, -clamp_c), clamp_c); v.w = fminf(fmaxf(v.w, -clamp_c), clamp_c);
+      }
+      obs_dst[q] = v;
+    };
+    if (HA_EARLY_STORE && !HA_BULK_STORE && warp != 3) {
+      constexpr int kStep = kPostThreads - 32, kColStep = (4 * kStep) % OBS;   // column offset of a thread's next word
+      int q = warp * 32 + lane, c = (4 * q) % OBS;
+#pragma unroll 2
+      for (; q < obs_nvec; q += kStep) {
+        if (c < kLate0) store_word(q);
+        c += kColStep;
+        c -= (c >= OBS) ? OBS : 0;
+      }
+    }
 
     if (warp == 3) {
       float cur[kT1];
@@ -697,33 +746,25 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
         bulk_commit();
       }
     } else {
-      // obs tile: clamp (unless the roles already did) and store as one contiguous run of 128-bit words
-      const bool clamp_here = do_clamp && !HA_BULK_STORE;
-      const float c = clamp_c;
-      float4* dst = reinterpret_cast<float4*>(b.obs_buf + (size_t)env0 * OBS);   // 16-byte aligned: env0 % 32 == 0
-      const float4* src = reinterpret_cast<const float4*>(sm.obs);
-      const int total = nvalid * OBS, nvec = total >> 2;
-      const int sid = warp * 32 + lane, nst = kPostThreads;
+      if (!HA_EARLY_STORE) {
 #pragma unroll 2
-      for (int q = sid; q < nvec; q += nst) {
-        float4 v = src[q];
-        if (clamp_here) {
-          v.x = fminf(fmaxf(v.x, -c), c); v.y = fminf(fmaxf(v.y, -c), c);
-          v.z = fminf(fmaxf(v.z, -c), c); v.w = fminf(fmaxf(v.w, -c), c);
-        }
-        dst[q] = v;
+        for (int q = tid; q < obs_nvec; q += kPostThreads) store_word(q);
+      } else if (tid < 3 * kTile) {   // the words that overlap the late columns: 3 per row
+        const int r = tid / 3, j = tid - 3 * r;
+        const int q = (OBS * r + kLate0 + 3) / 4 + j;
+        if (q < obs_nvec) store_word(q);
       }
-      const int f = (nvec << 2) + sid;                  // ragged last tile: up to 3 trailing floats
-      if (f < total) {
+      const int f = (obs_nvec << 2) + tid;              // ragged last tile: up to 3 trailing floats
+      if (f < obs_total) {
         float v = sm.obs[f];
-        if (clamp_here) v = fminf(fmaxf(v, -c), c);
+        if (clamp_here) v = fminf(fmaxf(v, -clamp_c), clamp_c);
         b.obs_buf[(size_t)env0 * OBS + f] = v;
       }
     }
     if constexpr (NS == 1) {
       if (next < n_tiles) {
         __syncthreads();                                // every warp is done with the stage and the obs tile
-        kuka_post_issue<K, SOA>(p, b, sm.st[0], next * kTile, min(kTile, n - next * kTile), tid, &sm.mbar[0]);
+        kuka_post_issue<K, SOA>(p, b, sm.st[0], next * kTile, min(kTile, n - next * kTile), tid, &sm.mbar[0], sm.rowp);
       }
       cp_async_commit();
     }
