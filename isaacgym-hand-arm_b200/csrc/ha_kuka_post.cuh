@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(kThreads) kuka_stats_finalize_kernel(const __g
 }
 
 // Issue the cp.async copies of one tile (all 128 threads).  Idle envs of a ragged last tile re-read the last valid env.
-template <int K, bool SOA>
+template <int K, bool SOA, int NT = kPostThreads>
 __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaKukaBuffers& b, KukaPostStage<K>& s, const int env0,
                                                 const int nvalid, const int tid, unsigned long long* bar, const float* const* rowp) {
   using S = KukaPostStage<K>;
@@ -321,12 +321,12 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
       // staged rows are contiguous (palm, obj, tip images follow each other: row r at 32 * r floats), sources come from the CTA's table
       static_assert(offsetof(S, obj) == 13 * kTile * 4 && offsetof(S, tip) == 26 * kTile * 4, "row images must be contiguous");
 #pragma unroll
-      for (int i = 0; i < (kRows * 8 + kPostThreads - 1) / kPostThreads; ++i) {
-        const int q = tid + kPostThreads * i;
+      for (int i = 0; i < (kRows * 8 + NT - 1) / NT; ++i) {
+        const int q = tid + NT * i;
         if (q < kRows * 8) cp_async16(s.palm + 4 * q, rowp[q >> 3] + env0 + 4 * (q & 7));
       }
     } else {
-      for (int q = tid; q < kRows * kTile; q += kPostThreads) {
+      for (int q = tid; q < kRows * kTile; q += NT) {
         const int r = q >> 5, e = q & 31;
         cp_async4(row_dst(r) + e, row_src(r) + min(e, last));
       }
@@ -335,8 +335,8 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
   {   // palm rows, 13 floats each
     const float* src = rb0 + (size_t)p.palm_body[0] * 13;
 #pragma unroll
-    for (int i = 0; i < (kTile * 13 + kPostThreads - 1) / kPostThreads; ++i) {
-      const int j = tid + kPostThreads * i;
+    for (int i = 0; i < (kTile * 13 + NT - 1) / NT; ++i) {
+      const int j = tid + NT * i;
       if (j < kTile * 13) {
         const int e = j / 13, c = j - 13 * e;
         cp_async4(s.palm + j, src + (size_t)min(e, last) * rbs + c);
@@ -345,8 +345,8 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
   }
   {   // object root rows
 #pragma unroll
-    for (int i = 0; i < (kTile * 13 + kPostThreads - 1) / kPostThreads; ++i) {
-      const int j = tid + kPostThreads * i;
+    for (int i = 0; i < (kTile * 13 + NT - 1) / NT; ++i) {
+      const int j = tid + NT * i;
       if (j < kTile * 13) {
         const int e = j / 13, c = j - 13 * e, env = env0 + min(e, last);
         const size_t row = p.root_regular ? (size_t)env * p.actors_per_env + p.object_slot : (size_t)__ldg(b.object_actor + env);
@@ -356,17 +356,19 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
   }
   {   // fingertip rows: pos + quat (7 of 13 floats)
 #pragma unroll
-    for (int i = 0; i < (kTile * kT1 * 7) / kPostThreads; ++i) {
-      const int j = tid + kPostThreads * i;
-      const int e = j / (kT1 * 7), r = j - (kT1 * 7) * e, t = r / 7, c = r - 7 * t;
-      cp_async4(s.tip + e * S::kTipW + r, rb0 + (size_t)min(e, last) * rbs + (size_t)p.tip_body[t] * 13 + c);
+    for (int i = 0; i < (kTile * kT1 * 7 + NT - 1) / NT; ++i) {
+      const int j = tid + NT * i;
+      if (j < kTile * kT1 * 7) {
+        const int e = j / (kT1 * 7), r = j - (kT1 * 7) * e, t = r / 7, c = r - 7 * t;
+        cp_async4(s.tip + e * S::kTipW + r, rb0 + (size_t)min(e, last) * rbs + (size_t)p.tip_body[t] * 13 + c);
+      }
     }
   }
   }   // !SOA
   if (nvalid == kTile) {   // goal rows: the tile's 32 x 13 floats are one contiguous, 16-byte aligned run (whole lines are fetched anyway)
     if (tid < kTile * 13 / 4) cp_async16(s.goal + 4 * tid, b.goal_states + (size_t)env0 * 13 + 4 * tid);
   } else {                 // ragged last tile: pose columns only
-    for (int j = tid; j < kTile * 7; j += kPostThreads) {
+    for (int j = tid; j < kTile * 7; j += NT) {
       const int e = j / 7, c = j - 7 * e;
       cp_async4(s.goal + e * 13 + c, b.goal_states + (size_t)(env0 + min(e, last)) * 13 + c);
     }
@@ -381,19 +383,19 @@ __device__ __forceinline__ void kuka_post_issue(const HaKukaParams& p, const HaK
   } else if (nvalid == kTile) {   // contiguous tiles: 16-byte copies (tile bases are 16-byte aligned: env0 % 32 == 0)
     constexpr int kKpVec = kTile * 3 * K / 4, kScVec = kTile * 3 / 4, kDofVec = kTile * 2 * kD1 / 4;
     if (tid < kKpVec) cp_async16(reinterpret_cast<float4*>(s.kp) + tid, reinterpret_cast<const float4*>(kp_src) + tid);
-    if (tid >= kPostThreads - kScVec) {
-      const int q = tid - (kPostThreads - kScVec);
+    if (tid >= NT - kScVec) {
+      const int q = tid - (NT - kScVec);
       cp_async16(reinterpret_cast<float4*>(s.scales) + q, reinterpret_cast<const float4*>(sc_src) + q);
     }
 #pragma unroll
-    for (int i = 0; i < (kDofVec + kPostThreads - 1) / kPostThreads; ++i) {
-      const int q = tid + kPostThreads * i;
+    for (int i = 0; i < (kDofVec + NT - 1) / NT; ++i) {
+      const int q = tid + NT * i;
       if (q < kDofVec) cp_async16(reinterpret_cast<float4*>(s.dof) + q, reinterpret_cast<const float4*>(dof_src) + q);
     }
   } else {                 // ragged last tile: element copies, nothing is read past the end of the arrays
-    for (int j = tid; j < nvalid * 3 * K; j += kPostThreads) cp_async4(s.kp + j, kp_src + j);
-    for (int j = tid; j < nvalid * 3; j += kPostThreads) cp_async4(s.scales + j, sc_src + j);
-    for (int j = tid; j < nvalid * 2 * kD1; j += kPostThreads) cp_async4(s.dof + j, dof_src + j);
+    for (int j = tid; j < nvalid * 3 * K; j += NT) cp_async4(s.kp + j, kp_src + j);
+    for (int j = tid; j < nvalid * 3; j += NT) cp_async4(s.scales + j, sc_src + j);
+    for (int j = tid; j < nvalid * 2 * kD1; j += NT) cp_async4(s.dof + j, dof_src + j);
   }
 }
 
