@@ -686,6 +686,32 @@ size_t ha_sizeof_noise_params(void);
 int ha_dr_noise_apply(const HaNoiseParams* p, const float* x, const float* corr, float* out, size_t count, const float* ext_white,
                       ha_stream_t stream);
 
+
+/* =====================================================================================================
+ * rl_games observer, episode_cumulative half: RLGPUAlgoObserver.process_infos
+ * (isaacgymenvs/utils/rlgames_utils.py:149-172) adds every step's per-env reward terms to running sums and, for each
+ * finished env in ascending env order, appends the sums to one deque(maxlen = games_to_track) per term (a Python loop with
+ * one .item() sync per finished env and term) and zeroes them; after_print_stats (:192-205) logs mean / min / max of each
+ * deque.  ha_observer_step does the per-step half in one launch from the done MASK (no nonzero(), no host sync): running sums
+ * += terms; finished envs get their deque position from an order-preserving scan over the grid and write ring slot
+ * (appended + rank) mod capacity when the deque would still hold them; ha_observer_summary reduces the ring to
+ * [mean, min, max][n_terms] on the device (one small copy to the host at logging time).
+ * ===================================================================================================== */
+#define HA_OBSERVER_MAX_TERMS 16
+#define HA_OBSERVER_MAX_CTAS 592
+typedef struct HaObserverBuffers {
+  const float* terms;      /* [n_terms, n_envs] this step's terms: the rows of extras["episode_cumulative"] */
+  const int64_t* dones;    /* [n_envs] non-zero = episode finished this step (the dones rl_games derives done_indices from) */
+  float* cumulative;       /* [n_terms, n_envs] running sums since each env's last finished episode; zero-initialised */
+  float* ring;             /* [n_terms, capacity] finished-episode sums, ring buffer == deque(maxlen=capacity) */
+  int64_t* state;          /* [4]: episodes appended so far, launch epoch, ticket, unused; zero-initialised */
+  int64_t* block_counts;   /* [HA_OBSERVER_MAX_CTAS] per-CTA finished-env counts tagged with the epoch; zero-initialised */
+  float* summary;          /* [3, n_terms] mean, min, max over the ring's valid entries (NaN while it is empty) */
+} HaObserverBuffers;
+size_t ha_sizeof_observer_buffers(void);
+int ha_observer_step(int32_t n_envs, int32_t n_terms, int32_t capacity, const HaObserverBuffers* b, ha_stream_t stream);
+int ha_observer_summary(int32_t n_terms, int32_t capacity, const HaObserverBuffers* b, ha_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -115,6 +115,7 @@ HaDexBuffers = STRUCTS["HaDexBuffers"]
 HaDexAdrTable = STRUCTS["HaDexAdrTable"]
 HaDexAdrBuffers = STRUCTS["HaDexAdrBuffers"]
 HaNoiseParams = STRUCTS["HaNoiseParams"]
+HaObserverBuffers = STRUCTS["HaObserverBuffers"]
 
 _lib = None
 
@@ -195,6 +196,12 @@ def load():
         raise HandArmLibraryError(f"struct HaNoiseParams: ctypes size {ctypes.sizeof(HaNoiseParams)} != C size {lib.ha_sizeof_noise_params()}")
     lib.ha_dr_noise_apply.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
                                       ctypes.c_void_p]
+    # rl_games observer
+    lib.ha_sizeof_observer_buffers.restype = ctypes.c_size_t
+    if ctypes.sizeof(HaObserverBuffers) != lib.ha_sizeof_observer_buffers():
+        raise HandArmLibraryError(f"struct HaObserverBuffers: ctypes size {ctypes.sizeof(HaObserverBuffers)} != C size {lib.ha_sizeof_observer_buffers()}")
+    lib.ha_observer_step.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_observer_summary.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
     _lib = lib
     return lib
 

@@ -709,3 +709,29 @@ def reference_adr_resample(env, c, table, mask: torch.Tensor, arnd: torch.Tensor
             assert len(rest) == 0, f"{len(rest)} scripted random tensors were not consumed (adr)"
     finally:
         cls.apply_randomizations, torch.randint = saved, old_randint
+
+
+def load_rlgames_utils() -> types.ModuleType:
+    """``isaacgymenvs/utils/rlgames_utils.py`` imported from where it lies (the real ``RLGPUAlgoObserver`` /
+    ``ComplexObsRLGPUEnv``).  rl_games is not installed here: ``rl_games.common`` is stubbed with an empty
+    ``AlgoObserver`` base class, which is all the observer inherits (its hooks are plain methods)."""
+    if "rlu" in _loaded:
+        return _loaded["rlu"]
+    load_reference()
+
+    class AlgoObserver:                                   # rl_games.common.algo_observer.AlgoObserver: hooks only
+        def __init__(self):
+            pass
+
+    rg = _stub("rl_games")
+    rg.common = _stub("rl_games.common", env_configurations=_Any(), vecenv=_Any())
+    rg.common.algo_observer = _stub("rl_games.common.algo_observer", AlgoObserver=AlgoObserver)
+    sys.modules["rl_games.common.vecenv"] = _stub("rl_games.common.vecenv", IVecEnv=object)
+    sys.modules["rl_games.common.env_configurations"] = _stub("rl_games.common.env_configurations")
+    rg.common.vecenv = sys.modules["rl_games.common.vecenv"]
+    rg.common.env_configurations = sys.modules["rl_games.common.env_configurations"]
+    sys.modules["isaacgymenvs.tasks"].isaacgym_task_map = {}
+    if not hasattr(sys.modules["gym"].spaces, "Space"):
+        sys.modules["gym"].spaces.Space = object              # only used in a type annotation
+    _loaded["rlu"] = importlib.import_module("isaacgymenvs.utils.rlgames_utils")
+    return _loaded["rlu"]
