@@ -712,6 +712,32 @@ size_t ha_sizeof_observer_buffers(void);
 int ha_observer_step(int32_t n_envs, int32_t n_terms, int32_t capacity, const HaObserverBuffers* b, ha_stream_t stream);
 int ha_observer_summary(int32_t n_terms, int32_t capacity, const HaObserverBuffers* b, ha_stream_t stream);
 
+
+/* =====================================================================================================
+ * Random network adversary of the DeXtreme tasks: RandomNetworkAdversary.forward
+ * (isaacgymenvs/utils/rna_util.py:124-150) and its call site get_random_network_adversary_action
+ * (allegro_hand_dextreme.py:864-879).  Chain per step: cat(dof_pos, object_pose_wrt_wrist) [N,23] -> fc1 + ReLU [N,512] ->
+ * fc1_1, * dropout_masks1 -> fc2 + ReLU [N,1024] -> fc2_1, * dropout_masks2 -> fc3 [N,16*32] -> softmax -> argmax over the 32
+ * bins -> gather(discretised_dofs).  The thin first layer (K = 23, no concatenation), the bias / ReLU / mask epilogues and the
+ * bias + argmax + gather tail are the kernels below; the four wide layers are fp32 GEMMs the host side issues between them
+ * (handarm_b200/rna.py).  The result is the DOF-space perturbation ha_dex_pre_step takes as rna_perturbation (it unscales and
+ * blends with rna_alpha, :879-889).
+ * ===================================================================================================== */
+#define HA_RNA_DOFS 16
+#define HA_RNA_BINS 32
+#define HA_RNA_IN_DIMS 23
+#define HA_RNA_FEATS1 512
+#define HA_RNA_FEATS2 1024
+/* out[N,512] = relu(cat(dof_state[:, :, 0], object_pose_wrt_wrist) @ w1^T + b1); dof_state [N,16,2], pose rows of 7 floats at
+ * pose_stride floats (7 if packed; 285 for the object_pose band of the DeXtreme observation rows), w1 [512,23] */
+int ha_rna_input_layer(int32_t n_envs, const float* dof_state, const float* object_pose_wrt_wrist, int32_t pose_stride, const float* w1, const float* b1,
+                       float* out, ha_stream_t stream);
+/* x[rows, cols] = (x + bias[cols]), then ReLU if relu != 0, then * mask[rows, cols] if mask != NULL; in place */
+int ha_rna_bias_act(float* x, const float* bias, const float* mask, int32_t relu, size_t rows, int32_t cols, ha_stream_t stream);
+/* out[N,16] = discretised_dofs[d, argmax_bin(logits[n, d, :] + bias3[d, :])]; idx_out: nullable [N,16] chosen bins */
+int ha_rna_select(int32_t n_envs, const float* logits, const float* bias3, const float* discretised_dofs, float* out, int32_t* idx_out,
+                  ha_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

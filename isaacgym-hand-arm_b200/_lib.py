@@ -202,6 +202,10 @@ def load():
         raise HandArmLibraryError(f"struct HaObserverBuffers: ctypes size {ctypes.sizeof(HaObserverBuffers)} != C size {lib.ha_sizeof_observer_buffers()}")
     lib.ha_observer_step.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_observer_summary.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
+    # random network adversary
+    lib.ha_rna_input_layer.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32] + [ctypes.c_void_p] * 4
+    lib.ha_rna_bias_act.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_size_t, ctypes.c_int32, ctypes.c_void_p]
+    lib.ha_rna_select.argtypes = [ctypes.c_int32] + [ctypes.c_void_p] * 6
     _lib = lib
     return lib
 

@@ -1,0 +1,141 @@
+// Random network adversary of the DeXtreme tasks (isaacgymenvs/utils/rna_util.py:37-150, call site
+// allegro_hand_dextreme.py:864-879): the hand-written ends of the chain.  The four wide layers in the middle are plain
+// fp32 library GEMMs issued by the host side (handarm_b200/rna.py); see include/handarm_b200.h.
+#include <cuda_runtime.h>
+
+#include "../../include/handarm_b200.h"
+#include "ha_device.cuh"
+#include "ha_host.h"
+
+namespace ha {
+
+constexpr int kRnaIn = HA_RNA_IN_DIMS;        // 16 joint angles + cube pose wrt wrist (pos3 quat4)
+constexpr int kRnaF1 = HA_RNA_FEATS1;         // 512
+
+// fc1 + ReLU (rna_util.py:126-127) without torch.cat: the 23 inputs of an env are read from dof_state ([N,16,2], pos) and
+// object_pose_wrt_wrist ([N,7]).  K = 23 is far too thin for a tensor-core tile: CTA = 32 envs x 512 features, the weight
+// matrix (47 KB) and the tile's inputs sit in shared memory, thread = 1 feature column x 32 envs... every weight is read once
+// per CTA from smem into registers and reused for the 32 envs.
+__global__ void __launch_bounds__(256)
+rna_input_layer_kernel(const int n_envs, const float* __restrict__ dof_state, const float* __restrict__ obj_pose, const int pose_stride,
+                       const float* __restrict__ w1, const float* __restrict__ b1, float* __restrict__ out) {
+  __shared__ float xs[32][kRnaIn + 1];
+  const int tid = threadIdx.x, env0 = blockIdx.x * 32;
+  const int nvalid = min(32, n_envs - env0);
+  for (int i = tid; i < 32 * kRnaIn; i += 256) {
+    const int e = i / kRnaIn, c = i - e * kRnaIn;
+    float v = 0.f;
+    if (e < nvalid) v = (c < 16) ? __ldg(dof_state + ((size_t)(env0 + e) * 16 + c) * 2) : __ldg(obj_pose + (size_t)(env0 + e) * pose_stride + (c - 16));
+    xs[e][c] = v;
+  }
+  __syncthreads();
+  // thread -> features f = tid, tid + 256: weights of a feature in registers, loop over the tile's envs
+#pragma unroll
+  for (int h = 0; h < kRnaF1 / 256; ++h) {
+    const int f = tid + 256 * h;
+    float w[kRnaIn];
+#pragma unroll
+    for (int c = 0; c < kRnaIn; ++c) w[c] = __ldg(w1 + (size_t)f * kRnaIn + c);
+    const float bias = __ldg(b1 + f);
+    for (int e = 0; e < nvalid; ++e) {
+      float acc = 0.f;
+#pragma unroll
+      for (int c = 0; c < kRnaIn; ++c) acc = fmaf(xs[e][c], w[c], acc);
+      out[(size_t)(env0 + e) * kRnaF1 + f] = fmaxf(acc + bias, 0.f);      // coalesced over f
+    }
+  }
+}
+
+// x = (x + bias) [relu] [* mask], in place, 128-bit accesses; cols % 4 == 0.
+// fc1_1 / fc2_1 + dropout mask (rna_util.py:128-129, :133-134: no activation before the mask), fc2 + ReLU (:131-132).
+__global__ void __launch_bounds__(256)
+rna_bias_act_kernel(float* __restrict__ x, const float* __restrict__ bias, const float* __restrict__ mask, const int relu,
+                    const size_t nvec, const int cols4) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) {
+    const int c = (int)(q % (size_t)cols4);
+    float4 v = reinterpret_cast<float4*>(x)[q];
+    const float4 bv = __ldg(reinterpret_cast<const float4*>(bias) + c);
+    v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+    if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+    if (mask) {
+      const float4 m = __ldg(reinterpret_cast<const float4*>(mask) + q);
+      v.x = m.x * v.x; v.y = m.y * v.y; v.z = m.z * v.z; v.w = m.w * v.w;
+    }
+    reinterpret_cast<float4*>(x)[q] = v;
+  }
+}
+
+// fc3 bias + softmax + argmax + gather (rna_util.py:136-139, allegro_hand_dextreme.py:871-876): softmax is monotone, so the bin
+// is the argmax of the logits (first maximum, as torch.argmax); out[env, d] = discretised_dofs[d, bin].  Warp = env, lane = bin.
+__global__ void __launch_bounds__(256)
+rna_select_kernel(const int n_envs, const float* __restrict__ logits, const float* __restrict__ bias3,
+                  const float* __restrict__ discretised, float* __restrict__ out, int32_t* __restrict__ idx_out) {
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x * (256 / 32) + (threadIdx.x >> 5);
+  if (env >= n_envs) return;
+  const float* row = logits + (size_t)env * (HA_RNA_DOFS * HA_RNA_BINS);
+  float res = 0.f;
+  int res_idx = 0;
+#pragma unroll
+  for (int d = 0; d < HA_RNA_DOFS; ++d) {
+    float v = row[d * HA_RNA_BINS + lane] + __ldg(bias3 + d * HA_RNA_BINS + lane);
+    int idx = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+      if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+    }
+    if (lane == d) { res = __ldg(discretised + d * HA_RNA_BINS + idx); res_idx = idx; }
+  }
+  if (lane < HA_RNA_DOFS) {
+    out[(size_t)env * HA_RNA_DOFS + lane] = res;
+    if (idx_out) idx_out[(size_t)env * HA_RNA_DOFS + lane] = res_idx;
+  }
+}
+
+}  // namespace ha
+
+extern "C" {
+
+int ha_rna_input_layer(int32_t n_envs, const float* dof_state, const float* object_pose_wrt_wrist, int32_t pose_stride, const float* w1, const float* b1,
+                       float* out, ha_stream_t stream) {
+  HA_REQUIRE(n_envs > 0, "n_envs must be positive (got %d)", n_envs);
+  HA_REQUIRE(dof_state && object_pose_wrt_wrist && w1 && b1 && out, "null pointer");
+  HA_REQUIRE(pose_stride >= 7, "pose_stride must be >= 7 floats (got %d)", pose_stride);
+  const int grid = (n_envs + 31) / 32;
+  return ha::check_cuda(ha::launch(ha::rna_input_layer_kernel, grid, 256, 0, (cudaStream_t)stream, (int)n_envs, dof_state, object_pose_wrt_wrist,
+                                   (int)pose_stride, w1, b1, out), "rna_input_layer_kernel launch");
+}
+
+int ha_rna_bias_act(float* x, const float* bias, const float* mask, int32_t relu, size_t rows, int32_t cols, ha_stream_t stream) {
+  HA_REQUIRE(x && bias, "null pointer");
+  HA_REQUIRE(cols > 0 && cols % 4 == 0, "cols must be a positive multiple of 4 (got %d)", cols);
+  HA_REQUIRE_ALIGNED16(x);
+  HA_REQUIRE_ALIGNED16(bias);
+  if (mask) HA_REQUIRE_ALIGNED16(mask);
+  if (rows == 0) return HA_OK;
+  const size_t nvec = rows * (size_t)(cols / 4);
+  static int sm_count = 0;
+  if (sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+  }
+  const size_t want = (nvec + 255) / 256;
+  const int grid = (int)(want < (size_t)sm_count * 8 ? want : (size_t)sm_count * 8);
+  return ha::check_cuda(ha::launch(ha::rna_bias_act_kernel, grid, 256, 0, (cudaStream_t)stream, x, bias, mask, (int)relu, nvec, (int)(cols / 4)),
+                        "rna_bias_act_kernel launch");
+}
+
+int ha_rna_select(int32_t n_envs, const float* logits, const float* bias3, const float* discretised_dofs, float* out, int32_t* idx_out,
+                  ha_stream_t stream) {
+  HA_REQUIRE(n_envs > 0, "n_envs must be positive (got %d)", n_envs);
+  HA_REQUIRE(logits && bias3 && discretised_dofs && out, "null pointer");
+  const int grid = (n_envs + 7) / 8;
+  return ha::check_cuda(ha::launch(ha::rna_select_kernel, grid, 256, 0, (cudaStream_t)stream, (int)n_envs, logits, bias3, discretised_dofs, out,
+                                   idx_out), "rna_select_kernel launch");
+}
+
+}  // extern "C"

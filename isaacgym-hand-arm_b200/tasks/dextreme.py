@@ -252,7 +252,16 @@ class AllegroHandDextremeADR(VecTask):
         self._dynamic[C["HA_DEX_DYN_RNG_SEED"]] = self._seed
         self.ext_rand: Optional[torch.Tensor] = None                   # parity mode: [N, HA_DEX_RND_STRIDE] raw draws (pre)
         self.ext_rand_post: Optional[torch.Tensor] = None              # parity mode: [N, HA_DEX_POST_RND_STRIDE] raw draws (post)
-        self.rna_perturbation: Optional[torch.Tensor] = None           # [N, 16] DOF-space output of the RNA network, if a caller runs one
+        self.rna_perturbation: Optional[torch.Tensor] = None           # [N, 16] DOF-space output of the RNA network
+        # random network adversary (:417-430): 32 bins per joint between the limits, network on the device
+        self.rna_network = None
+        self.run_rna = True                                            # parity harnesses that feed rna_perturbation themselves clear this
+        if self.enable_rna and torch.device(self.device).type == "cuda":
+            from ..rna import RandomNetworkAdversary
+            lo_l, hi_l = self.hand_dof_lower_limits.cpu(), self.hand_dof_upper_limits.cpu()
+            self.discretised_dofs = torch.stack([torch.linspace(float(lo_l[i]), float(hi_l[i]), steps=32) for i in range(16)]).to(self.device)
+            self.rna_network = RandomNetworkAdversary(self.num_envs, 16 + 7, 16, 32, self.device, seed=self._seed)
+            self.random_adversary_weight_sample_freq = self.cfg["env"]["random_network_adversary"]["weight_sample_freq"]
         self.obs_views: Dict[str, torch.Tensor] = {}                   # concatenated views emitted by K_post (set_obs_views)
         self.adr_resample_on_step = True                               # launch the per-env ADR resampling ahead of every K_pre
 
@@ -494,6 +503,10 @@ class AllegroHandDextremeADR(VecTask):
         self._rebind_sim_state()
         if self.randomize and self.use_adr and self.adr_resample_on_step:
             self.apply_randomizations(self.randomization_params, None, adr_objective=self.successes)      # (:926-937), mask derived in-kernel
+        if self.rna_network is not None and self.run_rna:                     # get_random_network_adversary_action (:864-876)
+            if self.last_step > 0 and self.last_step % self.random_adversary_weight_sample_freq == 0:
+                self.rna_network._refresh()
+            self.rna_perturbation = self.rna_network.perturbation(self.sim.dof_state, self.object_pose_wrt_wrist, self.discretised_dofs)
         rna = self.rna_perturbation
         rna_ptr = ctypes.c_void_p(rna.data_ptr()) if rna is not None else ctypes.c_void_p(0)
         _lib.check(self._lib.ha_dex_pre_step(ctypes.byref(self._params), ctypes.byref(self._buffers), ctypes.c_void_p(actions.data_ptr()),

@@ -1,0 +1,69 @@
+"""GPU: the random network adversary (``handarm_b200.rna`` on ``csrc/ha_rna.cu`` + library GEMMs) against the CPU oracle (pinned to
+the reference module) with the same weights and dropout masks.
+
+Tolerances: logits within 1e-4 relative to the row scale (fp32 GEMMs, summation order differs from the CPU's); the chosen bin is
+an argmax, so it must agree wherever the oracle's top-2 margin exceeds that tolerance (checked), and the disagreements that
+remain must pick a bin whose oracle logit is within the tolerance of the maximum."""
+import pytest
+import torch
+
+from oracle import rna_oracle as ro
+
+pytestmark = pytest.mark.gpu
+
+
+def _load(net, w):
+    for name in ("fc1", "fc1_1", "fc2", "fc2_1", "fc3"):
+        getattr(net, name).weight.copy_(w[name + ".weight"])
+        getattr(net, name).bias.copy_(w[name + ".bias"])
+    net.dropout_masks1.copy_(w["dropout_masks1"])
+    net.dropout_masks2.copy_(w["dropout_masks2"])
+    net._wt = None
+
+
+@pytest.mark.parametrize("n", [1, 33, 1000, 4096])
+def test_rna_matches_oracle(n):
+    from handarm_b200.rna import RandomNetworkAdversary
+    g = torch.Generator().manual_seed(5)
+    w = ro.make_weights(n, seed=9)
+    dof_pos = torch.rand(n, 16, generator=g) * 1.5 - 0.3
+    dof_vel = torch.randn(n, 16, generator=g)
+    pose = torch.cat([torch.randn(n, 3, generator=g) * 0.1, torch.nn.functional.normalize(torch.randn(n, 4, generator=g), dim=-1)], dim=-1)
+    lo, hi = -0.47 - torch.rand(16, generator=g) * 0.1, 1.6 + torch.rand(16, generator=g) * 0.1
+    disc = torch.stack([torch.linspace(float(lo[i]), float(hi[i]), steps=32) for i in range(16)])
+    want, want_idx, want_logits = ro.perturbation(w, dof_pos, pose, disc)
+
+    net = RandomNetworkAdversary(n, 23, 16, 32, "cuda:0")
+    _load(net, w)
+    dof_state = torch.stack([dof_pos, dof_vel], dim=-1).contiguous().cuda()
+    got = net.perturbation(dof_state, pose.cuda(), disc.cuda()).cpu()
+    got_idx = net.bins.cpu().long()
+    got_logits = (net._logits + net.fc3.bias).cpu().view(n, 16, 32)
+
+    scale = want_logits.abs().amax(dim=-1, keepdim=True).clamp_min(1e-6)
+    tol = 1e-4
+    assert ((got_logits - want_logits).abs() / scale).max() < tol
+    top2 = want_logits.topk(2, dim=-1).values
+    margin = (top2[..., 0] - top2[..., 1]) / scale[..., 0]
+    agree = got_idx == want_idx
+    assert agree[margin > 2 * tol].all()
+    chosen = want_logits.gather(-1, got_idx.unsqueeze(-1))[..., 0]
+    assert ((top2[..., 0] - chosen) / scale[..., 0] <= 2 * tol).all()
+    assert torch.equal(got[agree], want[agree])
+    # reference surface: softmax probabilities
+    probs = net(torch.cat([dof_pos, pose], dim=-1).cuda()).cpu()
+    assert torch.allclose(probs, torch.softmax(want_logits, dim=-1), rtol=1e-3, atol=1e-6)
+
+
+def test_rna_feeds_the_dextreme_pre_step():
+    """The task runs the network itself when the config enables it (random_network_adversary.enable, the default) and hands the
+    perturbation to the pre-physics kernel."""
+    from oracle import dextreme_oracle as dx
+    from tests.test_dextreme_parity_gpu import make_task
+    task = make_task(512, dx.DexConsts())
+    task.run_rna = True
+    assert task.enable_rna and task.rna_network is not None
+    task.step(torch.zeros(512, 16, device="cuda:0"))
+    assert task.rna_perturbation is not None and task.rna_perturbation.shape == (512, 16)
+    lo, hi = task.discretised_dofs[:, 0], task.discretised_dofs[:, -1]
+    assert (task.rna_perturbation >= lo - 1e-6).all() and (task.rna_perturbation <= hi + 1e-6).all()
