@@ -731,12 +731,23 @@ int ha_observer_summary(int32_t n_terms, int32_t capacity, const HaObserverBuffe
 /* out[N,512] = relu(cat(dof_state[:, :, 0], object_pose_wrt_wrist) @ w1^T + b1); dof_state [N,16,2], pose rows of 7 floats at
  * pose_stride floats (7 if packed; 285 for the object_pose band of the DeXtreme observation rows), w1 [512,23] */
 int ha_rna_input_layer(int32_t n_envs, const float* dof_state, const float* object_pose_wrt_wrist, int32_t pose_stride, const float* w1, const float* b1,
-                       float* out, ha_stream_t stream);
+                       float* out, void* out_hi, void* out_lo, ha_stream_t stream);   /* out fp32, or (out NULL) bf16 hi / lo planes */
 /* x[rows, cols] = (x + bias[cols]), then ReLU if relu != 0, then * mask[rows, cols] if mask != NULL; in place */
 int ha_rna_bias_act(float* x, const float* bias, const float* mask, int32_t relu, size_t rows, int32_t cols, ha_stream_t stream);
 /* out[N,16] = discretised_dofs[d, argmax_bin(logits[n, d, :] + bias3[d, :])]; idx_out: nullable [N,16] chosen bins */
 int ha_rna_select(int32_t n_envs, const float* logits, const float* bias3, const float* discretised_dofs, float* out, int32_t* idx_out,
                   ha_stream_t stream);
+
+/* Tensor-core path of the wide layers (csrc/ha_rna_tc.cu): tcgen05 / TMEM / TMA GEMMs on split-bf16 operands.  An fp32 tensor x
+ * travels as two bf16 planes hi = bf16(x), lo = bf16(x - hi); a layer accumulates A_hi.W_hi + A_hi.W_lo + A_lo.W_hi in fp32
+ * (~1e-5 of an fp32 GEMM).  Planes are [rows, cols] row-major bf16, 16-byte aligned; n % 128 == 0, k % 64 == 0. */
+int ha_rna_split_bf16(const float* x, void* hi, void* lo, size_t count, ha_stream_t stream);
+/* out planes [m, n] = split((A . W^T + bias) [relu] [* mask]); A planes [m, k], W planes [n, k] */
+int ha_rna_layer_tc(int32_t m, int32_t n, int32_t k, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, const float* bias,
+                    const float* mask, int32_t relu, void* out_hi, void* out_lo, ha_stream_t stream);
+/* last layer fused with the bin selection: out[m,16] = discretised_dofs[d, argmax_bin(A . W3^T + bias3)], W3 planes [512, k] */
+int ha_rna_select_tc(int32_t m, int32_t k, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, const float* bias3,
+                     const float* discretised_dofs, float* out, int32_t* idx_out, ha_stream_t stream);
 
 #ifdef __cplusplus
 }

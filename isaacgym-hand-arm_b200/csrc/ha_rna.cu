@@ -1,6 +1,7 @@
 // Random network adversary of the DeXtreme tasks (isaacgymenvs/utils/rna_util.py:37-150, call site
 // allegro_hand_dextreme.py:864-879): the hand-written ends of the chain.  The four wide layers in the middle are plain
 // fp32 library GEMMs issued by the host side (handarm_b200/rna.py); see include/handarm_b200.h.
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
 #include "../../include/handarm_b200.h"
@@ -18,7 +19,8 @@ constexpr int kRnaF1 = HA_RNA_FEATS1;         // 512
 // per CTA from smem into registers and reused for the 32 envs.
 __global__ void __launch_bounds__(256)
 rna_input_layer_kernel(const int n_envs, const float* __restrict__ dof_state, const float* __restrict__ obj_pose, const int pose_stride,
-                       const float* __restrict__ w1, const float* __restrict__ b1, float* __restrict__ out) {
+                       const float* __restrict__ w1, const float* __restrict__ b1, float* __restrict__ out,
+                       __nv_bfloat16* __restrict__ out_hi, __nv_bfloat16* __restrict__ out_lo) {
   __shared__ float xs[32][kRnaIn + 1];
   const int tid = threadIdx.x, env0 = blockIdx.x * 32;
   const int nvalid = min(32, n_envs - env0);
@@ -41,7 +43,15 @@ rna_input_layer_kernel(const int n_envs, const float* __restrict__ dof_state, co
       float acc = 0.f;
 #pragma unroll
       for (int c = 0; c < kRnaIn; ++c) acc = fmaf(xs[e][c], w[c], acc);
-      out[(size_t)(env0 + e) * kRnaF1 + f] = fmaxf(acc + bias, 0.f);      // coalesced over f
+      const float v = fmaxf(acc + bias, 0.f);
+      const size_t o = (size_t)(env0 + e) * kRnaF1 + f;                   // coalesced over f
+      if (out_hi) {                                                       // operand planes of the tensor-core layers
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        out_hi[o] = h;
+        out_lo[o] = __float2bfloat16_rn(v - __bfloat162float(h));
+      } else {
+        out[o] = v;
+      }
     }
   }
 }
@@ -100,13 +110,14 @@ rna_select_kernel(const int n_envs, const float* __restrict__ logits, const floa
 extern "C" {
 
 int ha_rna_input_layer(int32_t n_envs, const float* dof_state, const float* object_pose_wrt_wrist, int32_t pose_stride, const float* w1, const float* b1,
-                       float* out, ha_stream_t stream) {
+                       float* out, void* out_hi, void* out_lo, ha_stream_t stream) {
   HA_REQUIRE(n_envs > 0, "n_envs must be positive (got %d)", n_envs);
-  HA_REQUIRE(dof_state && object_pose_wrt_wrist && w1 && b1 && out, "null pointer");
+  HA_REQUIRE(dof_state && object_pose_wrt_wrist && w1 && b1 && (out || (out_hi && out_lo)), "null pointer");
   HA_REQUIRE(pose_stride >= 7, "pose_stride must be >= 7 floats (got %d)", pose_stride);
   const int grid = (n_envs + 31) / 32;
   return ha::check_cuda(ha::launch(ha::rna_input_layer_kernel, grid, 256, 0, (cudaStream_t)stream, (int)n_envs, dof_state, object_pose_wrt_wrist,
-                                   (int)pose_stride, w1, b1, out), "rna_input_layer_kernel launch");
+                                   (int)pose_stride, w1, b1, out, reinterpret_cast<__nv_bfloat16*>(out_hi), reinterpret_cast<__nv_bfloat16*>(out_lo)),
+                        "rna_input_layer_kernel launch");
 }
 
 int ha_rna_bias_act(float* x, const float* bias, const float* mask, int32_t relu, size_t rows, int32_t cols, ha_stream_t stream) {

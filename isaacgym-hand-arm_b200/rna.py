@@ -31,7 +31,11 @@ class _Linear:
 
 
 class RandomNetworkAdversary:
-    def __init__(self, num_envs: int, in_dims: int, out_dims: int, softmax_bins: int, device, seed: int = 0):
+    def __init__(self, num_envs: int, in_dims: int, out_dims: int, softmax_bins: int, device, seed: int = 0, impl: str = "tc"):
+        """``impl``: "tc" = hand-written tcgen05 layers on split-bf16 operands (``csrc/ha_rna_tc.cu``, the default);
+        "fp32" = fp32 library GEMMs between the hand-written ends (the first version, kept as the cross-check)."""
+        assert impl in ("tc", "fp32")
+        self.impl = impl
         if torch.device(device).type != "cuda":
             raise _lib.HandArmLibraryError("RandomNetworkAdversary needs a CUDA device: there is no CPU fallback")
         assert in_dims == C["HA_RNA_IN_DIMS"] and out_dims == C["HA_RNA_DOFS"] and softmax_bins == C["HA_RNA_BINS"], \
@@ -56,6 +60,9 @@ class RandomNetworkAdversary:
         self._h2 = torch.empty(N, self.num_feats2, **f)
         self._h2b = torch.empty(N, self.num_feats2, **f)
         self._logits = torch.empty(N, out_dims * softmax_bins, **f)
+        bf = dict(dtype=torch.bfloat16, device=device)
+        self._p1 = [torch.empty(N, self.num_feats1, **bf) for _ in range(4)]        # hi / lo planes of the 512-wide activations (two layers)
+        self._p2 = [torch.empty(N, self.num_feats2, **bf) for _ in range(4)]        # ... of the 1024-wide activations
         self.out = torch.empty(N, out_dims, **f)
         self.bins = torch.empty(N, out_dims, dtype=torch.int32, device=device)
         self._refresh()
@@ -72,6 +79,7 @@ class RandomNetworkAdversary:
             w = (torch.rand(lin.weight.shape, generator=self._gen) * 2 - 1) * bound
             lin.weight.copy_(w)
         self._wt = None
+        self._wsplit = None
 
     def refresh_dropout_masks(self):
         p = torch.rand(2, generator=self._gen)
@@ -88,6 +96,7 @@ class RandomNetworkAdversary:
         self.dropout_masks1.copy_(ref.dropout_masks1)
         self.dropout_masks2.copy_(ref.dropout_masks2)
         self._wt = None
+        self._wsplit = None
 
     # ---- forward ----------------------------------------------------------------------------------------------------------
     def _weights_t(self):
@@ -102,7 +111,8 @@ class RandomNetworkAdversary:
         st = ctypes.c_void_p(torch.cuda.current_stream(self.out.device).cuda_stream)
         P = lambda t: ctypes.c_void_p(t.data_ptr())
         w11, w2, w21, w3 = self._weights_t()
-        _lib.check(lib.ha_rna_input_layer(N, P(dof_state), P(object_pose_wrt_wrist), object_pose_wrt_wrist.stride(0), P(self.fc1.weight), P(self.fc1.bias), P(self._h1), st))
+        _lib.check(lib.ha_rna_input_layer(N, P(dof_state), P(object_pose_wrt_wrist), object_pose_wrt_wrist.stride(0), P(self.fc1.weight), P(self.fc1.bias), P(self._h1),
+                                          None, None, st))
         torch.mm(self._h1, w11, out=self._h1b)                                                        # fc1_1
         _lib.check(lib.ha_rna_bias_act(P(self._h1b), P(self.fc1_1.bias), P(self.dropout_masks1), 0, N, self.num_feats1, st))
         torch.mm(self._h1b, w2, out=self._h2)                                                         # fc2 + ReLU
@@ -112,8 +122,43 @@ class RandomNetworkAdversary:
         torch.mm(self._h2b, w3, out=self._logits)                                                     # fc3 (bias joins in the select kernel)
         return self._logits
 
+    def _weights_split(self):
+        """bf16 hi / lo planes of the four wide weight matrices ([out, in] row-major, as nn.Linear stores them)."""
+        if self._wsplit is None:
+            st = ctypes.c_void_p(torch.cuda.current_stream(self.out.device).cuda_stream)
+            self._wsplit = []
+            for lin in (self.fc1_1, self.fc2, self.fc2_1, self.fc3):
+                w = lin.weight.contiguous()
+                hi, lo = torch.empty_like(w, dtype=torch.bfloat16), torch.empty_like(w, dtype=torch.bfloat16)
+                _lib.check(self._lib.ha_rna_split_bf16(ctypes.c_void_p(w.data_ptr()), ctypes.c_void_p(hi.data_ptr()), ctypes.c_void_p(lo.data_ptr()),
+                                                       w.numel(), st))
+                self._wsplit.append((hi, lo))
+        return self._wsplit
+
+    def _perturbation_tc(self, dof_state, object_pose_wrt_wrist, discretised_dofs) -> torch.Tensor:
+        lib, N = self._lib, self.num_envs
+        assert dof_state.is_contiguous() and dof_state.numel() == N * 16 * 2
+        assert object_pose_wrt_wrist.shape == (N, 7) and object_pose_wrt_wrist.stride(1) == 1, "pose rows must be 7 consecutive floats"
+        st = ctypes.c_void_p(torch.cuda.current_stream(self.out.device).cuda_stream)
+        P = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+        (w11h, w11l), (w2h, w2l), (w21h, w21l), (w3h, w3l) = self._weights_split()
+        a_h, a_l, b_h, b_l = self._p1
+        c_h, c_l, d_h, d_l = self._p2
+        F1, F2 = self.num_feats1, self.num_feats2
+        _lib.check(lib.ha_rna_input_layer(N, P(dof_state), P(object_pose_wrt_wrist), object_pose_wrt_wrist.stride(0), P(self.fc1.weight),
+                                          P(self.fc1.bias), None, P(a_h), P(a_l), st))                                       # fc1 + ReLU
+        _lib.check(lib.ha_rna_layer_tc(N, F1, F1, P(a_h), P(a_l), P(w11h), P(w11l), P(self.fc1_1.bias), P(self.dropout_masks1), 0,
+                                       P(b_h), P(b_l), st))                                                                # fc1_1, * mask1
+        _lib.check(lib.ha_rna_layer_tc(N, F2, F1, P(b_h), P(b_l), P(w2h), P(w2l), P(self.fc2.bias), None, 1, P(c_h), P(c_l), st))      # fc2 + ReLU
+        _lib.check(lib.ha_rna_layer_tc(N, F2, F2, P(c_h), P(c_l), P(w21h), P(w21l), P(self.fc2_1.bias), P(self.dropout_masks2), 0,
+                                       P(d_h), P(d_l), st))                                                                # fc2_1, * mask2
+        _lib.check(lib.ha_rna_select_tc(N, F2, P(d_h), P(d_l), P(w3h), P(w3l), P(self.fc3.bias), P(discretised_dofs), P(self.out), P(self.bins), st))
+        return self.out
+
     def perturbation(self, dof_state: torch.Tensor, object_pose_wrt_wrist: torch.Tensor, discretised_dofs: torch.Tensor) -> torch.Tensor:
         """[N,16] joint-space value of the most likely bin per joint (``allegro_hand_dextreme.py:871-876``)."""
+        if self.impl == "tc":
+            return self._perturbation_tc(dof_state, object_pose_wrt_wrist, discretised_dofs)
         logits = self._logits_into(dof_state, object_pose_wrt_wrist)
         st = ctypes.c_void_p(torch.cuda.current_stream(self.out.device).cuda_stream)
         P = lambda t: ctypes.c_void_p(t.data_ptr())
