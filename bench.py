@@ -227,6 +227,10 @@ def measure_other(key, device, steps, blocks=4, snapshots=2):
     tasks, actions, post_b, pre_b = build_other(key, device, blocks, snapshots)
     n = OTHER_CONFIGS[key]["envs"]
     stream = torch.cuda.Stream()
+    has_rna = getattr(tasks[0], "rna_network", None) is not None
+    for t in tasks:                       # the memory-bound task kernels are timed on their own; the RNA chain (tensor cores) rides along below
+        if has_rna:
+            t.run_rna = False
     with torch.cuda.stream(stream):
         for t, a in zip(tasks, actions):
             for _ in range(3):
@@ -265,7 +269,22 @@ def measure_other(key, device, steps, blocks=4, snapshots=2):
         step_us = time_graph(graph_of("step"), reps)
         post_us = time_graph(graph_of("post"), reps)
         pre_us = time_graph(graph_of("pre"), reps)
-    return {"envs_per_gpu": n, "value": n / (step_us * 1e-6), "unit": UNIT, "ms_per_step": step_us * 1e-3, "steps": reps * per_graph,
+        rna = None
+        if has_rna:                       # DeXtreme default config: random_network_adversary.enable = True (allegro_hand_dextreme.py:864-879)
+            for t in tasks:
+                t.run_rna = True
+            for t, a in zip(tasks, actions):
+                one_step(t, a)
+            stream.synchronize()
+            rna_step_us = time_graph(graph_of("step"), max(4, reps // 4))
+            net = tasks[0].rna_network
+            rna_us = rna_step_us - step_us
+            rna = {"ms_per_step_with_rna": rna_step_us * 1e-3, "value_with_rna": n / (rna_step_us * 1e-6), "rna_ms": rna_us * 1e-3,
+                   "rna_gflop": net.flops_per_env() * n / 1e9, "rna_fp32_equiv_tflops": net.flops_per_env() * n / (rna_us * 1e-6) / 1e12,
+                   "rna_bf16_mma_tflops": 3 * (net.flops_per_env() - 2 * net.in_dims * net.num_feats1) * n / (rna_us * 1e-6) / 1e12,
+                   "rna_impl": "tcgen05 split-bf16 (3 MMAs per product), fused epilogues"}
+    out_extra = {"rna": rna} if rna else {}
+    return {**out_extra, "envs_per_gpu": n, "value": n / (step_us * 1e-6), "unit": UNIT, "ms_per_step": step_us * 1e-3, "steps": reps * per_graph,
             "bytes_per_env": post_b + pre_b, "step_frac": n * (post_b + pre_b) / (step_us * 1e-6) / 1e9 / hbm_gbs,
             "post_kernel_us": post_us, "post_frac": n * post_b / (post_us * 1e-6) / 1e9 / hbm_gbs, "pre_kernel_us": pre_us}
 
