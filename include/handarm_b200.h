@@ -740,11 +740,12 @@ int ha_rna_select(int32_t n_envs, const float* logits, const float* bias3, const
 
 /* Tensor-core path of the wide layers (csrc/ha_rna_tc.cu): tcgen05 / TMEM / TMA GEMMs on split-bf16 operands.  An fp32 tensor x
  * travels as two bf16 planes hi = bf16(x), lo = bf16(x - hi); a layer accumulates A_hi.W_hi + A_hi.W_lo + A_lo.W_hi in fp32
- * (~1e-5 of an fp32 GEMM).  Planes are [rows, cols] row-major bf16, 16-byte aligned; n % 128 == 0, k % 64 == 0. */
+ * (~1e-5 of an fp32 GEMM).  Planes are [rows, cols] row-major bf16, 16-byte aligned; n % 128 == 0, k % 32 == 0. */
 int ha_rna_split_bf16(const float* x, void* hi, void* lo, size_t count, ha_stream_t stream);
-/* out planes [m, n] = split((A . W^T + bias) [relu] [* mask]); A planes [m, k], W planes [n, k] */
+/* out planes [m, n] = split((A . W^T + bias) [relu] [* mask]); A planes [m, k], W planes [n, k];
+ * mask_bits: nullable [m, n / 32] words, bit j of word (row, c) = dropout mask {0, 1} of column 32 c + j */
 int ha_rna_layer_tc(int32_t m, int32_t n, int32_t k, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, const float* bias,
-                    const float* mask, int32_t relu, void* out_hi, void* out_lo, ha_stream_t stream);
+                    const uint32_t* mask_bits, int32_t relu, void* out_hi, void* out_lo, ha_stream_t stream);
 /* last layer fused with the bin selection: out[m,16] = discretised_dofs[d, argmax_bin(A . W3^T + bias3)], W3 planes [512, k] */
 int ha_rna_select_tc(int32_t m, int32_t k, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, const float* bias3,
                      const float* discretised_dofs, float* out, int32_t* idx_out, ha_stream_t stream);

@@ -8,8 +8,10 @@
 // exceeds that (tests/test_rna_gpu.py) -- at 3 bf16 MMAs per product instead of an fp32 SIMT GEMM (51 TFLOP/s measured for the
 // library fp32 path on B200).
 //
-// CTA = one 128 x 128 output tile, 6 warps: warp 0 lane 0 = TMA producer (3 stages of A 128x64 + W 128x64 bf16, 128-byte swizzle),
-// warp 1 = TMEM allocation, lane 0 = MMA issuer (4 x tcgen05.mma K=16 per stage, tcgen05.commit frees the stage), warps 2..5 =
+// CTA = one 128 x 128 output tile, 6 warps: warp 0 lane 0 = TMA producer (3 stages; a stage is one k-block of 32 with all four
+// operand tiles A_hi, A_lo, W_hi, W_lo of 128 x 32 bf16 in 64-byte swizzled rows, so each tile is fetched once for the three
+// products: 96 flop per L2 byte instead of 64 -- the first version, one (A, W) pair per stage, ran at the L2 -> SM bandwidth),
+// warp 1 = TMEM allocation, lane 0 = MMA issuer (3 products x 2 tcgen05.mma K=16 per stage, tcgen05.commit frees the stage), warps 2..5 =
 // epilogue: tcgen05.ld 32 columns at a time (thread = output row), then either
 //   kEpiAct     + bias, ReLU, * dropout mask, split to bf16 hi / lo planes (the next layer's operand), 64-byte stores
 //   kEpiSelect  + bias, argmax over the 32 bins of a joint (one tcgen05.ld chunk = one joint), gather from discretised_dofs
@@ -24,9 +26,11 @@
 
 namespace ha {
 
-constexpr int kBM = 128, kBN = 128, kBK = 64, kStages = 3, kUmmaK = 16;
+constexpr int kBM = 128, kBN = 128, kBK = 32, kStages = 3, kUmmaK = 16;
 constexpr int kTcThreads = 192;
-constexpr unsigned kStageBytes = (kBM * kBK + kBN * kBK) * 2;          // 32 KB
+constexpr unsigned kTileBytes = kBM * kBK * 2;                        // 8 KB: 128 rows of 64 bytes
+constexpr unsigned kStageBytes = 4 * kTileBytes;                       // A_hi, A_lo, W_hi, W_lo
+static_assert(kBM == kBN, "operand tiles share one box shape");
 constexpr unsigned kTmemCols = 128;
 enum { kEpiAct = 0, kEpiSelect = 1 };
 
@@ -54,10 +58,10 @@ __device__ __forceinline__ void tc_mma_bf16(unsigned d_tmem, unsigned long long 
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
       "}\n" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
-// shared-memory matrix descriptor: K-major tile of 128-byte rows, 128-byte swizzle, 8-row groups 1024 bytes apart
+// shared-memory matrix descriptor: K-major tile of 64-byte rows, 64-byte swizzle (layout type 4), 8-row groups 512 bytes apart
 __device__ __forceinline__ unsigned long long tc_smem_desc(const void* tile) {
   const unsigned long long addr = (unsigned long long)(smem_u32(tile) & 0x3FFFFu) >> 4;
-  return addr | (1ull << 16) | ((unsigned long long)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+  return addr | (1ull << 16) | ((unsigned long long)(512 >> 4) << 32) | (1ull << 46) | (4ull << 61);
 }
 // 32 lanes x 32 columns of fp32 accumulators: thread = lane (row), v[j] = column j
 __device__ __forceinline__ void tc_ld32(unsigned taddr, float (&v)[32]) {
@@ -82,7 +86,7 @@ __device__ __forceinline__ unsigned pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) 
 struct RnaTcArgs {
   int M, N, K;
   const float* bias;                 // [N]
-  const float* mask;                 // kEpiAct: nullable [M, N]
+  const uint32_t* mask_bits;         // kEpiAct: nullable [M, N / 32], bit j of word (row, c) = dropout mask of column 32 c + j
   int relu;
   __nv_bfloat16* out_hi;             // kEpiAct: [M, N] planes of the result
   __nv_bfloat16* out_lo;
@@ -101,7 +105,7 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
   RnaTcSmem& sm = *reinterpret_cast<RnaTcSmem*>(stages + (size_t)kStages * kStageBytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * kBN, m0 = blockIdx.y * kBM;
-  const int n_iters = 3 * (g.K / kBK);
+  const int n_iters = g.K / kBK;
 
   if (threadIdx.x == 0) {
 #pragma unroll
@@ -120,15 +124,16 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
 
   if (warp == 0) {
     if (lane == 0) {
-      // ===== TMA producer: per k-block three (A, W) pairs: (hi, hi), (hi, lo), (lo, hi) =====
+      // ===== TMA producer: the four operand tiles of a k-block =====
       for (int it = 0; it < n_iters; ++it) {
-        const int s = it % kStages, kb = it / 3, pass = it - 3 * kb;
+        const int s = it % kStages;
         mbar_wait(&sm.empty[s], ((it / kStages) & 1) ^ 1);
         mbar_arrive_expect_tx(&sm.full[s], kStageBytes);
-        unsigned char* a_dst = stages + (size_t)s * kStageBytes;
-        unsigned char* w_dst = a_dst + kBM * kBK * 2;
-        tma_load_2d(a_dst, pass < 2 ? &map_a_hi : &map_a_lo, kb * kBK, m0, &sm.full[s]);
-        tma_load_2d(w_dst, pass == 1 ? &map_w_lo : &map_w_hi, kb * kBK, n0, &sm.full[s]);
+        unsigned char* dst = stages + (size_t)s * kStageBytes;
+        tma_load_2d(dst, &map_a_hi, it * kBK, m0, &sm.full[s]);
+        tma_load_2d(dst + kTileBytes, &map_a_lo, it * kBK, m0, &sm.full[s]);
+        tma_load_2d(dst + 2 * kTileBytes, &map_w_hi, it * kBK, n0, &sm.full[s]);
+        tma_load_2d(dst + 3 * kTileBytes, &map_w_lo, it * kBK, n0, &sm.full[s]);
       }
     }
   } else if (warp == 1) {
@@ -140,11 +145,15 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
         const int s = it % kStages;
         mbar_wait(&sm.full[s], (it / kStages) & 1);
         tc_fence_after();
-        const unsigned char* a_src = stages + (size_t)s * kStageBytes;
-        const unsigned long long a_desc = tc_smem_desc(a_src), b_desc = tc_smem_desc(a_src + kBM * kBK * 2);
+        const unsigned char* src = stages + (size_t)s * kStageBytes;
+        const unsigned long long a_hi = tc_smem_desc(src), a_lo = tc_smem_desc(src + kTileBytes);
+        const unsigned long long w_hi = tc_smem_desc(src + 2 * kTileBytes), w_lo = tc_smem_desc(src + 3 * kTileBytes);
 #pragma unroll
-        for (int k = 0; k < kBK / kUmmaK; ++k)     // 32 bytes further along K inside the swizzle atom per K = 16 slice
-          tc_mma_bf16(tmem, a_desc + 2ull * k, b_desc + 2ull * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < kBK / kUmmaK; ++k) {   // 32 bytes further along K inside the swizzle atom per K = 16 slice
+          tc_mma_bf16(tmem, a_hi + 2ull * k, w_hi + 2ull * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          tc_mma_bf16(tmem, a_hi + 2ull * k, w_lo + 2ull * k, idesc, 1u);
+          tc_mma_bf16(tmem, a_lo + 2ull * k, w_hi + 2ull * k, idesc, 1u);
+        }
         tc_commit(&sm.empty[s]);                    // the stage is free once these MMAs have read it
       }
       tc_commit(&sm.tmem_full);                     // accumulators complete
@@ -171,13 +180,10 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
           }
-          if (g.mask) {
-            const float4* mrow = reinterpret_cast<const float4*>(g.mask + (size_t)row * g.N + col0);
+          if (g.mask_bits) {                           // dropout_masks * x (the mask is {0, 1}): one word per 32 columns
+            const unsigned m = __ldg(g.mask_bits + (size_t)row * (g.N >> 5) + (col0 >> 5));
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 m = __ldg(mrow + (j >> 2));
-              v[j] = m.x * v[j]; v[j + 1] = m.y * v[j + 1]; v[j + 2] = m.z * v[j + 2]; v[j + 3] = m.w * v[j + 3];
-            }
+            for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.0f * v[j];
           }
           unsigned hi[16], lo[16];
 #pragma unroll
@@ -247,16 +253,16 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// [rows, cols] row-major bf16, box = 64 columns (128 bytes, one swizzle atom) x 128 rows
+// [rows, cols] row-major bf16, box = 32 columns (64 bytes, one swizzle row) x 128 rows
 int make_map(CUtensorMap* map, const void* ptr, int rows, int cols) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return ha::set_error(HA_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)ha::kBK, (cuuint32_t)ha::kBM};
+  const cuuint32_t box[2] = {(cuuint32_t)ha::kBK, (cuuint32_t)ha::kBM};      // 32 columns = 64 bytes = one swizzle row
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return ha::set_error(HA_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows %d, cols %d)", (int)r, rows, cols);
   return HA_OK;
 }
@@ -302,11 +308,11 @@ int ha_rna_split_bf16(const float* x, void* hi, void* lo, size_t count, ha_strea
 }
 
 int ha_rna_layer_tc(int32_t m, int32_t n, int32_t k, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, const float* bias,
-                    const float* mask, int32_t relu, void* out_hi, void* out_lo, ha_stream_t stream) {
+                    const uint32_t* mask_bits, int32_t relu, void* out_hi, void* out_lo, ha_stream_t stream) {
   HA_REQUIRE(out_hi && out_lo, "null output");
-  HA_REQUIRE(ha::aligned16(out_hi) && ha::aligned16(out_lo) && (!mask || ha::aligned16(mask)), "outputs / mask must be 16-byte aligned");
+  HA_REQUIRE(ha::aligned16(out_hi) && ha::aligned16(out_lo), "outputs must be 16-byte aligned");
   ha::RnaTcArgs g = {};
-  g.M = m; g.N = n; g.K = k; g.bias = bias; g.mask = mask; g.relu = relu;
+  g.M = m; g.N = n; g.K = k; g.bias = bias; g.mask_bits = mask_bits; g.relu = relu;
   g.out_hi = reinterpret_cast<__nv_bfloat16*>(out_hi);
   g.out_lo = reinterpret_cast<__nv_bfloat16*>(out_lo);
   return launch_tc<ha::kEpiAct>(g, a_hi, a_lo, w_hi, w_lo, (cudaStream_t)stream);
