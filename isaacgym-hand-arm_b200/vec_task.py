@@ -187,6 +187,9 @@ class VecTask(Env):
         for _ in range(self.control_freq_inv):
             self.sim.simulate()
         self.post_physics_step()          # also fills timeout_buf and clips obs (vec_task.py:424, :432)
+        finalize = getattr(self, "finalize_stats", None)
+        if finalize is not None:          # extras of THIS step are exact when step() returns (a raw pre/post loop folds them one launch later)
+            finalize()
         self.control_steps += 1
         if self.dr_randomizations.get("observations", None):
             self.obs_buf = self.dr_randomizations["observations"]["noise_lambda"](self.obs_buf)
