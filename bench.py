@@ -203,6 +203,7 @@ def build_other(key, device, blocks, snapshots):
             cfg = hcfg.load_task_config(spec["task"], num_envs=n, sim_device=device)
             sim = hsim.SyntheticSim(n, dextreme.DEXTREME_LAYOUT, device, seed=seed, snapshots=snapshots)
             task = dextreme.AllegroHandDextremeADR(cfg, device, device, 0, True, sim=sim, seed=seed)      # create_sim fills the snapshots
+            task.adr_update_on_step = False      # the ADR range update reads its queue summary on the host (one sync): not capturable in a graph
         else:
             shadow = key == "cfg1_shadow_hand"
             cfg = hcfg.load_task_config(spec["task"], num_envs=n, sim_device=device)

@@ -750,6 +750,33 @@ int ha_rna_layer_tc(int32_t m, int32_t n, int32_t k, const void* a_hi, const voi
 int ha_rna_select_tc(int32_t m, int32_t k, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, const float* bias3,
                      const float* discretised_dofs, float* out, int32_t* idx_out, ha_stream_t stream);
 
+
+/* =====================================================================================================
+ * ADR range update, data half: adr_update (adr_vec_task.py:760-812) extends, per ADR parameter and bound, a
+ * deque(maxlen = adr_queue_threshold_length) with the objectives of the boundary workers that finished an episode, each via boolean
+ * masks, a gather and a .cpu().numpy().tolist() sync.  ha_adr_queue_step keeps all 2 * n_params queues as device rings: one
+ * order-preserving compaction of the finished boundary workers (ascending env index, as the boolean-mask gather lists them) and one
+ * launch with a CTA per queue that extends its ring and leaves [mean, length] in summary.  The host reads summary once per step and
+ * runs the scalar range logic (:814-870, handarm_b200/tasks/dextreme.py adr_update); clearing a queue = appended[q] = 0.
+ * ===================================================================================================== */
+#define HA_ADR_WORKER_ROLLOUT 0
+#define HA_ADR_WORKER_BOUNDARY 1
+typedef struct HaAdrQueueBuffers {
+  const int64_t* reset_buf;        /* [n_envs]  rand_env_mask = all_envs | (reset_buf & ~apply_reset_buf) */
+  const int64_t* apply_reset_buf;  /* [n_envs], nullable */
+  const int64_t* worker_types;     /* [n_envs] RolloutWorkerModes (before this step's recycle_envs) */
+  const int64_t* adr_modes;        /* [n_envs] queue index 2n (lower bound of parameter n) / 2n + 1 (upper) */
+  const float* objective;          /* [n_envs] adr_objective (successes) */
+  float* queues;                   /* [n_queues, capacity] rings */
+  int64_t* appended;               /* [n_queues] entries appended since the queue was last cleared; zero-initialised */
+  int32_t* list;                   /* [n_envs] scratch: finished boundary workers in env order */
+  int64_t* state;                  /* [4] scan state; zero-initialised */
+  int64_t* block_counts;           /* [HA_OBSERVER_MAX_CTAS]; zero-initialised */
+  double* summary;                 /* [n_queues, 2]: float64 mean (0 if empty), length */
+} HaAdrQueueBuffers;
+size_t ha_sizeof_adr_queue_buffers(void);
+int ha_adr_queue_step(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_t all_envs, const HaAdrQueueBuffers* b, ha_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

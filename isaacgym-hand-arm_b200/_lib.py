@@ -116,6 +116,7 @@ HaDexAdrTable = STRUCTS["HaDexAdrTable"]
 HaDexAdrBuffers = STRUCTS["HaDexAdrBuffers"]
 HaNoiseParams = STRUCTS["HaNoiseParams"]
 HaObserverBuffers = STRUCTS["HaObserverBuffers"]
+HaAdrQueueBuffers = STRUCTS["HaAdrQueueBuffers"]
 
 _lib = None
 
@@ -209,6 +210,11 @@ def load():
     lib.ha_rna_select_tc.argtypes = [ctypes.c_int32] * 2 + [ctypes.c_void_p] * 9
     lib.ha_rna_bias_act.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_size_t, ctypes.c_int32, ctypes.c_void_p]
     lib.ha_rna_select.argtypes = [ctypes.c_int32] + [ctypes.c_void_p] * 6
+    # ADR objective queues
+    lib.ha_sizeof_adr_queue_buffers.restype = ctypes.c_size_t
+    if ctypes.sizeof(HaAdrQueueBuffers) != lib.ha_sizeof_adr_queue_buffers():
+        raise HandArmLibraryError("struct HaAdrQueueBuffers: ctypes size != C size")
+    lib.ha_adr_queue_step.argtypes = [ctypes.c_int32] * 4 + [ctypes.c_void_p, ctypes.c_void_p]
     _lib = lib
     return lib
 

@@ -62,6 +62,13 @@ class AllegroHandDextremeADR(VecTask):
         self.adr_params = adr.get("params", {})
         self.worker_adr_boundary_fraction = adr.get("worker_adr_boundary_fraction", 0.4)
         self.adr_extended_boundary_sample = bool(adr.get("adr_extended_boundary_sample", False))
+        self.update_adr_ranges = bool(adr.get("update_adr_ranges", False))       # adr_vec_task.py:501-515
+        self.adr_queue_threshold_length = adr.get("adr_queue_threshold_length", 256)
+        self.adr_objective_threshold_low = adr.get("adr_objective_threshold_low", 5)
+        self.adr_objective_threshold_high = adr.get("adr_objective_threshold_high", 20)
+        self.adr_clear_other_queues = bool(adr.get("clear_other_queues", False))
+        self.adr_update_on_step = True       # run adr_update (one device->host copy per call) ahead of the resampling kernel
+        self._adr_updater = None
         for k, prm in self.adr_params.items():                               # adr_vec_task.py:530-545
             prm["range"] = list(prm["init_range"])
             prm.setdefault("limits", [None, None])
@@ -453,6 +460,20 @@ class AllegroHandDextremeADR(VecTask):
         v = self.adr_tensor_values[param_name]
         return v if env_ids is None else v[env_ids]
 
+    def adr_update(self, adr_objective: torch.Tensor, all_envs: bool = False) -> None:
+        """``ADRVecTask.adr_update`` (adr_vec_task.py:760-918) up to its recycle / resample tail (``ha_dex_adr_resample``, launched
+        right after by ``apply_randomizations``): objective queues on the device, one copy to the host, scalar range logic there
+        (``handarm_b200/adr.py``).  ``rand_envs`` is the mask the resampling kernel uses: ``reset_buf & ~apply_reset_buf``."""
+        if self._adr_updater is None:
+            from ..adr import AdrRangeUpdater
+            self._adr_updater = AdrRangeUpdater(self.adr_params, self.num_envs, self.device, self.worker_types, self.adr_modes,
+                                                self.adr_queue_threshold_length, self.adr_objective_threshold_low,
+                                                self.adr_objective_threshold_high, self.adr_clear_other_queues)
+        obj = adr_objective if adr_objective.dtype == torch.float32 else adr_objective.float()
+        log = self.last_step % 100 == 0
+        if self._adr_updater.update(self.reset_buf, self.apply_reset_buf, obj.contiguous(), all_envs=all_envs, extras=self.extras, log=log):
+            self.refresh_adr_table()
+
     def get_rna_alpha(self):
         return self.get_adr_tensor("rna_alpha").view(-1, 1)
 
@@ -463,6 +484,8 @@ class AllegroHandDextremeADR(VecTask):
         if self._adr_table is None:
             return
         self._require_engine()
+        if self.use_adr and self.update_adr_ranges and self.adr_update_on_step and adr_objective is not None:
+            self.adr_update(adr_objective, all_envs=self.first_randomization)
         self._adr_table.all_envs = 1 if self.first_randomization else 0
         self.first_randomization = False
         if self.ext_rand_adr is not None:
