@@ -19,6 +19,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include "../../include/handarm_b200.h"
 #include "ha_device.cuh"
@@ -95,6 +96,55 @@ struct RnaTcArgs {
   int32_t* idx_out;                  // kEpiSelect: nullable [M, 16]
 };
 
+// Epilogue of 32 consecutive columns [col0, col0 + 32) of one output row (v = fp32 accumulators of that row)
+template <int EPI>
+__device__ __forceinline__ void rna_epi_chunk(const RnaTcArgs& g, float (&v)[32], const int row, const int col0) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + col0 + j));
+    v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+  }
+  if (row < g.M) {
+    if constexpr (EPI == kEpiAct) {
+      if (g.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+      }
+      if (g.mask_bits) {                           // dropout_masks * x (the mask is {0, 1}): one word per 32 columns
+        const unsigned m = __ldg(g.mask_bits + (size_t)row * (g.N >> 5) + (col0 >> 5));
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.0f * v[j];
+      }
+      unsigned hi[16], lo[16];
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[j]), h1 = __float2bfloat16_rn(v[j + 1]);
+        const __nv_bfloat16 l0 = __float2bfloat16_rn(v[j] - __bfloat162float(h0)), l1 = __float2bfloat16_rn(v[j + 1] - __bfloat162float(h1));
+        hi[j >> 1] = pack_bf16(h0, h1);
+        lo[j >> 1] = pack_bf16(l0, l1);
+      }
+      uint4* dh = reinterpret_cast<uint4*>(g.out_hi + (size_t)row * g.N + col0);
+      uint4* dl = reinterpret_cast<uint4*>(g.out_lo + (size_t)row * g.N + col0);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+        dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+      }
+    } else {
+      // softmax is monotone: bin = first maximum of the logits (torch.argmax), value = discretised_dofs[d, bin]
+      const int d = col0 / HA_RNA_BINS;
+      float best = v[0];
+      int idx = 0;
+#pragma unroll
+      for (int j = 1; j < 32; ++j) {
+        if (v[j] > best) { best = v[j]; idx = j; }
+      }
+      g.out[(size_t)row * HA_RNA_DOFS + d] = __ldg(g.discretised + d * HA_RNA_BINS + idx);
+      if (g.idx_out) g.idx_out[(size_t)row * HA_RNA_DOFS + d] = idx;
+    }
+  }
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(kTcThreads, 2)
 rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
@@ -169,50 +219,7 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
       float v[32];
       tc_ld32(tmem + ((unsigned)(32 * q) << 16) + (unsigned)(32 * c), v);
       const int col0 = n0 + 32 * c;
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        const float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + col0 + j));
-        v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
-      }
-      if (row < g.M) {
-        if constexpr (EPI == kEpiAct) {
-          if (g.relu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-          }
-          if (g.mask_bits) {                           // dropout_masks * x (the mask is {0, 1}): one word per 32 columns
-            const unsigned m = __ldg(g.mask_bits + (size_t)row * (g.N >> 5) + (col0 >> 5));
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.0f * v[j];
-          }
-          unsigned hi[16], lo[16];
-#pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            const __nv_bfloat16 h0 = __float2bfloat16_rn(v[j]), h1 = __float2bfloat16_rn(v[j + 1]);
-            const __nv_bfloat16 l0 = __float2bfloat16_rn(v[j] - __bfloat162float(h0)), l1 = __float2bfloat16_rn(v[j + 1] - __bfloat162float(h1));
-            hi[j >> 1] = pack_bf16(h0, h1);
-            lo[j >> 1] = pack_bf16(l0, l1);
-          }
-          uint4* dh = reinterpret_cast<uint4*>(g.out_hi + (size_t)row * g.N + col0);
-          uint4* dl = reinterpret_cast<uint4*>(g.out_lo + (size_t)row * g.N + col0);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-            dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
-          }
-        } else {
-          // softmax is monotone: bin = first maximum of the logits (torch.argmax), value = discretised_dofs[d, bin]
-          const int d = col0 / HA_RNA_BINS;
-          float best = v[0];
-          int idx = 0;
-#pragma unroll
-          for (int j = 1; j < 32; ++j) {
-            if (v[j] > best) { best = v[j]; idx = j; }
-          }
-          g.out[(size_t)row * HA_RNA_DOFS + d] = __ldg(g.discretised + d * HA_RNA_BINS + idx);
-          if (g.idx_out) g.idx_out[(size_t)row * HA_RNA_DOFS + d] = idx;
-        }
-      }
+      rna_epi_chunk<EPI>(g, v, row, col0);
     }
     tc_fence_before();
   }
@@ -220,6 +227,123 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// Persistent version (the default): one CTA per SM walks 128 x 256 output tiles (tile = blockIdx.x, + gridDim.x, ...; the N tiles of
+// a row block are neighbours, so concurrent CTAs share their A rows in L2).  What it removes from the one-tile-per-CTA kernel
+// above, measured at 8-12 us of fixed cost per 24-37 us tile: barrier / TMEM set-up once per CTA instead of per tile, a TMA ring
+// that never drains between tiles (4 stages of 48 KB: A_hi, A_lo 128 x 32 and W_hi, W_lo 256 x 32), and two accumulator buffers
+// in TMEM (2 x 256 columns) so the epilogue of tile i runs under the main loop of tile i + 1.  N = 256 per MMA halves the A traffic
+// per flop (128 flop per L2 byte): the L2 -> SM path (~12 TB/s chip-wide) is what bounded the first version's main loop.
+constexpr int kPBN = 256, kPStages = 4;
+constexpr unsigned kPATile = kBM * kBK * 2, kPWTile = kPBN * kBK * 2;              // 8 KB, 16 KB
+constexpr unsigned kPStageBytes = 2 * kPATile + 2 * kPWTile;                       // 48 KB
+struct RnaTcPSmem {
+  unsigned long long full[kPStages], empty[kPStages], tmem_full[2], tmem_empty[2];
+  unsigned tmem_base;
+};
+constexpr size_t kTcPSmemBytes = 1024 + (size_t)kPStages * kPStageBytes + sizeof(RnaTcPSmem);
+
+template <int EPI>
+__global__ void __launch_bounds__(kTcThreads, 1)
+rna_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                              const __grid_constant__ CUtensorMap map_w_hi, const __grid_constant__ CUtensorMap map_w_lo,
+                              const __grid_constant__ RnaTcArgs g) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* stages = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  RnaTcPSmem& sm = *reinterpret_cast<RnaTcPSmem*>(stages + (size_t)kPStages * kPStageBytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_iters = g.K / kBK;
+  const int tiles_n = g.N / kPBN, tiles_m = (g.M + kBM - 1) / kBM, n_tiles = tiles_n * tiles_m;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < kPStages; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], 1); }
+#pragma unroll
+    for (int b = 0; b < 2; ++b) { mbar_init(&sm.tmem_full[b], 1); mbar_init(&sm.tmem_empty[b], 128); }
+    mbar_fence_init();
+  }
+  if (warp == 1) {                                   // all 512 TMEM columns: two 128 x 256 fp32 accumulator buffers
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const unsigned tmem = sm.tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer: runs ahead across tiles, bounded only by the ring =====
+      int git = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int m0 = (tile / tiles_n) * kBM, n0 = (tile % tiles_n) * kPBN;
+        for (int it = 0; it < n_iters; ++it, ++git) {
+          const int s = git % kPStages;
+          mbar_wait(&sm.empty[s], ((git / kPStages) & 1) ^ 1);
+          mbar_arrive_expect_tx(&sm.full[s], kPStageBytes);
+          unsigned char* dst = stages + (size_t)s * kPStageBytes;
+          tma_load_2d(dst, &map_a_hi, it * kBK, m0, &sm.full[s]);
+          tma_load_2d(dst + kPATile, &map_a_lo, it * kBK, m0, &sm.full[s]);
+          tma_load_2d(dst + 2 * kPATile, &map_w_hi, it * kBK, n0, &sm.full[s]);
+          tma_load_2d(dst + 2 * kPATile + kPWTile, &map_w_lo, it * kBK, n0, &sm.full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer: D = F32, A = B = BF16, K-major, M = 128, N = 256 =====
+      constexpr unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(kPBN >> 3) << 17) | ((unsigned)(kBM >> 4) << 24);
+      int git = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+        const int buf = lt & 1;
+        mbar_wait(&sm.tmem_empty[buf], ((lt >> 1) & 1) ^ 1);          // the epilogue has drained this accumulator buffer
+        tc_fence_after();
+        const unsigned d_tmem = tmem + (unsigned)(buf * kPBN);
+        for (int it = 0; it < n_iters; ++it, ++git) {
+          const int s = git % kPStages;
+          mbar_wait(&sm.full[s], (git / kPStages) & 1);
+          tc_fence_after();
+          const unsigned char* src = stages + (size_t)s * kPStageBytes;
+          const unsigned long long a_hi = tc_smem_desc(src), a_lo = tc_smem_desc(src + kPATile);
+          const unsigned long long w_hi = tc_smem_desc(src + 2 * kPATile), w_lo = tc_smem_desc(src + 2 * kPATile + kPWTile);
+#pragma unroll
+          for (int k = 0; k < kBK / kUmmaK; ++k) {
+            tc_mma_bf16(d_tmem, a_hi + 2ull * k, w_hi + 2ull * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+            tc_mma_bf16(d_tmem, a_hi + 2ull * k, w_lo + 2ull * k, idesc, 1u);
+            tc_mma_bf16(d_tmem, a_lo + 2ull * k, w_hi + 2ull * k, idesc, 1u);
+          }
+          tc_commit(&sm.empty[s]);
+        }
+        tc_commit(&sm.tmem_full[buf]);
+      }
+    }
+  } else {
+    // ===== epilogue warps: thread = output row, 8 chunks of 32 columns per tile =====
+    const int q = warp & 3;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+      const int buf = lt & 1;
+      const int m0 = (tile / tiles_n) * kBM, n0 = (tile % tiles_n) * kPBN;
+      const int row = m0 + 32 * q + lane;
+      mbar_wait(&sm.tmem_full[buf], (lt >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < kPBN / 32; ++c) {
+        float v[32];
+        tc_ld32(tmem + ((unsigned)(32 * q) << 16) + (unsigned)(buf * kPBN + 32 * c), v);
+        rna_epi_chunk<EPI>(g, v, row, n0 + 32 * c);
+      }
+      tc_fence_before();
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&sm.tmem_empty[buf])) : "memory");   // 128 arrivals free the buffer
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
   }
 }
 
@@ -254,12 +378,12 @@ EncodeTiledFn encode_fn() {
 }
 
 // [rows, cols] row-major bf16, box = 32 columns (64 bytes, one swizzle row) x 128 rows
-int make_map(CUtensorMap* map, const void* ptr, int rows, int cols) {
+int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int box_rows = ha::kBM) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return ha::set_error(HA_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)ha::kBK, (cuuint32_t)ha::kBM};      // 32 columns = 64 bytes = one swizzle row
+  const cuuint32_t box[2] = {(cuuint32_t)ha::kBK, (cuuint32_t)box_rows};      // 32 columns = 64 bytes = one swizzle row
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                         CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -268,7 +392,7 @@ int make_map(CUtensorMap* map, const void* ptr, int rows, int cols) {
 }
 
 template <int EPI>
-int launch_tc(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, cudaStream_t st) {
+int launch_tc_tiles(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, cudaStream_t st) {
   HA_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "M, N, K must be positive");
   HA_REQUIRE(g.N % ha::kBN == 0 && g.K % ha::kBK == 0, "N must be a multiple of %d and K of %d (got N %d, K %d)", ha::kBN, ha::kBK, g.N, g.K);
   HA_REQUIRE(a_hi && a_lo && w_hi && w_lo && g.bias, "null operand");
@@ -292,6 +416,49 @@ int launch_tc(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, const 
   cfg.dynamicSmemBytes = ha::kTcSmemBytes;
   cfg.stream = st;
   return ha::check_cuda(cudaLaunchKernelEx(&cfg, ha::rna_gemm_tc_kernel<EPI>, ma_hi, ma_lo, mw_hi, mw_lo, g), "rna_gemm_tc_kernel launch");
+}
+
+
+bool tc_persistent() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("HA_RNA_TC_TILES");     // tuning hook: 1 selects the one-tile-per-CTA kernel
+    v = (e && e[0] == '1') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+template <int EPI>
+int launch_tc(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, cudaStream_t st) {
+  if (!tc_persistent() || g.N % ha::kPBN != 0) return launch_tc_tiles<EPI>(g, a_hi, a_lo, w_hi, w_lo, st);
+  HA_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "M, N, K must be positive");
+  HA_REQUIRE(g.K % ha::kBK == 0, "K must be a multiple of %d (got %d)", ha::kBK, g.K);
+  HA_REQUIRE(a_hi && a_lo && w_hi && w_lo && g.bias, "null operand");
+  HA_REQUIRE(ha::aligned16(a_hi) && ha::aligned16(a_lo) && ha::aligned16(w_hi) && ha::aligned16(w_lo) && ha::aligned16(g.bias), "operands must be 16-byte aligned");
+  CUtensorMap ma_hi, ma_lo, mw_hi, mw_lo;
+  int rc;
+  if ((rc = make_map(&ma_hi, a_hi, g.M, g.K))) return rc;
+  if ((rc = make_map(&ma_lo, a_lo, g.M, g.K))) return rc;
+  if ((rc = make_map(&mw_hi, w_hi, g.N, g.K, ha::kPBN))) return rc;
+  if ((rc = make_map(&mw_lo, w_lo, g.N, g.K, ha::kPBN))) return rc;
+  static bool configured = false;
+  static int sm_count = 0;
+  if (!configured) {
+    rc = ha::check_cuda(cudaFuncSetAttribute(ha::rna_gemm_tc_persistent_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ha::kTcPSmemBytes),
+                        "cudaFuncSetAttribute(rna_gemm_tc_persistent_kernel)");
+    if (rc) return rc;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+    configured = true;
+  }
+  const int n_tiles = (g.N / ha::kPBN) * ((g.M + ha::kBM - 1) / ha::kBM);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(n_tiles < sm_count ? n_tiles : sm_count));
+  cfg.blockDim = dim3(ha::kTcThreads);
+  cfg.dynamicSmemBytes = ha::kTcPSmemBytes;
+  cfg.stream = st;
+  return ha::check_cuda(cudaLaunchKernelEx(&cfg, ha::rna_gemm_tc_persistent_kernel<EPI>, ma_hi, ma_lo, mw_hi, mw_lo, g), "rna_gemm_tc_persistent_kernel launch");
 }
 
 }  // namespace
