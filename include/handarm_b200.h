@@ -726,6 +726,7 @@ int ha_observer_summary(int32_t n_terms, int32_t capacity, const HaObserverBuffe
 #define HA_RNA_DOFS 16
 #define HA_RNA_BINS 32
 #define HA_RNA_IN_DIMS 23
+#define HA_RNA_IN_PAD 64          /* fc1's K padded with zeros to one tensor-core k-block */
 #define HA_RNA_FEATS1 512
 #define HA_RNA_FEATS2 1024
 /* out[N,512] = relu(cat(dof_state[:, :, 0], object_pose_wrt_wrist) @ w1^T + b1); dof_state [N,16,2], pose rows of 7 floats at
@@ -742,6 +743,10 @@ int ha_rna_select(int32_t n_envs, const float* logits, const float* bias3, const
  * travels as two bf16 planes hi = bf16(x), lo = bf16(x - hi); a layer accumulates A_hi.W_hi + A_hi.W_lo + A_lo.W_hi in fp32
  * (~1e-5 of an fp32 GEMM).  Planes are [rows, cols] row-major bf16, 16-byte aligned; n % 128 == 0, k % 32 == 0. */
 int ha_rna_split_bf16(const float* x, void* hi, void* lo, size_t count, ha_stream_t stream);
+/* fc1's A operand without torch.cat: planes [n_envs, HA_RNA_IN_PAD] = split([dof_state[:, :, 0] | pose | 0 ...]); fc1 then runs as
+ * ha_rna_layer_tc(n_envs, 512, HA_RNA_IN_PAD, ...) on W1 padded the same way */
+int ha_rna_input_planes(int32_t n_envs, const float* dof_state, const float* object_pose_wrt_wrist, int32_t pose_stride, void* out_hi, void* out_lo,
+                        ha_stream_t stream);
 /* out planes [m, n] = split((A . W^T + bias) [relu] [* mask]); A planes [m, k], W planes [n, k];
  * mask_bits: nullable [m, n / 32] words, bit j of word (row, c) = dropout mask {0, 1} of column 32 c + j */
 int ha_rna_layer_tc(int32_t m, int32_t n, int32_t k, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, const float* bias,

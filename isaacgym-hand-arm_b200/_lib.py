@@ -205,6 +205,7 @@ def load():
     lib.ha_observer_summary.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
     # random network adversary
     lib.ha_rna_input_layer.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32] + [ctypes.c_void_p] * 6
+    lib.ha_rna_input_planes.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_rna_split_bf16.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
     lib.ha_rna_layer_tc.argtypes = [ctypes.c_int32] * 3 + [ctypes.c_void_p] * 6 + [ctypes.c_int32] + [ctypes.c_void_p] * 3
     lib.ha_rna_select_tc.argtypes = [ctypes.c_int32] * 2 + [ctypes.c_void_p] * 9

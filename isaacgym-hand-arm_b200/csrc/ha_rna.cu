@@ -21,39 +21,63 @@ __global__ void __launch_bounds__(256)
 rna_input_layer_kernel(const int n_envs, const float* __restrict__ dof_state, const float* __restrict__ obj_pose, const int pose_stride,
                        const float* __restrict__ w1, const float* __restrict__ b1, float* __restrict__ out,
                        __nv_bfloat16* __restrict__ out_hi, __nv_bfloat16* __restrict__ out_lo) {
-  __shared__ float xs[32][kRnaIn + 1];
+  __shared__ __align__(16) float xs[32][24];            // 23 inputs + one zero pad: rows are read as six 128-bit broadcasts
   const int tid = threadIdx.x, env0 = blockIdx.x * 32;
   const int nvalid = min(32, n_envs - env0);
-  for (int i = tid; i < 32 * kRnaIn; i += 256) {
-    const int e = i / kRnaIn, c = i - e * kRnaIn;
+  for (int i = tid; i < 32 * 24; i += 256) {
+    const int e = i / 24, c = i - e * 24;
     float v = 0.f;
-    if (e < nvalid) v = (c < 16) ? __ldg(dof_state + ((size_t)(env0 + e) * 16 + c) * 2) : __ldg(obj_pose + (size_t)(env0 + e) * pose_stride + (c - 16));
+    if (e < nvalid && c < kRnaIn) v = (c < 16) ? __ldg(dof_state + ((size_t)(env0 + e) * 16 + c) * 2) : __ldg(obj_pose + (size_t)(env0 + e) * pose_stride + (c - 16));
     xs[e][c] = v;
   }
   __syncthreads();
-  // thread -> features f = tid, tid + 256: weights of a feature in registers, loop over the tile's envs
+  // thread -> the feature pair (2 tid, 2 tid + 1): both weight rows in registers, loop over the tile's envs; a warp stores 128
+  // contiguous bytes per plane and env (bf16x2 per lane)
+  static_assert(kRnaF1 == 2 * 256, "one feature pair per thread");
+  const int f = 2 * tid;
+  float w0[kRnaIn], w1r[kRnaIn];
 #pragma unroll
-  for (int h = 0; h < kRnaF1 / 256; ++h) {
-    const int f = tid + 256 * h;
-    float w[kRnaIn];
+  for (int c = 0; c < kRnaIn; ++c) { w0[c] = __ldg(w1 + (size_t)f * kRnaIn + c); w1r[c] = __ldg(w1 + (size_t)(f + 1) * kRnaIn + c); }
+  const float bias0 = __ldg(b1 + f), bias1 = __ldg(b1 + f + 1);
+  for (int e = 0; e < nvalid; ++e) {
+    float a0 = 0.f, a1 = 0.f;
+    float x[24];
 #pragma unroll
-    for (int c = 0; c < kRnaIn; ++c) w[c] = __ldg(w1 + (size_t)f * kRnaIn + c);
-    const float bias = __ldg(b1 + f);
-    for (int e = 0; e < nvalid; ++e) {
-      float acc = 0.f;
+    for (int c4 = 0; c4 < 6; ++c4) {
+      const float4 t = *reinterpret_cast<const float4*>(&xs[e][4 * c4]);
+      x[4 * c4] = t.x; x[4 * c4 + 1] = t.y; x[4 * c4 + 2] = t.z; x[4 * c4 + 3] = t.w;
+    }
 #pragma unroll
-      for (int c = 0; c < kRnaIn; ++c) acc = fmaf(xs[e][c], w[c], acc);
-      const float v = fmaxf(acc + bias, 0.f);
-      const size_t o = (size_t)(env0 + e) * kRnaF1 + f;                   // coalesced over f
-      if (out_hi) {                                                       // operand planes of the tensor-core layers
-        const __nv_bfloat16 h = __float2bfloat16_rn(v);
-        out_hi[o] = h;
-        out_lo[o] = __float2bfloat16_rn(v - __bfloat162float(h));
-      } else {
-        out[o] = v;
-      }
+    for (int c = 0; c < kRnaIn; ++c) { a0 = fmaf(x[c], w0[c], a0); a1 = fmaf(x[c], w1r[c], a1); }
+    const float v0 = fmaxf(a0 + bias0, 0.f), v1 = fmaxf(a1 + bias1, 0.f);
+    const size_t o = (size_t)(env0 + e) * kRnaF1 + f;
+    if (out_hi) {                                                         // operand planes of the tensor-core layers
+      const __nv_bfloat16 h0 = __float2bfloat16_rn(v0), h1 = __float2bfloat16_rn(v1);
+      __nv_bfloat162 hh, ll;
+      hh.x = h0; hh.y = h1;
+      ll.x = __float2bfloat16_rn(v0 - __bfloat162float(h0)); ll.y = __float2bfloat16_rn(v1 - __bfloat162float(h1));
+      *reinterpret_cast<__nv_bfloat162*>(out_hi + o) = hh;
+      *reinterpret_cast<__nv_bfloat162*>(out_lo + o) = ll;
+    } else {
+      *reinterpret_cast<float2*>(out + o) = make_float2(v0, v1);
     }
   }
+}
+
+// Operand planes of fc1 for the tensor-core path: row = [dof_pos 16 | object pose 7 | zeros to HA_RNA_IN_PAD], split to bf16 hi / lo.
+// One thread per (env, column); 4 MB written per step at 16384 envs.
+__global__ void __launch_bounds__(256)
+rna_input_planes_kernel(const int n_envs, const float* __restrict__ dof_state, const float* __restrict__ obj_pose, const int pose_stride,
+                        __nv_bfloat16* __restrict__ out_hi, __nv_bfloat16* __restrict__ out_lo) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_envs * HA_RNA_IN_PAD) return;
+  const int env = (int)(i / HA_RNA_IN_PAD), c = (int)(i - (size_t)env * HA_RNA_IN_PAD);
+  float v = 0.f;
+  if (c < 16) v = __ldg(dof_state + ((size_t)env * 16 + c) * 2);
+  else if (c < kRnaIn) v = __ldg(obj_pose + (size_t)env * pose_stride + (c - 16));
+  const __nv_bfloat16 h = __float2bfloat16_rn(v);
+  out_hi[i] = h;
+  out_lo[i] = __float2bfloat16_rn(v - __bfloat162float(h));
 }
 
 // x = (x + bias) [relu] [* mask], in place, 128-bit accesses; cols % 4 == 0.
@@ -118,6 +142,17 @@ int ha_rna_input_layer(int32_t n_envs, const float* dof_state, const float* obje
   return ha::check_cuda(ha::launch(ha::rna_input_layer_kernel, grid, 256, 0, (cudaStream_t)stream, (int)n_envs, dof_state, object_pose_wrt_wrist,
                                    (int)pose_stride, w1, b1, out, reinterpret_cast<__nv_bfloat16*>(out_hi), reinterpret_cast<__nv_bfloat16*>(out_lo)),
                         "rna_input_layer_kernel launch");
+}
+
+int ha_rna_input_planes(int32_t n_envs, const float* dof_state, const float* object_pose_wrt_wrist, int32_t pose_stride, void* out_hi, void* out_lo,
+                        ha_stream_t stream) {
+  HA_REQUIRE(n_envs > 0, "n_envs must be positive (got %d)", n_envs);
+  HA_REQUIRE(dof_state && object_pose_wrt_wrist && out_hi && out_lo, "null pointer");
+  HA_REQUIRE(pose_stride >= 7, "pose_stride must be >= 7 floats (got %d)", pose_stride);
+  const size_t count = (size_t)n_envs * HA_RNA_IN_PAD;
+  return ha::check_cuda(ha::launch(ha::rna_input_planes_kernel, (int)((count + 255) / 256), 256, 0, (cudaStream_t)stream, (int)n_envs, dof_state,
+                                   object_pose_wrt_wrist, (int)pose_stride, reinterpret_cast<__nv_bfloat16*>(out_hi), reinterpret_cast<__nv_bfloat16*>(out_lo)),
+                        "rna_input_planes_kernel launch");
 }
 
 int ha_rna_bias_act(float* x, const float* bias, const float* mask, int32_t relu, size_t rows, int32_t cols, ha_stream_t stream) {

@@ -97,11 +97,12 @@ struct RnaTcArgs {
 };
 
 // Epilogue of 32 consecutive columns [col0, col0 + 32) of one output row (v = fp32 accumulators of that row)
+// `bias32`: the 32 bias values of these columns (global or shared memory, 16-byte aligned)
 template <int EPI>
-__device__ __forceinline__ void rna_epi_chunk(const RnaTcArgs& g, float (&v)[32], const int row, const int col0) {
+__device__ __forceinline__ void rna_epi_chunk(const RnaTcArgs& g, float (&v)[32], const int row, const int col0, const float* bias32) {
 #pragma unroll
   for (int j = 0; j < 32; j += 4) {
-    const float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + col0 + j));
+    const float4 bv = *reinterpret_cast<const float4*>(bias32 + j);
     v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
   }
   if (row < g.M) {
@@ -117,11 +118,12 @@ __device__ __forceinline__ void rna_epi_chunk(const RnaTcArgs& g, float (&v)[32]
       }
       unsigned hi[16], lo[16];
 #pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[j]), h1 = __float2bfloat16_rn(v[j + 1]);
-        const __nv_bfloat16 l0 = __float2bfloat16_rn(v[j] - __bfloat162float(h0)), l1 = __float2bfloat16_rn(v[j + 1] - __bfloat162float(h1));
-        hi[j >> 1] = pack_bf16(h0, h1);
-        lo[j >> 1] = pack_bf16(l0, l1);
+      for (int j = 0; j < 32; j += 2) {          // packed conversions: one cvt.rn.bf16x2.f32 per pair; bf16 -> fp32 is a shift
+        const __nv_bfloat162 h = __floats2bfloat162_rn(v[j], v[j + 1]);
+        const unsigned hb = *reinterpret_cast<const unsigned*>(&h);
+        const __nv_bfloat162 l = __floats2bfloat162_rn(v[j] - __uint_as_float(hb << 16), v[j + 1] - __uint_as_float(hb & 0xffff0000u));
+        hi[j >> 1] = hb;
+        lo[j >> 1] = *reinterpret_cast<const unsigned*>(&l);
       }
       uint4* dh = reinterpret_cast<uint4*>(g.out_hi + (size_t)row * g.N + col0);
       uint4* dl = reinterpret_cast<uint4*>(g.out_lo + (size_t)row * g.N + col0);
@@ -219,7 +221,7 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
       float v[32];
       tc_ld32(tmem + ((unsigned)(32 * q) << 16) + (unsigned)(32 * c), v);
       const int col0 = n0 + 32 * c;
-      rna_epi_chunk<EPI>(g, v, row, col0);
+      rna_epi_chunk<EPI>(g, v, row, col0, g.bias + col0);
     }
     tc_fence_before();
   }
@@ -234,20 +236,35 @@ rna_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
 // Persistent version (the default): one CTA per SM walks 128 x 256 output tiles (tile = blockIdx.x, + gridDim.x, ...; the N tiles of
 // a row block are neighbours, so concurrent CTAs share their A rows in L2).  What it removes from the one-tile-per-CTA kernel
 // above, measured at 8-12 us of fixed cost per 24-37 us tile: barrier / TMEM set-up once per CTA instead of per tile, a TMA ring
-// that never drains between tiles (4 stages of 48 KB: A_hi, A_lo 128 x 32 and W_hi, W_lo 256 x 32), and two accumulator buffers
+// that never drains between tiles (stage = A_hi, A_lo 128 x kPBK and W_hi, W_lo 256 x kPBK), and two accumulator buffers
 // in TMEM (2 x 256 columns) so the epilogue of tile i runs under the main loop of tile i + 1.  N = 256 per MMA halves the A traffic
 // per flop (128 flop per L2 byte): the L2 -> SM path (~12 TB/s chip-wide) is what bounded the first version's main loop.
-constexpr int kPBN = 256, kPStages = 4;
-constexpr unsigned kPATile = kBM * kBK * 2, kPWTile = kPBN * kBK * 2;              // 8 KB, 16 KB
-constexpr unsigned kPStageBytes = 2 * kPATile + 2 * kPWTile;                       // 48 KB
+#ifndef HA_RNA_PBK
+#define HA_RNA_PBK 64      // k-block of the persistent kernel: 64 (128-byte swizzled rows, 2 stages of 96 KB) or 32 (64-byte rows, 4 stages of 48 KB)
+#endif
+constexpr int kPBN = 256, kPBK = HA_RNA_PBK, kPStages = (kPBK == 64) ? 2 : 4;
+constexpr unsigned kPATile = kBM * kPBK * 2, kPWTile = kPBN * kPBK * 2;
+constexpr unsigned kPStageBytes = 2 * kPATile + 2 * kPWTile;
+#ifndef HA_RNA_EPI_WARPS
+#define HA_RNA_EPI_WARPS 4    // epilogue warps of the persistent kernel (one per TMEM lane quarter); 16 (four per quarter) measured slower: 0.267 vs 0.253 ms
+#endif
+constexpr int kPEpiWarps = HA_RNA_EPI_WARPS, kPThreads = 64 + 32 * kPEpiWarps;
+static_assert(kPEpiWarps % 4 == 0 && (kPBN / 32) % (kPEpiWarps / 4) == 0, "epilogue warps split the column chunks of their lane quarter evenly");
+// K-major tile descriptor for the persistent kernel's row width: 128-byte rows / 128-byte swizzle (layout 2, 8-row groups 1024 bytes apart)
+__device__ __forceinline__ unsigned long long tc_smem_desc_p(const void* tile) {
+  if constexpr (kPBK == 32) return tc_smem_desc(tile);
+  const unsigned long long addr = (unsigned long long)(smem_u32(tile) & 0x3FFFFu) >> 4;
+  return addr | (1ull << 16) | ((unsigned long long)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
 struct RnaTcPSmem {
   unsigned long long full[kPStages], empty[kPStages], tmem_full[2], tmem_empty[2];
   unsigned tmem_base;
+  alignas(16) float bias[2][kPBN];     // the tile's bias slice per accumulator buffer, staged by the epilogue warps ahead of the wait
 };
 constexpr size_t kTcPSmemBytes = 1024 + (size_t)kPStages * kPStageBytes + sizeof(RnaTcPSmem);
 
 template <int EPI>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kPThreads, 1)
 rna_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                               const __grid_constant__ CUtensorMap map_w_hi, const __grid_constant__ CUtensorMap map_w_lo,
                               const __grid_constant__ RnaTcArgs g) {
@@ -255,14 +272,14 @@ rna_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a_hi, cons
   unsigned char* stages = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   RnaTcPSmem& sm = *reinterpret_cast<RnaTcPSmem*>(stages + (size_t)kPStages * kPStageBytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_iters = g.K / kBK;
+  const int n_iters = g.K / kPBK;
   const int tiles_n = g.N / kPBN, tiles_m = (g.M + kBM - 1) / kBM, n_tiles = tiles_n * tiles_m;
 
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int s = 0; s < kPStages; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], 1); }
 #pragma unroll
-    for (int b = 0; b < 2; ++b) { mbar_init(&sm.tmem_full[b], 1); mbar_init(&sm.tmem_empty[b], 128); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&sm.tmem_full[b], 1); mbar_init(&sm.tmem_empty[b], 32 * kPEpiWarps); }
     mbar_fence_init();
   }
   if (warp == 1) {                                   // all 512 TMEM columns: two 128 x 256 fp32 accumulator buffers
@@ -285,10 +302,10 @@ rna_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a_hi, cons
           mbar_wait(&sm.empty[s], ((git / kPStages) & 1) ^ 1);
           mbar_arrive_expect_tx(&sm.full[s], kPStageBytes);
           unsigned char* dst = stages + (size_t)s * kPStageBytes;
-          tma_load_2d(dst, &map_a_hi, it * kBK, m0, &sm.full[s]);
-          tma_load_2d(dst + kPATile, &map_a_lo, it * kBK, m0, &sm.full[s]);
-          tma_load_2d(dst + 2 * kPATile, &map_w_hi, it * kBK, n0, &sm.full[s]);
-          tma_load_2d(dst + 2 * kPATile + kPWTile, &map_w_lo, it * kBK, n0, &sm.full[s]);
+          tma_load_2d(dst, &map_a_hi, it * kPBK, m0, &sm.full[s]);
+          tma_load_2d(dst + kPATile, &map_a_lo, it * kPBK, m0, &sm.full[s]);
+          tma_load_2d(dst + 2 * kPATile, &map_w_hi, it * kPBK, n0, &sm.full[s]);
+          tma_load_2d(dst + 2 * kPATile + kPWTile, &map_w_lo, it * kPBK, n0, &sm.full[s]);
         }
       }
     }
@@ -307,10 +324,10 @@ rna_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a_hi, cons
           mbar_wait(&sm.full[s], (git / kPStages) & 1);
           tc_fence_after();
           const unsigned char* src = stages + (size_t)s * kPStageBytes;
-          const unsigned long long a_hi = tc_smem_desc(src), a_lo = tc_smem_desc(src + kPATile);
-          const unsigned long long w_hi = tc_smem_desc(src + 2 * kPATile), w_lo = tc_smem_desc(src + 2 * kPATile + kPWTile);
+          const unsigned long long a_hi = tc_smem_desc_p(src), a_lo = tc_smem_desc_p(src + kPATile);
+          const unsigned long long w_hi = tc_smem_desc_p(src + 2 * kPATile), w_lo = tc_smem_desc_p(src + 2 * kPATile + kPWTile);
 #pragma unroll
-          for (int k = 0; k < kBK / kUmmaK; ++k) {
+          for (int k = 0; k < kPBK / kUmmaK; ++k) {
             tc_mma_bf16(d_tmem, a_hi + 2ull * k, w_hi + 2ull * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
             tc_mma_bf16(d_tmem, a_hi + 2ull * k, w_lo + 2ull * k, idesc, 1u);
             tc_mma_bf16(d_tmem, a_lo + 2ull * k, w_hi + 2ull * k, idesc, 1u);
@@ -321,23 +338,25 @@ rna_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a_hi, cons
       }
     }
   } else {
-    // ===== epilogue warps: thread = output row, 8 chunks of 32 columns per tile =====
-    const int q = warp & 3;
+    // ===== epilogue warps: thread = output row; the kPEpiWarps / 4 warps of a TMEM lane quarter (warp % 4) share its 8 column chunks =====
+    const int q = warp & 3, sub = (warp - 2) >> 2;
     int lt = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
       const int buf = lt & 1;
       const int m0 = (tile / tiles_n) * kBM, n0 = (tile % tiles_n) * kPBN;
       const int row = m0 + 32 * q + lane;
+      for (int i = threadIdx.x - 64; i < kPBN; i += 32 * kPEpiWarps) sm.bias[buf][i] = __ldg(g.bias + n0 + i);
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kPEpiWarps) : "memory");      // epilogue warps only
       mbar_wait(&sm.tmem_full[buf], (lt >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < kPBN / 32; ++c) {
+      for (int c = sub; c < kPBN / 32; c += kPEpiWarps / 4) {
         float v[32];
         tc_ld32(tmem + ((unsigned)(32 * q) << 16) + (unsigned)(buf * kPBN + 32 * c), v);
-        rna_epi_chunk<EPI>(g, v, row, n0 + 32 * c);
+        rna_epi_chunk<EPI>(g, v, row, n0 + 32 * c, &sm.bias[buf][32 * c]);
       }
       tc_fence_before();
-      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&sm.tmem_empty[buf])) : "memory");   // 128 arrivals free the buffer
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&sm.tmem_empty[buf])) : "memory");   // every epilogue thread arrives: the buffer is free
     }
   }
   __syncthreads();
@@ -378,15 +397,15 @@ EncodeTiledFn encode_fn() {
 }
 
 // [rows, cols] row-major bf16, box = 32 columns (64 bytes, one swizzle row) x 128 rows
-int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int box_rows = ha::kBM) {
+int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int box_rows = ha::kBM, int box_cols = ha::kBK) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return ha::set_error(HA_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)ha::kBK, (cuuint32_t)box_rows};      // 32 columns = 64 bytes = one swizzle row
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};      // box_cols bf16 = one swizzle row (64 or 128 bytes)
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        box_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return ha::set_error(HA_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows %d, cols %d)", (int)r, rows, cols);
   return HA_OK;
 }
@@ -430,17 +449,17 @@ bool tc_persistent() {
 
 template <int EPI>
 int launch_tc(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, cudaStream_t st) {
-  if (!tc_persistent() || g.N % ha::kPBN != 0) return launch_tc_tiles<EPI>(g, a_hi, a_lo, w_hi, w_lo, st);
+  if (!tc_persistent() || g.N % ha::kPBN != 0 || g.K % ha::kPBK != 0) return launch_tc_tiles<EPI>(g, a_hi, a_lo, w_hi, w_lo, st);
   HA_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "M, N, K must be positive");
-  HA_REQUIRE(g.K % ha::kBK == 0, "K must be a multiple of %d (got %d)", ha::kBK, g.K);
+  HA_REQUIRE(g.K % ha::kPBK == 0, "K must be a multiple of %d (got %d)", ha::kPBK, g.K);
   HA_REQUIRE(a_hi && a_lo && w_hi && w_lo && g.bias, "null operand");
   HA_REQUIRE(ha::aligned16(a_hi) && ha::aligned16(a_lo) && ha::aligned16(w_hi) && ha::aligned16(w_lo) && ha::aligned16(g.bias), "operands must be 16-byte aligned");
   CUtensorMap ma_hi, ma_lo, mw_hi, mw_lo;
   int rc;
-  if ((rc = make_map(&ma_hi, a_hi, g.M, g.K))) return rc;
-  if ((rc = make_map(&ma_lo, a_lo, g.M, g.K))) return rc;
-  if ((rc = make_map(&mw_hi, w_hi, g.N, g.K, ha::kPBN))) return rc;
-  if ((rc = make_map(&mw_lo, w_lo, g.N, g.K, ha::kPBN))) return rc;
+  if ((rc = make_map(&ma_hi, a_hi, g.M, g.K, ha::kBM, ha::kPBK))) return rc;
+  if ((rc = make_map(&ma_lo, a_lo, g.M, g.K, ha::kBM, ha::kPBK))) return rc;
+  if ((rc = make_map(&mw_hi, w_hi, g.N, g.K, ha::kPBN, ha::kPBK))) return rc;
+  if ((rc = make_map(&mw_lo, w_lo, g.N, g.K, ha::kPBN, ha::kPBK))) return rc;
   static bool configured = false;
   static int sm_count = 0;
   if (!configured) {
@@ -455,7 +474,7 @@ int launch_tc(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, const 
   const int n_tiles = (g.N / ha::kPBN) * ((g.M + ha::kBM - 1) / ha::kBM);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(n_tiles < sm_count ? n_tiles : sm_count));
-  cfg.blockDim = dim3(ha::kTcThreads);
+  cfg.blockDim = dim3(ha::kPThreads);
   cfg.dynamicSmemBytes = ha::kTcPSmemBytes;
   cfg.stream = st;
   return ha::check_cuda(cudaLaunchKernelEx(&cfg, ha::rna_gemm_tc_persistent_kernel<EPI>, ma_hi, ma_lo, mw_hi, mw_lo, g), "rna_gemm_tc_persistent_kernel launch");

@@ -61,6 +61,7 @@ class RandomNetworkAdversary:
         self._h2b = torch.empty(N, self.num_feats2, **f)
         self._logits = torch.empty(N, out_dims * softmax_bins, **f)
         bf = dict(dtype=torch.bfloat16, device=device)
+        self._px = [torch.empty(N, C["HA_RNA_IN_PAD"], **bf) for _ in range(2)]   # hi / lo planes of the padded input rows
         self._p1 = [torch.empty(N, self.num_feats1, **bf) for _ in range(4)]        # hi / lo planes of the 512-wide activations (two layers)
         self._p2 = [torch.empty(N, self.num_feats2, **bf) for _ in range(4)]        # ... of the 1024-wide activations
         self.out = torch.empty(N, out_dims, **f)
@@ -129,8 +130,10 @@ class RandomNetworkAdversary:
         if self._wsplit is None:
             st = ctypes.c_void_p(torch.cuda.current_stream(self.out.device).cuda_stream)
             self._wsplit = []
-            for lin in (self.fc1_1, self.fc2, self.fc2_1, self.fc3):
-                w = lin.weight.contiguous()
+            w1p = torch.zeros(self.num_feats1, C["HA_RNA_IN_PAD"], dtype=torch.float32, device=self.fc1.weight.device)
+            w1p[:, : self.in_dims] = self.fc1.weight                        # fc1 with K padded to one tensor-core k-block
+            for w in (w1p, self.fc1_1.weight, self.fc2.weight, self.fc2_1.weight, self.fc3.weight):
+                w = w.contiguous()
                 hi, lo = torch.empty_like(w, dtype=torch.bfloat16), torch.empty_like(w, dtype=torch.bfloat16)
                 _lib.check(self._lib.ha_rna_split_bf16(ctypes.c_void_p(w.data_ptr()), ctypes.c_void_p(hi.data_ptr()), ctypes.c_void_p(lo.data_ptr()),
                                                        w.numel(), st))
@@ -153,13 +156,14 @@ class RandomNetworkAdversary:
         assert object_pose_wrt_wrist.shape == (N, 7) and object_pose_wrt_wrist.stride(1) == 1, "pose rows must be 7 consecutive floats"
         st = ctypes.c_void_p(torch.cuda.current_stream(self.out.device).cuda_stream)
         P = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
-        (w11h, w11l), (w2h, w2l), (w21h, w21l), (w3h, w3l) = self._weights_split()
+        (w1h, w1l), (w11h, w11l), (w2h, w2l), (w21h, w21l), (w3h, w3l) = self._weights_split()
         mb1, mb2 = self._mask_bits()
         a_h, a_l, b_h, b_l = self._p1
         c_h, c_l, d_h, d_l = self._p2
         F1, F2 = self.num_feats1, self.num_feats2
-        _lib.check(lib.ha_rna_input_layer(N, P(dof_state), P(object_pose_wrt_wrist), object_pose_wrt_wrist.stride(0), P(self.fc1.weight),
-                                          P(self.fc1.bias), None, P(a_h), P(a_l), st))                                       # fc1 + ReLU
+        x_h, x_l = self._px
+        _lib.check(lib.ha_rna_input_planes(N, P(dof_state), P(object_pose_wrt_wrist), object_pose_wrt_wrist.stride(0), P(x_h), P(x_l), st))
+        _lib.check(lib.ha_rna_layer_tc(N, F1, C["HA_RNA_IN_PAD"], P(x_h), P(x_l), P(w1h), P(w1l), P(self.fc1.bias), None, 1, P(a_h), P(a_l), st))   # fc1 + ReLU
         _lib.check(lib.ha_rna_layer_tc(N, F1, F1, P(a_h), P(a_l), P(w11h), P(w11l), P(self.fc1_1.bias), P(mb1), 0,
                                        P(b_h), P(b_l), st))                                                                # fc1_1, * mask1
         _lib.check(lib.ha_rna_layer_tc(N, F2, F1, P(b_h), P(b_l), P(w2h), P(w2l), P(self.fc2.bias), None, 1, P(c_h), P(c_l), st))      # fc2 + ReLU
