@@ -237,10 +237,11 @@ typedef struct HaKukaBuffers {
   /* ---- reductions ---- */
   float* stats;                 /* [HA_STATS_LEN], see HA_KUKA_STAT_* */
   int64_t* stat_accum;          /* fixed-point statistics scratch.
-                                   single arm: [HA_KUKA_N_PARTIAL_STATS][HA_KUKA_STAT_SLOTS], one slot per CTA of the last
+                                   single arm, and two arms with n_envs <= 32 * HA_KUKA_STAT_SLOTS:
+                                   [HA_KUKA_N_PARTIAL_STATS][HA_KUKA_STAT_SLOTS], one slot per CTA of the last
                                    ha_kuka_post_step (plain stores; initialise every slot of row i once with ha_kuka_stat_accum_init(i)), folded into stats[] by the next
                                    ha_kuka_pre_step / ha_kuka_reset_idx or by ha_kuka_stats_finalize;
-                                   two arms: [HA_STATS_LEN] accumulators, initialise once with ha_kuka_stat_accum_init(i):
+                                   two arms beyond that size: [HA_STATS_LEN] accumulators, initialise once with ha_kuka_stat_accum_init(i):
                                    0 for sums, INT32_MIN for the two MAX slots (the kernel re-arms them itself) */
   uint32_t* tickets;            /* [8], zero-initialised once by the caller */
   /* ---- dynamic scalars ---- */

@@ -216,7 +216,7 @@ int ha_kuka_observe(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t s
 int ha_kuka_stats_finalize(const HaKukaParams* p, const HaKukaBuffers* b, ha_stream_t stream) {
   int rc = validate_kuka(p, b);
   if (rc) return rc;
-  if (p->n_arms == 2) return HA_OK;
+  if (p->n_arms == 2 && (p->n_envs + ha::kTile - 1) / ha::kTile > HA_KUKA_STAT_SLOTS) return HA_OK;      // finalised inside the post launch
   return ha::check_cuda(ha::launch(ha::kuka_stats_finalize_kernel, (int)ha::kNPart, ha::kThreads, 0, (cudaStream_t)stream, *b, p->n_envs), "kuka_stats_finalize_kernel launch");
 }
 

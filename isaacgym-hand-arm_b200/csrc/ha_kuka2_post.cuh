@@ -304,8 +304,19 @@ kuka2_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant_
     }
   }
   __syncthreads();
+  // statistics: deferred like the single-arm kernel (one slot of partials per CTA, folded by the next pre step) whenever the
+  // grid fits the slots; integer atomics + last-CTA ticket inside the launch otherwise
+  const bool deferred = gridDim.x <= HA_KUKA_STAT_SLOTS;
   if (warp == 3 && mode == kPostFull) {
-    kuka_post_stats(b, acc, lane);
+    if (deferred) {
+      kuka_post_store_partials(b, acc, lane);
+      if (blockIdx.x == 0 && lane == 0) {               // step bookkeeping, see kuka_post_kernel
+        b.reset_counts[0] = 0; b.reset_counts[1] = 0; b.reset_counts[2] = 0; b.reset_counts[3] = 0;
+        b.dynamic->rng_step = b.dynamic->rng_step + 1;
+      }
+    } else {
+      kuka_post_stats(b, acc, lane);
+    }
   } else {
     const float c = p.clamp_abs_obs;
     const bool do_clamp = c > 0.0f;

@@ -14,7 +14,10 @@
 
 namespace ha {
 
-struct Kuka2PreSmem { float pos[kEnvsPerCta][48]; };
+struct Kuka2PreSmem {
+  float pos[kEnvsPerCta][48];
+  long long fold[kThreads / 32];      // statistics fold of the CTAs below kNPart (kuka_fold_*)
+};
 
 __global__ void __launch_bounds__(kThreads)
 kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ HaKukaBuffers b, const float* __restrict__ actions,
@@ -33,6 +36,10 @@ kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   const size_t base = (size_t)env0 * D;
   const int total = nvalid * D, nvec = total >> 2;
 
+  // CTAs 0 .. kNPart-1 also fold one statistic of the previous post step each (deferred statistics, see kuka_pre_kernel)
+  const bool fold = blockIdx.x < kNPart && (n + kTile - 1) / kTile <= HA_KUKA_STAT_SLOTS;      // uniform over the CTA
+  KukaStatFold sf;
+  if (fold) kuka_fold_load(b, blockIdx.x, tid, sf);
   float4 a[kIters], prev[kIters];
 #pragma unroll
   for (int i = 0; i < kIters; ++i) {
@@ -78,7 +85,9 @@ kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       }
     }
   }
+  if (fold) kuka_fold_warp(sf, blockIdx.x, tid, s.fold);
   __syncthreads();
+  if (fold && tid == kThreads - 1) kuka_fold_finish(b, blockIdx.x, n, s.fold);
 
   // ---------------- all threads: every DOF is position-controlled (scale, moving average, clamp) ----------------
   if (!reset_only) {
