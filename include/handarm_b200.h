@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define HA_ABI_VERSION 4
+#define HA_ABI_VERSION 5
 
 #define HA_OK 0
 #define HA_ERR_INVALID (-1)   /* bad argument / unsupported dimension */
@@ -425,11 +425,17 @@ typedef struct HaHandBuffers {
   int32_t* reset_counts;          /* [4]: n_root, n_hand, n_reset_envs, n_goal_resets */
   /* reductions */
   float* stats;                   /* [HA_STATS_LEN], HA_HAND_STAT_* */
-  int64_t* stat_accum;            /* [HA_STATS_LEN], zero-initialised once */
+  int64_t* stat_accum;            /* [HA_HAND_N_PARTIAL_STATS][HA_HAND_STAT_SLOTS], zero-initialised once.  n_envs <=
+                                     32 * HA_HAND_STAT_SLOTS: one slot of partials per CTA of the last ha_hand_post_step,
+                                     folded into stats / consecutive_successes by the next ha_hand_pre_step /
+                                     ha_hand_reset_idx or by ha_hand_stats_finalize (whichever comes first; the running
+                                     average is applied once per post step).  Larger n_envs: the first HA_STATS_LEN
+                                     entries are atomic accumulators and the post launch finishes the statistics itself */
   uint32_t* tickets;              /* [8], zero-initialised once */
   HaHandDynamic* dynamic;
 } HaHandBuffers;
 
+#define HA_HAND_STAT_SLOTS 768      /* statistic slots per row of HaHandBuffers.stat_accum (one per CTA of the post kernel) */
 enum {
   HA_HAND_STAT_N = 0,
   HA_HAND_STAT_SUM_REWARD,
@@ -455,6 +461,10 @@ int ha_hand_pre_step(const HaHandParams* p, const HaHandBuffers* b, const float*
 int ha_hand_reset_idx(const HaHandParams* p, const HaHandBuffers* b, const float* ext_rand, ha_stream_t stream);
 int ha_hand_post_step(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream);
 int ha_hand_observe(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream);
+/* Fold the statistic slots of the last ha_hand_post_step now (stats, consecutive_successes) instead of at the head of the next
+ * pre step: what the reference has after compute_hand_reward returns (shadow_hand.py:415-435).  No-op work when nothing is
+ * pending or n_envs > 32 * HA_HAND_STAT_SLOTS. */
+int ha_hand_stats_finalize(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream);
 
 /* =====================================================================================================
  * DeXtreme: AllegroHandDextremeADR (config 5) -- per-step tensor path of

@@ -170,6 +170,7 @@ def load():
     lib.ha_hand_reset_idx.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_hand_post_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_hand_observe.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_hand_stats_finalize.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.ha_hand_obs_dim.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.ha_hand_fill_derived.argtypes = [ctypes.c_void_p]
     lib.ha_hand_fill_derived.restype = None

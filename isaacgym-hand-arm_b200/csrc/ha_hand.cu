@@ -119,6 +119,7 @@ int ha_hand_pre_step(const HaHandParams* p, const HaHandBuffers* b, const float*
   HA_REQUIRE(actions != nullptr, "actions is null");
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  if (grid < ha::kHandNPart) { rc = ha_hand_stats_finalize(p, b, stream); if (rc) return rc; }      // too few CTAs to fold a statistic each
   return ha::check_cuda(ha::launch(ha::hand_pre_kernel, grid, ha::kThreads, 0, (cudaStream_t)stream, *p, *b, actions, ext_rand,
                                    (int)ha::kHandPreFull), "hand_pre_kernel launch");
 }
@@ -128,6 +129,7 @@ int ha_hand_reset_idx(const HaHandParams* p, const HaHandBuffers* b, const float
   if (rc) return rc;
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  if (grid < ha::kHandNPart) { rc = ha_hand_stats_finalize(p, b, stream); if (rc) return rc; }
   rc = ha::check_cuda(ha::launch(ha::hand_pre_kernel, grid, ha::kThreads, 0, (cudaStream_t)stream, *p, *b, (const float*)nullptr, ext_rand,
                                  (int)ha::kHandPreResetOnly), "hand_pre_kernel(reset_only) launch");
   if (rc) return rc;
@@ -139,6 +141,14 @@ int ha_hand_post_step(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t
   int rc = validate_hand(p, b);
   if (rc) return rc;
   return launch_hand_post(p, b, ha::kHandPostFull, (cudaStream_t)stream);
+}
+
+int ha_hand_stats_finalize(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream) {
+  int rc = validate_hand(p, b);
+  if (rc) return rc;
+  if ((p->n_envs + ha::kHandTile - 1) / ha::kHandTile > HA_HAND_STAT_SLOTS) return HA_OK;      // finished inside the post launch
+  return ha::check_cuda(ha::launch(ha::hand_stats_finalize_kernel, (int)ha::kHandNPart, 128, 0, (cudaStream_t)stream, *b, (int)p->n_envs,
+                                   p->av_factor), "hand_stats_finalize_kernel launch");
 }
 
 int ha_hand_observe(const HaHandParams* p, const HaHandBuffers* b, ha_stream_t stream) {

@@ -24,6 +24,51 @@ namespace ha {
 enum { kHandPostFull = 0, kHandPostObserveOnly = 1 };
 constexpr int kHandThreads = 128;
 constexpr int kHandTile = 32;
+constexpr int kHandNPart = HA_HAND_N_PARTIAL_STATS;
+constexpr int kHandFoldPerThread = HA_HAND_STAT_SLOTS / 128;      // the folding kernels run 128 threads
+static_assert(HA_HAND_STAT_SLOTS % 128 == 0, "slot rows are folded by 128 threads");
+
+// ---- deferred statistics (grid <= HA_HAND_STAT_SLOTS): the post kernel leaves one slot of integer partials per CTA in
+// stat_accum[stat][slot] (plain stores, no atomics, no last-CTA tail) and raises tickets[1]; CTA s < kHandNPart of the next
+// pre kernel (or of hand_stats_finalize_kernel) folds row s into stats[s].  The CTA of SUM_FINISHED_SUCCESSES also folds
+// SUM_RESETS and applies the consecutive_successes average ONCE per post step (tickets[1] is its pending flag).
+struct HandStatFold { long long v[kHandFoldPerThread], w[kHandFoldPerThread]; };
+
+__device__ __forceinline__ void hand_fold_load(const long long* accum, const int stat, const int tid, HandStatFold& f) {
+  const long long* row = accum + (size_t)stat * HA_HAND_STAT_SLOTS;
+  const long long* row2 = accum + (size_t)HA_HAND_STAT_SUM_RESETS * HA_HAND_STAT_SLOTS;
+#pragma unroll
+  for (int i = 0; i < kHandFoldPerThread; ++i) {
+    f.v[i] = row[tid + 128 * i];
+    f.w[i] = (stat == HA_HAND_STAT_SUM_FINISHED_SUCCESSES) ? row2[tid + 128 * i] : 0;
+  }
+}
+// red: 8 shared-memory entries (4 warps x {v, w})
+__device__ __forceinline__ void hand_fold_warp(const HandStatFold& f, const int tid, long long* red) {
+  long long v = 0, w = 0;
+#pragma unroll
+  for (int i = 0; i < kHandFoldPerThread; ++i) { v += f.v[i]; w += f.w[i]; }
+  v = warp_sum_ll(v);
+  w = warp_sum_ll(w);
+  if ((tid & 31) == 0) { red[tid >> 5] = v; red[4 + (tid >> 5)] = w; }
+}
+// after a CTA barrier, one thread.  av_factor / n_envs are the only task constants of the tail.
+__device__ __forceinline__ void hand_fold_finish(float* stats, float* consecutive_successes, unsigned* tickets, const int stat,
+                                                 const int n_envs, const float av, const long long* red) {
+  const long long raw = red[0] + red[1] + red[2] + red[3];
+  const float fv = (stat == HA_HAND_STAT_SUM_REWARD) ? (float)((double)raw / 65536.0) : (float)raw;
+  stats[stat] = fv;
+  if (stat == HA_HAND_STAT_SUM_REWARD) stats[HA_HAND_STAT_MEAN_REWARD] = fv / (float)n_envs;
+  if (stat == HA_HAND_STAT_SUM_FINISHED_SUCCESSES && tickets[1] != 0u) {
+    const float num_resets = (float)(red[4] + red[5] + red[6] + red[7]);
+    const float cons = consecutive_successes[0];
+    const float upd = av * fv / num_resets + (1.0f - av) * cons;
+    const float out = (num_resets > 0.0f) ? upd : cons;
+    consecutive_successes[0] = out;
+    stats[HA_HAND_STAT_CONSECUTIVE_SUCCESSES] = out;
+    tickets[1] = 0u;
+  }
+}
 
 
 struct HandStageOfs {   // float offsets into the stage (contiguous images first: they are filled by 16-byte copies)
@@ -248,6 +293,15 @@ hand_post_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__
     case HA_HAND_STAT_SUM_TIMEOUTS: val = s_to; break;
     default: break;
   }
+  if (gridDim.x <= HA_HAND_STAT_SLOTS) {                                        // deferred: see hand_fold_*
+    if (lane < kHandNPart) accum[(size_t)lane * HA_HAND_STAT_SLOTS + blockIdx.x] = val;
+    if (blockIdx.x == 0 && lane == 0) {
+      b.tickets[1] = 1u;
+      b.reset_counts[0] = 0; b.reset_counts[1] = 0; b.reset_counts[2] = 0; b.reset_counts[3] = 0;
+      b.dynamic->rng_step = b.dynamic->rng_step + 1;
+    }
+    return;
+  }
   long long old = 0;
   if (lane < HA_HAND_N_PARTIAL_STATS) old = (long long)atomicAdd(reinterpret_cast<unsigned long long*>(accum + lane), (unsigned long long)val);
   const unsigned dep = __any_sync(FULL, old == 0x7fffffffffffffffLL) ? 1u : 0u;   // ticket depends on every returned atomic
@@ -277,6 +331,16 @@ hand_post_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__
     b.reset_counts[0] = 0; b.reset_counts[1] = 0; b.reset_counts[2] = 0; b.reset_counts[3] = 0;
     b.dynamic->rng_step = b.dynamic->rng_step + 1;
   }
+}
+
+// the fold as a launch of its own (ha_hand_stats_finalize): grid kHandNPart x 128 threads
+__global__ void __launch_bounds__(128) hand_stats_finalize_kernel(const __grid_constant__ HaHandBuffers b, const int n_envs, const float av) {
+  __shared__ long long red[8];
+  HandStatFold f;
+  hand_fold_load(reinterpret_cast<const long long*>(b.stat_accum), blockIdx.x, threadIdx.x, f);
+  hand_fold_warp(f, threadIdx.x, red);
+  __syncthreads();
+  if (threadIdx.x == 0) hand_fold_finish(b.stats, b.consecutive_successes, b.tickets, blockIdx.x, n_envs, av, red);
 }
 
 }  // namespace ha

@@ -10,6 +10,7 @@
 #pragma once
 #include "ha_device.cuh"
 #include "../../include/handarm_b200.h"
+#include "ha_hand_post.cuh"      // hand_fold_*: the statistics fold of the previous post step
 
 namespace ha {
 
@@ -46,6 +47,7 @@ __device__ __forceinline__ f4 hand_random_rotation(float r0, float r1) {
 
 struct HandPreSmem {
   float pos[kEnvsPerCta][HA_HAND_MAX_DOFS];   // re-randomised DOF positions of the tile's reset envs
+  long long fold[8];                          // statistics fold of the CTAs below kHandNPart (hand_fold_*)
 };
 
 __global__ void __launch_bounds__(kThreads)
@@ -60,6 +62,11 @@ hand_pre_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__ 
   const int env = env0 + lane;
   const bool valid = lane < nvalid;
   const bool reset_only = (mode == kHandPreResetOnly);
+
+  // CTAs 0 .. kHandNPart-1 also fold one statistic of the previous post step each (loads in flight with the tile's)
+  const bool fold = blockIdx.x < kHandNPart && (n + kHandTile - 1) / kHandTile <= HA_HAND_STAT_SLOTS;      // uniform over the CTA
+  HandStatFold sf;
+  if (fold) hand_fold_load(reinterpret_cast<const long long*>(b.stat_accum), blockIdx.x, tid, sf);
 
   HandRand R;
   R.ext = p.use_fast_rng ? nullptr : ext_rand;
@@ -96,7 +103,9 @@ hand_pre_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__ 
       b.cur_targets[(size_t)re * Dp + d] = pos;
     }
   }
+  if (fold) hand_fold_warp(sf, tid, s.fold);
   __syncthreads();
+  if (fold && tid == kThreads - 1) hand_fold_finish(b.stats, b.consecutive_successes, b.tickets, blockIdx.x, n, p.av_factor, s.fold);
 
   // ---------------- all threads: actions -> DOF targets of the actuated DOFs ----------------
   if (!reset_only) {

@@ -172,6 +172,7 @@ int ha_kuka_pre_step(const HaKukaParams* p, const HaKukaBuffers* b, const float*
   HA_REQUIRE(ha::aligned16(actions), "actions must be 16-byte aligned");
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  if (grid < ha::kNPart) { rc = ha_kuka_stats_finalize(p, b, stream); if (rc) return rc; }      // too few CTAs to fold a statistic each
   if (p->n_arms == 2) {
     HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING, "two arms: only the regrasping reset path is built (subtask %d)", p->subtask);
     return ha::check_cuda(ha::launch(ha::kuka2_pre_kernel, grid, ha::kThreads, 0, (cudaStream_t)stream, *p, *b, actions, ext_rand,
@@ -186,6 +187,7 @@ int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float
   if (rc) return rc;
   HA_REQUIRE(p->use_fast_rng || ext_rand != nullptr, "ext_rand is required unless use_fast_rng is set");
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
+  if (grid < ha::kNPart) { rc = ha_kuka_stats_finalize(p, b, stream); if (rc) return rc; }      // too few CTAs to fold a statistic each
   if (p->n_arms == 2) {
     HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING, "two arms: only the regrasping reset path is built (subtask %d)", p->subtask);
     ha::kuka2_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);

@@ -317,7 +317,6 @@ class AllegroKukaBase(VecTask):
         self._params = p
         self._observe_params = _lib.HaKukaParams.from_buffer_copy(p)
         self._observe_params.clamp_abs_obs = 0.0    # VecTask.reset() clips on the host side copy only
-        self._pre_folds_stats = (self.num_envs + 31) // 32 >= C["HA_KUKA_N_PARTIAL_STATS"]    # one statistic per CTA of the pre grid
         self._stats_deferred = self.num_arms == 1 or (self.num_envs + 31) // 32 <= C["HA_KUKA_STAT_SLOTS"]
         if self._stats_deferred:   # one slot of partials per CTA of the post kernel, folded by the next pre step / finalize_stats()
             init = torch.tensor([int(self._lib.ha_kuka_stat_accum_init(i)) for i in range(C["HA_KUKA_N_PARTIAL_STATS"])], dtype=torch.int64)
@@ -433,8 +432,7 @@ class AllegroKukaBase(VecTask):
         rnd = self._rand_ptr()
         _lib.check(self._lib.ha_kuka_pre_step(ctypes.byref(self._params), ctypes.byref(self._buffers), ctypes.c_void_p(actions.data_ptr()),
                                               rnd, self._stream()))
-        if self._pre_folds_stats:         # CTAs 0 .. N_PARTIAL-1 of the pre kernel folded the previous step's statistic slots
-            self._stats_pending = False
+        self._stats_pending = False       # the pre launch folded the previous step's statistic slots
         # what the reference hands to PhysX after this point (recorded, not executed):
         sim = self.sim
         if sim.record_calls:
@@ -502,8 +500,7 @@ class AllegroKukaBase(VecTask):
         self.reset_buf[env_ids] = 1
         self._rebind_sim_state()
         _lib.check(self._lib.ha_kuka_reset_idx(ctypes.byref(self._params), ctypes.byref(self._buffers), self._rand_ptr(), self._stream()))
-        if self._pre_folds_stats:
-            self._stats_pending = False
+        self._stats_pending = False
         saved[env_ids] = 0
         self.reset_buf.copy_(saved)
         self.extras["scalars"] = {"success_tolerance": self.success_tolerance}

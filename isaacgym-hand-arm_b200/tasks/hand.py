@@ -132,7 +132,7 @@ class _HandTask(VecTask):
         self.z_unit_tensor = torch.tensor([0, 0, 1], **f).repeat((N, 1))
         self.reset_goal_buf = self.reset_buf.clone()
         self.successes = torch.zeros(N, **f)
-        self.consecutive_successes = torch.zeros(1, **f)
+        self._consecutive_successes = torch.zeros(1, **f)
         self.total_successes = self.total_resets = 0
         self.force_decay_t = torch.tensor(self.force_decay, **f)
         self.force_prob_range_t = torch.tensor(self.force_prob_range, **f)
@@ -145,8 +145,12 @@ class _HandTask(VecTask):
         self.root_reset_indices = torch.zeros(2 * N, dtype=torch.int32, device=dev)
         self.hand_reset_indices = torch.zeros(N, dtype=torch.int32, device=dev)
         self.reset_counts = torch.zeros(4, dtype=torch.int32, device=dev)
-        self.stats = torch.zeros(C["HA_STATS_LEN"], **f)
-        self._stat_accum = torch.zeros(C["HA_STATS_LEN"], dtype=torch.int64, device=dev)
+        self._stats = torch.zeros(C["HA_STATS_LEN"], **f)
+        # one slot of integer partials per CTA of the post kernel, folded by the next pre step / finalize_stats()
+        self._stat_accum = torch.zeros(C["HA_HAND_N_PARTIAL_STATS"] * C["HA_HAND_STAT_SLOTS"], dtype=torch.int64, device=dev)
+        n_tiles = (self.num_envs + 31) // 32
+        self._stats_deferred = n_tiles <= C["HA_HAND_STAT_SLOTS"]
+        self._stats_pending = False
         self._tickets = torch.zeros(8, dtype=torch.int32, device=dev)
         self._object_actor_i32 = self.object_indices.to(torch.int32)
         self._goal_actor_i32 = self.goal_object_indices.to(torch.int32)
@@ -219,10 +223,10 @@ class _HandTask(VecTask):
             goal_actor=self._goal_actor_i32, hand_actor=self._hand_actor_i32, object_init_state=self.object_init_state,
             goal_init_state=self.goal_init_state, goal_states=self.goal_states, obs_buf=self.obs_buf, rew_buf=self.rew_buf,
             reset_buf=self.reset_buf, reset_goal_buf=self.reset_goal_buf, progress_buf=self.progress_buf, randomize_buf=self.randomize_buf,
-            timeout_buf=self.timeout_buf, successes=self.successes, consecutive_successes=self.consecutive_successes,
+            timeout_buf=self.timeout_buf, successes=self.successes, consecutive_successes=self._consecutive_successes,
             prev_targets=self.prev_targets, cur_targets=self.cur_targets, actions=self.actions, rb_forces=self.rb_forces,
             random_force_prob=self.random_force_prob, root_reset_indices=self.root_reset_indices,
-            hand_reset_indices=self.hand_reset_indices, reset_counts=self.reset_counts, stats=self.stats, stat_accum=self._stat_accum,
+            hand_reset_indices=self.hand_reset_indices, reset_counts=self.reset_counts, stats=self._stats, stat_accum=self._stat_accum,
             tickets=self._tickets, dynamic=self._dynamic)
         if self.num_states > 0:
             self._bound["states_buf"] = self.states_buf
@@ -297,6 +301,7 @@ class _HandTask(VecTask):
         self._rebind_sim_state()
         _lib.check(self._lib.ha_hand_pre_step(ctypes.byref(self._params), ctypes.byref(self._buffers), ctypes.c_void_p(actions.data_ptr()),
                                               self._rand_ptr(), self._stream()))
+        self._stats_pending = False       # the pre launch folded the previous step's statistic slots
         sim = self.sim
         if sim.record_calls:
             sim.record("set_actor_root_state_tensor_indexed", sim.root_state, self.root_reset_indices, self.reset_counts[0:1])
@@ -311,7 +316,28 @@ class _HandTask(VecTask):
         self._require_engine()
         self._rebind_sim_state()
         _lib.check(self._lib.ha_hand_post_step(ctypes.byref(self._params), ctypes.byref(self._buffers), self._stream()))
-        self.extras["consecutive_successes"] = self.consecutive_successes[0]      # mean of the [1] tensor: a 0-dim view, no launch
+        self._stats_pending = self._stats_deferred
+        # mean of the [1] tensor: a 0-dim view, no launch; filled in place by the next pre step or by finalize_stats()
+        self.extras["consecutive_successes"] = self._consecutive_successes[0]
+
+    def finalize_stats(self) -> None:
+        """Fold the post kernel's per-CTA statistic slots into ``stats`` / ``consecutive_successes`` now (one small launch)
+        instead of at the head of the next ``pre_physics_step``.  Nothing pending: no-op."""
+        if self._stats_pending:
+            _lib.check(self._lib.ha_hand_stats_finalize(ctypes.byref(self._params), ctypes.byref(self._buffers), self._stream()))
+            self._stats_pending = False
+
+    @property
+    def stats(self) -> torch.Tensor:
+        """Statistics of the last post step ([HA_STATS_LEN] float32, ``HA_HAND_STAT_*``)."""
+        self.finalize_stats()
+        return self._stats
+
+    @property
+    def consecutive_successes(self) -> torch.Tensor:
+        """Running average of the successes of finished episodes ([1] float32, shadow_hand.py:795-798)."""
+        self.finalize_stats()
+        return self._consecutive_successes
 
     def compute_observations(self):
         """compute_observations only (VecTask.reset())."""
@@ -327,6 +353,7 @@ class _HandTask(VecTask):
         self.reset_buf[env_ids] = 1
         self._rebind_sim_state()
         _lib.check(self._lib.ha_hand_reset_idx(ctypes.byref(self._params), ctypes.byref(self._buffers), self._rand_ptr(), self._stream()))
+        self._stats_pending = False
         saved[env_ids] = 0
         self.reset_buf.copy_(saved)
 
