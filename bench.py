@@ -572,8 +572,9 @@ def measure(args, layout, device, rank, world, local, headline=True):
                              "algorithmic bytes per round", "launch": f"CUDA graph of {per_graph} steps", "rng": "in-kernel Philox"},
             "roofline": {"bound": "hbm", "kernel": f"kuka_post_kernel<K=4, SOA={int(layout == 'soa')}, NS=2>", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
                          "frac": achieved / hbm_gbs, "traffic": ncu_traffic(layout), "peak_source": peak_src, "kernel_us": post_avg,
-                         "bytes_per_env": post_bytes, "pre_kernel_us": pre_avg, "pre_bytes_per_env": pre_bytes,
-                         "step_frac": step_frac, "kernel_timing": "CUDA events around graph replays of only-post / only-pre launches"},
+                         "bytes_per_env": post_bytes, "pre_kernel_us": pre_avg, "pre_in_step_us": ms * 1e3 / args.steps - post_avg, "pre_bytes_per_env": pre_bytes,
+                         "step_frac": step_frac, "kernel_timing": "CUDA events around graph replays of only-post / only-pre launches; the only-pre replays see no resets "
+                                          "(the masks are consumed by the first launch), pre_in_step_us = step - post is the pre launch with the step's resets"},
             "value_l2_warm": warm_value,
             "value_concurrent_blocks": conc_value,
             "clocks": clk.summary(),

@@ -233,7 +233,7 @@ typedef struct HaKukaBuffers {
   /* ---- outputs for the simulator's *_indexed setters ---- */
   int32_t* root_reset_indices;  /* [2*n_envs] ascending actor rows */
   int32_t* hand_reset_indices;  /* [n_arms*n_envs] ascending actor rows */
-  int32_t* reset_counts;        /* [4]: n_root, n_hand, n_reset_envs, n_goal_resets */
+  int32_t* reset_counts;        /* [4]: n_root, n_hand, n_reset_envs, n_goal_resets; 8-byte aligned */
   /* ---- reductions ---- */
   float* stats;                 /* [HA_STATS_LEN], see HA_KUKA_STAT_* */
   int64_t* stat_accum;          /* fixed-point statistics scratch.

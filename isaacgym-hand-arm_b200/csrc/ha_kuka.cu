@@ -44,6 +44,7 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   HA_REQUIRE(A == 2 || (b->finger_rew_coeffs != nullptr && b->furthest_hand_dist != nullptr),
              "finger_rew_coeffs / furthest_hand_dist are required by the single-arm task");
   HA_REQUIRE_ALIGNED16(b->dof_state);
+  HA_REQUIRE(((uintptr_t)b->reset_counts & 7) == 0, "reset_counts must be 8-byte aligned");
   HA_REQUIRE_ALIGNED16(b->obs_buf);
   HA_REQUIRE_ALIGNED16(b->closest_fingertip_dist);
   if (b->finger_rew_coeffs) HA_REQUIRE_ALIGNED16(b->finger_rew_coeffs);

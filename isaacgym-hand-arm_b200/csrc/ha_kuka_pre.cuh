@@ -51,10 +51,12 @@ __device__ __forceinline__ float force_prob_from(const HaKukaParams& p, float u)
   return expf(p.force_log_c0 * u + p.force_log_c1);
 }
 
+constexpr int kSpecDraws = 5;      // Philox blocks of a full reset drawn ahead of the masks (kuka_spec_slot)
 struct KukaPreSmem {
   float lo[24], hi[24], dflt[24], noise[24];
   float pos[kEnvsPerCta][24];      // re-randomised DOF positions of the tile's reset envs (row = env in tile)
   long long fold[kThreads / 32];   // statistics fold of the CTAs below kNPart (kuka_fold_*)
+  float4 spec[kSpecDraws][kEnvsPerCta];      // fast-RNG draws of the scalar reset, made ahead of the masks (kuka_spec_slot)
 };
 
 // reset_idx DOF re-randomisation of one env by one warp, lane = dof (:1271-1290).
@@ -99,6 +101,21 @@ __device__ __forceinline__ float4 kuka_draw4(const KukaRand& R, int env, int slo
   return R.rng.uniform4(env, 32 + slot);
 }
 
+// Fast-RNG mode: the Philox draws of the scalar reset do not depend on the masks (only the choice between the two goal slots
+// does), so they are computed while the mask loads are still in flight (~1 us of DRAM latency in which the warps would
+// otherwise sit at the ballot) instead of on the critical path of the tiles that turn out to have a reset: warp w draws blocks
+// w and w + 4 of the five of a full reset for its lane's env into shared memory, warp 0 picks them up after the CTA barrier.
+// (a goal-only reset draws its two blocks once the masks are known)
+__device__ __forceinline__ int kuka_spec_slot(int k) {
+  switch (k) {
+    case 0: return HA_KUKA_RND_RESET_GOAL_POS;
+    case 1: return HA_KUKA_RND_RESET_GOAL_ROT;
+    case 2: return HA_KUKA_RND_OBJ_POS;
+    case 3: return HA_KUKA_RND_OBJ_ROT;
+    default: return HA_KUKA_RND_FORCE_PROB;
+  }
+}
+
 // Issue phase: loads, random draws and the list-slot atomics of a tile that has a goal / full reset.
 __device__ __forceinline__ void kuka_reset_prefetch(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env, int lane,
                                                 bool rst, bool grst, KukaResetPrefetch& f) {
@@ -112,10 +129,13 @@ __device__ __forceinline__ void kuka_reset_prefetch(const HaKukaParams& p, const
   const int n_hand = __popc(m_rst);
   int root_base = 0, hand_base = 0;
   if (lane == 0 && n_root) {
-    root_base = atomicAdd(b.reset_counts + 0, n_root);
-    if (n_hand) hand_base = atomicAdd(b.reset_counts + 1, n_hand);
-    if (n_hand) atomicAdd(b.reset_counts + 2, n_hand);
-    atomicAdd(b.reset_counts + 3, __popc(m_any));
+    // a third of the CTAs arrive here at the same moment and the four counters share one L2 line: one returning 64-bit add
+    // for the two list bases and one fire-and-forget add for the two plain counts (reset_counts is 8-byte aligned; < 2^31 each)
+    unsigned long long* rc = reinterpret_cast<unsigned long long*>(b.reset_counts);
+    const unsigned long long old = atomicAdd(rc + 0, (unsigned long long)(unsigned)n_root | ((unsigned long long)(unsigned)n_hand << 32));
+    root_base = (int)(unsigned)(old & 0xffffffffULL);
+    hand_base = (int)(unsigned)(old >> 32);
+    atomicAdd(rc + 1, (unsigned long long)(unsigned)n_hand | ((unsigned long long)(unsigned)__popc(m_any) << 32));
   }
   // _reset_target; an env that is in both sets is drawn twice by the
   // reference and the reset_idx draw wins
@@ -132,12 +152,17 @@ __device__ __forceinline__ void kuka_reset_prefetch(const HaKukaParams& p, const
     const float* init = b.object_init_state + (size_t)env * 13;
     f.init0 = __ldg(init + 0); f.init1 = __ldg(init + 1); f.init2 = __ldg(init + 2);
   }
-  const int ec = any_goal ? env : 0;                  // idle lanes draw for env 0 (cheap, keeps the warp converged)
-  f.u_gp = kuka_draw4(R, ec, sp);
-  f.u_gr = kuka_draw4(R, ec, sr);
-  f.u_op = kuka_draw4(R, ec, HA_KUKA_RND_OBJ_POS);
-  f.u_or = kuka_draw4(R, ec, HA_KUKA_RND_OBJ_ROT);
-  f.u_fp = kuka_draw4(R, ec, HA_KUKA_RND_FORCE_PROB).x;
+  if (R.ext) {
+    const int ec = any_goal ? env : 0;                // idle lanes read the row of env 0 (keeps the warp converged)
+    f.u_gp = kuka_draw4(R, ec, sp);
+    f.u_gr = kuka_draw4(R, ec, sr);
+    f.u_op = kuka_draw4(R, ec, HA_KUKA_RND_OBJ_POS);
+    f.u_or = kuka_draw4(R, ec, HA_KUKA_RND_OBJ_ROT);
+    f.u_fp = kuka_draw4(R, ec, HA_KUKA_RND_FORCE_PROB).x;
+  } else if (m_goal_only) {                           // fast mode: the full-reset blocks were drawn ahead of the masks (kuka_spec_slot)
+    f.u_gp = kuka_draw4(R, env, HA_KUKA_RND_GOAL_POS);
+    f.u_gr = kuka_draw4(R, env, HA_KUKA_RND_GOAL_ROT);
+  }
   const unsigned below = (1u << lane) - 1u;
   f.root_pos = 2 * __popc(m_rst & below) + __popc(m_goal_only & below);   // offsets inside the warp's list segments;
   f.hand_pos = __popc(m_rst & below);                                     // the bases (lane 0's atomics) are added on use
@@ -270,6 +295,11 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     s.lo[tid] = p.dof_lower[tid]; s.hi[tid] = p.dof_upper[tid];
     s.dflt[tid] = p.dof_default[tid]; s.noise[tid] = p.dof_reset_noise[tid];
   }
+  if (!R.ext) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+      if (warp + 4 * k < kSpecDraws) s.spec[warp + 4 * k][lane] = R.rng.uniform4(env, 32 + kuka_spec_slot(warp + 4 * k));
+  }
   const bool rst = raw_rst != 0, grst = raw_goal != 0;
   const unsigned m_rst = __ballot_sync(0xffffffffu, rst);
   const unsigned m_goal = __ballot_sync(0xffffffffu, grst);
@@ -280,6 +310,10 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   if (fold) kuka_fold_warp(sf, blockIdx.x, tid, s.fold);
   __syncthreads();
   if (fold && tid == kThreads - 1) kuka_fold_finish(b, blockIdx.x, n, s.fold);
+  if (warp == 0 && tile_resets && !R.ext) {
+    if (rst) { pf.u_gp = s.spec[0][lane]; pf.u_gr = s.spec[1][lane]; }
+    pf.u_op = s.spec[2][lane]; pf.u_or = s.spec[3][lane]; pf.u_fp = s.spec[4][lane].x;
+  }
   if (m_rst != 0u) {
     // DOF re-randomisation of the tile's reset envs, one warp per env (round robin), lane = dof
     unsigned m = m_rst;
