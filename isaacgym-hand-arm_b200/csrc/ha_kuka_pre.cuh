@@ -63,7 +63,7 @@ struct KukaPreSmem {
 // Writes dof_state; the new position goes to smem for the element pass (prev_targets = cur_targets = pos, :1289-1290),
 // and straight to global memory when there is no element pass (reset outside of a step).
 __device__ __noinline__ void kuka_reset_dofs_warp(const HaKukaBuffers& b, const KukaRand& R, KukaPreSmem& s, float vel_noise,
-                                                  int env, int e_local, int lane, bool write_targets) {
+                                                  int env, int e_local, int lane, bool write_targets, const HaKukaParams& p) {
   constexpr int D = 23;
   if (lane >= D) return;
   const int d = lane;
@@ -75,10 +75,11 @@ __device__ __noinline__ void kuka_reset_dofs_warp(const HaKukaBuffers& b, const 
     const float2 u = R.rng.uniform2(env, 64 + d);     // one Philox block per DOF: (.x, .y) = (pos, vel) draws
     u_pos = u.x; u_vel = u.y;
   }
-  const float lo = s.lo[d], hi = s.hi[d], dflt = s.dflt[d];
+  // limits straight from the kernel parameters: this runs ahead of the barrier that publishes the shared copies
+  const float lo = p.dof_lower[d], hi = p.dof_upper[d], dflt = p.dof_default[d], noise = p.dof_reset_noise[d];
   const float delta_max = hi - dflt, delta_min = lo - dflt;
   const float rand_delta = delta_min + (delta_max - delta_min) * u_pos;
-  const float pos = dflt + s.noise[d] * rand_delta;
+  const float pos = dflt + noise * rand_delta;
   const float vel = vel_noise * (2.0f * u_vel + -1.0f);
   const size_t idx = (size_t)env * D + d;
   *reinterpret_cast<float2*>(b.dof_state + 2 * idx) = make_float2(pos, vel);
@@ -308,22 +309,23 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   KukaResetPrefetch pf;
   if (warp == 0 && tile_resets) kuka_reset_prefetch(p, b, R, env, lane, rst, grst, pf);
   if (fold) kuka_fold_warp(sf, blockIdx.x, tid, s.fold);
-  __syncthreads();
-  if (fold && tid == kThreads - 1) kuka_fold_finish(b, blockIdx.x, n, s.fold);
-  if (warp == 0 && tile_resets && !R.ext) {
-    if (rst) { pf.u_gp = s.spec[0][lane]; pf.u_gr = s.spec[1][lane]; }
-    pf.u_op = s.spec[2][lane]; pf.u_or = s.spec[3][lane]; pf.u_fp = s.spec[4][lane].x;
-  }
   if (m_rst != 0u) {
-    // DOF re-randomisation of the tile's reset envs, one warp per env (round robin), lane = dof
+    // DOF re-randomisation of the tile's reset envs, one warp per env (round robin), lane = dof; before the barrier, so that it
+    // overlaps warp 0's atomics and the barrier below also publishes s.pos to the element pass
     unsigned m = m_rst;
     int rank = 0;
     while (m) {
       const int e = __ffs(m) - 1;
       m &= m - 1;
-      if ((rank++ & (kThreads / 32 - 1)) == warp) kuka_reset_dofs_warp(b, R, s, p.reset_dof_vel_noise, env0 + e, e, lane, reset_only);
+      if ((rank++ & (kThreads / 32 - 1)) == warp)
+        kuka_reset_dofs_warp(b, R, s, p.reset_dof_vel_noise, env0 + e, e, lane, reset_only, p);
     }
-    __syncthreads();                                   // s.pos visible to the element pass below
+  }
+  __syncthreads();
+  if (fold && tid == kThreads - 1) kuka_fold_finish(b, blockIdx.x, n, s.fold);
+  if (warp == 0 && tile_resets && !R.ext) {
+    if (rst) { pf.u_gp = s.spec[0][lane]; pf.u_gr = s.spec[1][lane]; }
+    pf.u_op = s.spec[2][lane]; pf.u_or = s.spec[3][lane]; pf.u_fp = s.spec[4][lane].x;
   }
 
   // ---------------- all threads: DOF targets, 4 consecutive elements per float4 ----------------
