@@ -40,6 +40,9 @@ def parse_args():
     ap.add_argument("--blocks", type=int, default=4, help="independent env blocks stepped round-robin so state does not stay in L2")
     ap.add_argument("--snapshots", type=int, default=4, help="rotating simulator snapshots per env block")
     ap.add_argument("--cpu-steps", type=int, default=0, help="steps of the CPU baseline sample (0 = auto, about 10-20 s)")
+    ap.add_argument("--stats-interval", type=int, default=1, help="N > 1: graph replays between two all-reduces of the episode statistics")
+    ap.add_argument("--peer-stats", action="store_true", help="N > 1: exchange the episode statistics with ha_stats_exchange (NVLink peer "
+                    "stores, in the step graph) instead of an asynchronous nccl all_reduce; couples the ranks, see DESIGN.md 5")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--layout", default="both", choices=["both", "isaacgym", "soa"],
@@ -365,24 +368,55 @@ def measure(args, layout, device, rank, world, local, headline=True):
         t.frame_since_restart = 0
         t.last_curriculum_update = 0
 
-    # one CUDA graph = S rounds over the B env blocks (B*S steps, 2 kernels each)
+    # whole-box episode statistics once per graph replay (the cadence rl_games logs at: one epoch = 16 steps).  Default: an
+    # asynchronous nccl all_reduce on nccl's own stream; --peer-stats: the engine's exchange over NVLink peer memory (one
+    # single-CTA launch at the end of the step graph; falls back to nccl if the rendezvous fails)
+    xchg, xchg_note = None, "single rank"
+    if world > 1:
+        from handarm_b200.stats import PeerStatsExchange, _MAX_SLOTS
+        xchg_note = "nccl all_reduce, async, once per graph replay"
+        if args.peer_stats:
+            try:
+                xchg = PeerStatsExchange.connect(device=device)
+                probe = torch.arange(16, device=device, dtype=torch.float32) * (rank + 1) + 0.25
+                xchg.exchange(probe)
+                got = xchg.exchange(probe).clone()          # the second call returns the reduction of the first
+                want, wmax = probe.clone(), probe.clone()
+                dist.all_reduce(want)
+                dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
+                want[_MAX_SLOTS] = wmax[_MAX_SLOTS]
+                torch.cuda.synchronize()
+                if not torch.allclose(got, want, rtol=1e-6, atol=0) or xchg.status() != 0:
+                    raise RuntimeError(f"peer exchange disagrees with nccl: {got.tolist()} vs {want.tolist()}")
+                xchg_note = "ha_stats_exchange: peer stores over NVLink (torch symmetric memory), checked against nccl all_reduce"
+            except Exception as e:       # noqa: BLE001 -- any rendezvous / IPC failure: fall back, and say so
+                xchg, xchg_note = None, f"nccl all_reduce (peer exchange unavailable: {type(e).__name__}: {e})"[:240]
+            ok = torch.tensor([1 if xchg is not None else 0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok) == 0 and xchg is not None:
+                xchg, xchg_note = None, "nccl all_reduce (peer exchange failed on another rank)"
+
+    # one CUDA graph = S rounds over the B env blocks (B*S steps, 2 kernels each); the statistics exchange rides at its end
+    # (every argument of the launch lives in device memory, so the node replays as it is) on the vector the last pre step folded
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.graph(graph, stream=stream):
         for _ in range(S):
             for t, a in zip(tasks, actions):
                 one_step(t, a)
+        if xchg is not None:
+            xchg.exchange(tasks[0].stats_folded)
     per_graph = B * S
 
     def run_steps(k):
         n_graph, rest = divmod(k, per_graph)
-        for _ in range(n_graph):
+        for r in range(n_graph):
             graph.replay()
             for t in tasks:
                 t.advance_frames(S)
-            if world > 1:
-                # episode statistics: one tiny all-reduce per replay (sum half; the max half is analogous)
-                stats_sum.copy_(tasks[0].stats, non_blocking=True)
-                dist.all_reduce(stats_sum, async_op=True)
+            if world > 1 and (r + 1) % max(1, args.stats_interval) == 0:
+                if xchg is None:        # one tiny all-reduce per replay (sum half; the max half is analogous)
+                    stats_sum.copy_(tasks[0].stats, non_blocking=True)
+                    dist.all_reduce(stats_sum, async_op=True)
         for i in range(rest):
             one_step(tasks[i % B], actions[i % B])
 
@@ -569,7 +603,7 @@ def measure(args, layout, device, rank, world, local, headline=True):
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "envs_per_gpu": N, "state_layout": layout, "env_blocks": B, "snapshots_per_block": S,
                        "l2": f"inputs larger than L2: {B} env blocks stepped round-robin, {B}x{N * (post_bytes + pre_bytes) / 1e6:.0f} MB "
-                             "algorithmic bytes per round", "launch": f"CUDA graph of {per_graph} steps", "rng": "in-kernel Philox"},
+                             "algorithmic bytes per round", "launch": f"CUDA graph of {per_graph} steps", "rng": "in-kernel Philox", "stats_exchange": xchg_note},
             "roofline": {"bound": "hbm", "kernel": f"kuka_post_kernel<K=4, SOA={int(layout == 'soa')}, NS=2>", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
                          "frac": achieved / hbm_gbs, "traffic": ncu_traffic(layout), "peak_source": peak_src, "kernel_us": post_avg,
                          "bytes_per_env": post_bytes, "pre_kernel_us": pre_avg, "pre_in_step_us": ms * 1e3 / args.steps - post_avg, "pre_bytes_per_env": pre_bytes,

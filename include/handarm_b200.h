@@ -793,6 +793,32 @@ typedef struct HaAdrQueueBuffers {
 size_t ha_sizeof_adr_queue_buffers(void);
 int ha_adr_queue_step(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_t all_envs, const HaAdrQueueBuffers* b, ha_stream_t stream);
 
+
+/* =====================================================================================================
+ * Cross-rank episode statistics over NVLink peer memory.  The env shards of a box never exchange data; the only
+ * cross-rank quantities are the <= 16 partial statistics of a step (sums, counts, [max, -min]).  A library all-reduce for 64
+ * bytes puts a collective kernel next to the persistent step kernels every few steps (measured: 8 GPUs at 92 % of linear with it,
+ * 99.6 % without).  ha_stats_exchange is one single-CTA launch instead: every rank stores its vector and a sequence tag straight
+ * into a slot of every peer's exchange buffer (peer pointers from CUDA IPC / torch symmetric memory), and reduces the vectors its
+ * peers stored during the PREVIOUS exchange (SUM, or MAX for the slots in max_mask), so nobody ever waits for a peer that is not
+ * already a whole exchange late.  Ring of HA_XCHG_RING slots: a writer can be at most one exchange ahead of a reader.
+ * ===================================================================================================== */
+#define HA_XCHG_RING 3
+#define HA_XCHG_MAX_RANKS 16
+#define HA_XCHG_SPIN_LIMIT 4000000        /* polls of a peer's tag before status is set and the slot is reduced as it is */
+typedef struct HaStatsExchange {
+  float** peer_bufs;         /* device array [world]: exchange buffer of every rank (own one included), each
+                                ha_stats_exchange_bytes(world) bytes, zero-initialised before the first exchange of any rank */
+  int32_t rank, world;
+  uint32_t max_mask;         /* bit i: statistic i is MAX-reduced, otherwise SUM */
+  int64_t* seq;              /* [1] exchanges done by this rank; zero-initialised */
+  int32_t* status;           /* [1] set to 1 if a peer's vector never arrived; zero-initialised */
+} HaStatsExchange;
+size_t ha_sizeof_stats_exchange(void);
+size_t ha_stats_exchange_bytes(int32_t world);
+/* stats: [HA_STATS_LEN] of this rank; reduced: [HA_STATS_LEN] whole-box values of the previous exchange (unchanged by the first) */
+int ha_stats_exchange(const HaStatsExchange* x, const float* stats, float* reduced, ha_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

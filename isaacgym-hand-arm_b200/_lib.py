@@ -117,6 +117,7 @@ HaDexAdrBuffers = STRUCTS["HaDexAdrBuffers"]
 HaNoiseParams = STRUCTS["HaNoiseParams"]
 HaObserverBuffers = STRUCTS["HaObserverBuffers"]
 HaAdrQueueBuffers = STRUCTS["HaAdrQueueBuffers"]
+HaStatsExchange = STRUCTS["HaStatsExchange"]
 
 _lib = None
 
@@ -217,6 +218,12 @@ def load():
     if ctypes.sizeof(HaAdrQueueBuffers) != lib.ha_sizeof_adr_queue_buffers():
         raise HandArmLibraryError("struct HaAdrQueueBuffers: ctypes size != C size")
     lib.ha_adr_queue_step.argtypes = [ctypes.c_int32] * 4 + [ctypes.c_void_p, ctypes.c_void_p]
+    lib.ha_sizeof_stats_exchange.restype = ctypes.c_size_t
+    if ctypes.sizeof(HaStatsExchange) != lib.ha_sizeof_stats_exchange():
+        raise HandArmLibraryError("struct HaStatsExchange: ctypes size != C size")
+    lib.ha_stats_exchange_bytes.restype = ctypes.c_size_t
+    lib.ha_stats_exchange_bytes.argtypes = [ctypes.c_int32]
+    lib.ha_stats_exchange.argtypes = [ctypes.c_void_p] * 4
     _lib = lib
     return lib
 

@@ -78,3 +78,78 @@ def summary(stats: torch.Tensor) -> Dict[str, float]:
         "true_objective_max": float(s[C["HA_KUKA_STAT_MAX_TRUE_OBJECTIVE"]]),
         "true_objective_min": -float(s[C["HA_KUKA_STAT_NEG_MIN_TRUE_OBJECTIVE"]]),
     }
+
+
+class PeerStatsExchange:
+    """Whole-box statistics without a collective launch: ``ha_stats_exchange`` stores this rank's partials into
+    every peer's exchange buffer over NVLink and reduces what the peers stored one exchange earlier.
+
+    ``peer_buffers``: one ``[ha_stats_exchange_bytes(world) / 4]`` float32 tensor per rank, this rank's own included, all
+    addressable from this device -- the views of a ``torch.distributed._symmetric_memory`` allocation (``connect``), or plain
+    tensors of one device when several ranks are emulated on one GPU (tests).  ``exchange(stats)`` returns the derived whole-box
+    vector of the PREVIOUS call (one exchange late, like the side-stream all-reduce it replaces); the first call returns the
+    rank's own statistics.
+    """
+
+    def __init__(self, rank: int, world: int, peer_buffers, device):
+        import ctypes
+        self._ctypes = ctypes
+        self._lib = _lib.load()
+        self.rank, self.world, self.device = rank, world, torch.device(device)
+        assert len(peer_buffers) == world
+        need = int(self._lib.ha_stats_exchange_bytes(world)) // 4
+        for t in peer_buffers:
+            assert t.dtype == torch.float32 and t.numel() >= need and t.is_contiguous()
+        self._peer_buffers = list(peer_buffers)
+        self._ptrs = torch.tensor([t.data_ptr() for t in peer_buffers], dtype=torch.int64, device=self.device)
+        self._seq = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self._status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._reduced = torch.zeros(C["HA_STATS_LEN"], dtype=torch.float32, device=self.device)
+        self._first = True
+        x = _lib.HaStatsExchange()
+        x.peer_bufs = self._ptrs.data_ptr()
+        x.rank, x.world = rank, world
+        x.max_mask = sum(1 << i for i in _MAX_SLOTS)
+        x.seq = self._seq.data_ptr()
+        x.status = self._status.data_ptr()
+        self._x = x
+
+    @staticmethod
+    def buffer_numel(world: int) -> int:
+        return int(_lib.load().ha_stats_exchange_bytes(world)) // 4
+
+    @classmethod
+    def connect(cls, group=None, device=None) -> "PeerStatsExchange":
+        """One exchange buffer per rank in symmetric memory (CUDA IPC handles exchanged over the process group's store)."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        n = cls.buffer_numel(world)
+        buf = symm_mem.empty(n, dtype=torch.float32, device=device)
+        buf.zero_()
+        hdl = symm_mem.rendezvous(buf, group)
+        peers = [buf if r == rank else hdl.get_buffer(r, (n,), torch.float32) for r in range(world)]
+        torch.cuda.synchronize(device)
+        hdl.barrier()                      # every rank's buffer is zeroed before anyone stores into it
+        self = cls(rank, world, peers, device)
+        self._handle = hdl
+        return self
+
+    def exchange(self, stats: torch.Tensor) -> torch.Tensor:
+        assert stats.dtype == torch.float32 and stats.numel() >= C["HA_STATS_LEN"] and stats.device == self.device
+        ct = self._ctypes
+        stream = ct.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        if self._first:
+            self._reduced.copy_(stats[:C["HA_STATS_LEN"]])
+            self._first = False
+        _lib.check(self._lib.ha_stats_exchange(ct.byref(self._x), ct.c_void_p(stats.data_ptr()), ct.c_void_p(self._reduced.data_ptr()), stream))
+        return self._reduced
+
+    def reduced(self) -> torch.Tensor:
+        """Derived whole-box vector of the last completed exchange."""
+        return derive(self._reduced)
+
+    def status(self) -> int:
+        return int(self._status.item())

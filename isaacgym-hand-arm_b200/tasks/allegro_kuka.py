@@ -485,6 +485,12 @@ class AllegroKukaBase(VecTask):
         self.finalize_stats()
         return self._stats
 
+    @property
+    def stats_folded(self) -> torch.Tensor:
+        """The statistics vector as the last pre step (or ``finalize_stats``) left it: no launch, one post step old inside a
+        step loop.  What a per-epoch consumer (logging, cross-rank exchange) reads without touching the stream."""
+        return self._stats
+
     def compute_observations(self):
         """allegro_kuka_base.py:991-1089 only (used by VecTask.reset()): obs + lazy init, no reward."""
         self._require_engine()
