@@ -798,25 +798,27 @@ int ha_adr_queue_step(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_
  * Cross-rank episode statistics over NVLink peer memory.  The env shards of a box never exchange data; the only
  * cross-rank quantities are the <= 16 partial statistics of a step (sums, counts, [max, -min]).  A library all-reduce for 64
  * bytes puts a collective kernel next to the persistent step kernels every few steps (measured: 8 GPUs at 92 % of linear with it,
- * 99.6 % without).  ha_stats_exchange is one single-CTA launch instead: every rank stores its vector and a sequence tag straight
- * into a slot of every peer's exchange buffer (peer pointers from CUDA IPC / torch symmetric memory), and reduces the vectors its
- * peers stored during the PREVIOUS exchange (SUM, or MAX for the slots in max_mask), so nobody ever waits for a peer that is not
- * already a whole exchange late.  Ring of HA_XCHG_RING slots: a writer can be at most one exchange ahead of a reader.
+ * 99.6 % without).  ha_stats_exchange is one single-CTA launch instead, wait-free on both sides: every rank stores its vector
+ * into slot (exchange number % HA_XCHG_RING) of every peer's exchange buffer (peer pointers from CUDA IPC / torch symmetric
+ * memory; slot tag = -number while under construction, = number when complete, then head[rank] = number), and reduces the newest
+ * exchange that every rank has published (min over head[]), reading its W vectors between two looks at their tags.  SUM in rank
+ * order (the same bits on every rank), MAX for the slots in max_mask.  A late rank delays the exchange number the others reduce,
+ * never the others; a rank more than HA_XCHG_RING - 2 exchanges behind makes the others skip (status = 2) until it catches up.
  * ===================================================================================================== */
-#define HA_XCHG_RING 3
+#define HA_XCHG_RING 16
 #define HA_XCHG_MAX_RANKS 16
-#define HA_XCHG_SPIN_LIMIT 4000000        /* polls of a peer's tag before status is set and the slot is reduced as it is */
 typedef struct HaStatsExchange {
   float** peer_bufs;         /* device array [world]: exchange buffer of every rank (own one included), each
                                 ha_stats_exchange_bytes(world) bytes, zero-initialised before the first exchange of any rank */
   int32_t rank, world;
   uint32_t max_mask;         /* bit i: statistic i is MAX-reduced, otherwise SUM */
-  int64_t* seq;              /* [1] exchanges done by this rank; zero-initialised */
-  int32_t* status;           /* [1] set to 1 if a peer's vector never arrived; zero-initialised */
+  int64_t* seq;              /* [2]: exchanges done by this rank, number of the last exchange reduced; zero-initialised */
+  int32_t* status;           /* [1]: 2 = a peer fell a whole ring behind at some point; zero-initialised */
 } HaStatsExchange;
 size_t ha_sizeof_stats_exchange(void);
 size_t ha_stats_exchange_bytes(int32_t world);
-/* stats: [HA_STATS_LEN] of this rank; reduced: [HA_STATS_LEN] whole-box values of the previous exchange (unchanged by the first) */
+/* stats: [HA_STATS_LEN] of this rank; reduced: [HA_STATS_LEN] whole-box values of the newest complete exchange (left as it is
+ * while there is none) */
 int ha_stats_exchange(const HaStatsExchange* x, const float* stats, float* reduced, ha_stream_t stream);
 
 #ifdef __cplusplus

@@ -82,13 +82,13 @@ def summary(stats: torch.Tensor) -> Dict[str, float]:
 
 class PeerStatsExchange:
     """Whole-box statistics without a collective launch: ``ha_stats_exchange`` stores this rank's partials into
-    every peer's exchange buffer over NVLink and reduces what the peers stored one exchange earlier.
+    every peer's exchange buffer over NVLink and reduces the newest exchange that all ranks have published (wait-free).
 
     ``peer_buffers``: one ``[ha_stats_exchange_bytes(world) / 4]`` float32 tensor per rank, this rank's own included, all
     addressable from this device -- the views of a ``torch.distributed._symmetric_memory`` allocation (``connect``), or plain
-    tensors of one device when several ranks are emulated on one GPU (tests).  ``exchange(stats)`` returns the derived whole-box
-    vector of the PREVIOUS call (one exchange late, like the side-stream all-reduce it replaces); the first call returns the
-    rank's own statistics.
+    tensors of one device when several ranks are emulated on one GPU (tests).  ``exchange(stats)`` returns the whole-box partials
+    of the newest complete exchange (normally the previous call's: one exchange late, like the side-stream all-reduce it
+    replaces); until there is one it returns the rank's own statistics.
     """
 
     def __init__(self, rank: int, world: int, peer_buffers, device):
@@ -102,7 +102,7 @@ class PeerStatsExchange:
             assert t.dtype == torch.float32 and t.numel() >= need and t.is_contiguous()
         self._peer_buffers = list(peer_buffers)
         self._ptrs = torch.tensor([t.data_ptr() for t in peer_buffers], dtype=torch.int64, device=self.device)
-        self._seq = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self._seq = torch.zeros(2, dtype=torch.int64, device=self.device)
         self._status = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._reduced = torch.zeros(C["HA_STATS_LEN"], dtype=torch.float32, device=self.device)
         self._first = True
