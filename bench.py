@@ -380,7 +380,9 @@ def measure(args, layout, device, rank, world, local, headline=True):
                 xchg = PeerStatsExchange.connect(device=device)
                 probe = torch.arange(16, device=device, dtype=torch.float32) * (rank + 1) + 0.25
                 xchg.exchange(probe)
-                got = xchg.exchange(probe).clone()          # the second call returns the reduction of the first
+                torch.cuda.synchronize()
+                dist.barrier()                              # the exchange never waits: make sure everyone has published number 1
+                got = xchg.exchange(probe).clone()          # ... so that the second call returns its reduction
                 want, wmax = probe.clone(), probe.clone()
                 dist.all_reduce(want)
                 dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
