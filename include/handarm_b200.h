@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define HA_ABI_VERSION 5
+#define HA_ABI_VERSION 6
 
 #define HA_OK 0
 #define HA_ERR_INVALID (-1)   /* bad argument / unsupported dimension */
@@ -147,6 +147,9 @@ typedef struct HaKukaParams {
   int32_t object_slot;
   int32_t goal_slot;
   int32_t state_layout;     /* HA_STATE_* */
+  /* test / tuning hook: > 0 forces the CTA count of the persistent single-arm post grid (capped at HA_KUKA_STAT_SLOTS), so a
+   * small env count can exercise the many-tiles-per-CTA regime of the headline size; 0: one full wave of resident CTAs */
+  int32_t post_grid;
 
   float palm_offset[3];
   float tip_offset[HA_MAX_TIPS][3];
@@ -175,7 +178,7 @@ typedef struct HaKukaParams {
   float reset_dof_vel_noise;
   float two_arm_x_ofs;      /* two arms: +-x offset of the goal side (0.75) */
   float two_arm_obj_x_ofs;  /* two arms: +-x offset of the object side (table_width / 2 - 0.2) */
-  float reserved_f[6];
+  float reserved_f[5];
 } HaKukaParams;
 
 /* values that change while training (tolerance curriculum); they live in

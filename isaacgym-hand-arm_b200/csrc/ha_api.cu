@@ -28,6 +28,13 @@ bool pdl_enabled() {
   return v == 1;
 }
 
+int device_sm_count() {
+  static int count[kMaxDevices] = {};
+  const int dev = current_device();
+  if (count[dev] == 0) cudaDeviceGetAttribute(&count[dev], cudaDevAttrMultiProcessorCount, dev);
+  return count[dev];
+}
+
 int check_cuda(cudaError_t e, const char* what) {
   if (e == cudaSuccess) return HA_OK;
   return set_error(HA_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));

@@ -63,7 +63,8 @@ int validate_dex(const HaDexParams* p, const HaDexBuffers* b) {
 }
 
 int launch_dex_post(const HaDexParams* p, const HaDexBuffers* b, const float* ext_rand, int mode, cudaStream_t st) {
-  static bool configured = false;
+  static ha::PerDeviceFlag flag;
+  bool& configured = flag.here();
   const size_t smem = ha::dex_post_smem_bytes();
   if (!configured) {
     int rc = ha::check_cuda(cudaFuncSetAttribute(ha::dex_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),

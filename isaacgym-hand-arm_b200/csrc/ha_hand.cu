@@ -55,7 +55,8 @@ int validate_hand(const HaHandParams* p, const HaHandBuffers* b) {
 }
 
 int launch_hand_post(const HaHandParams* p, const HaHandBuffers* b, int mode, cudaStream_t st) {
-  static bool configured = false;
+  static ha::PerDeviceFlag flag;
+  bool& configured = flag.here();
   const size_t smem = ha::hand_post_smem_bytes(p->n_dofs, p->n_actions, p->is_shadow ? p->n_tips : 0);
   if (!configured) {
     const size_t smem_max = ha::hand_post_smem_bytes(HA_HAND_MAX_DOFS, HA_HAND_MAX_DOFS, HA_HAND_MAX_TIPS);

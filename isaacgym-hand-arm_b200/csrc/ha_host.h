@@ -11,6 +11,19 @@ inline bool aligned8(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 7
 // true iff HA_PDL=1: kernels are launched with programmatic stream serialization (the launch of kernel k+1
 // overlaps the drain of kernel k; works in eager streams and under stream capture into CUDA graphs)
 bool pdl_enabled();
+// Per-device launch state: function attributes (cudaFuncSetAttribute) and the SM count belong to a device, not to the process,
+// so a process that drives several GPUs configures each one the first time it launches there.
+constexpr int kMaxDevices = 64;
+inline int current_device() {
+  int d = 0;
+  cudaGetDevice(&d);
+  return (d >= 0 && d < kMaxDevices) ? d : 0;
+}
+int device_sm_count();     // SM count of the current device (cached per device)
+struct PerDeviceFlag {     // "configured on this device yet?"
+  bool done[kMaxDevices] = {};
+  bool& here() { return done[current_device()]; }
+};
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream, Args&&... args) {

@@ -32,6 +32,7 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   for (int t = 0; t < p->n_tips; ++t)
     HA_REQUIRE(p->tip_body[t] >= 0 && p->tip_body[t] < p->n_bodies, "tip_body[%d] out of range", t);
   HA_REQUIRE(p->success_steps >= 1, "success_steps must be >= 1");
+  HA_REQUIRE(p->post_grid >= 0, "post_grid must be >= 0 (got %d)", p->post_grid);
   const void* need[] = {b->root_state, b->rigid_body_state, b->dof_state, b->object_actor, b->goal_actor, b->hand_actor,
                         b->object_init_state, b->object_keypoint_offsets, b->object_scales, b->goal_states,
                         b->obs_buf, b->rew_buf, b->reset_buf, b->reset_goal_buf, b->progress_buf, b->timeout_buf, b->successes,
@@ -66,17 +67,17 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
   return HA_OK;
 }
 
-int post_grid_limit(int blocks_per_sm) {
-  static int sm_count = 0;
-  static int override_grid = -1;
-  if (sm_count == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-    const char* e = getenv("HA_POST_GRID");      // tuning hook: force the persistent grid size
-    override_grid = e ? atoi(e) : 0;
+// CTAs of the persistent post grid: HaKukaParams.post_grid (test / tuning hook, per call) wins over the environment
+// variable HA_POST_GRID (A/B runs of a whole process), which wins over one full wave of resident CTAs.
+int post_grid_limit(const HaKukaParams* p, int blocks_per_sm) {
+  static int env_grid = -1;
+  if (env_grid < 0) {
+    const char* e = getenv("HA_POST_GRID");
+    env_grid = e ? atoi(e) : 0;
+    if (env_grid < 0) env_grid = 0;
   }
-  return override_grid > 0 ? override_grid : sm_count * blocks_per_sm;
+  if (p->post_grid > 0) return p->post_grid;
+  return env_grid > 0 ? env_grid : ha::device_sm_count() * blocks_per_sm;
 }
 
 #ifndef HA_POST_NS
@@ -87,7 +88,8 @@ constexpr int kPostNS = HA_POST_NS;   // cp.async stages per CTA (1: seven singl
 template <int K, bool SOA>
 int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {
   using S = ha::KukaPostSmem<K, kPostNS>;
-  static int blocks_per_sm = 0;
+  static int per_device[ha::kMaxDevices] = {};
+  int& blocks_per_sm = per_device[ha::current_device()];
   if (blocks_per_sm == 0) {
     int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka_post_kernel<K, SOA, kPostNS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
                             "cudaFuncSetAttribute(kuka_post_kernel)");
@@ -100,7 +102,7 @@ int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStr
   }
   // persistent CTAs: one wave of resident CTAs walks the 32-env tiles
   const int n_tiles = (p->n_envs + ha::kTile - 1) / ha::kTile;
-  int limit = post_grid_limit(blocks_per_sm);
+  int limit = post_grid_limit(p, blocks_per_sm);
   if (limit > HA_KUKA_STAT_SLOTS) limit = HA_KUKA_STAT_SLOTS;        // one statistics slot per CTA
   const int grid = n_tiles < limit ? n_tiles : limit;
   return ha::check_cuda(ha::launch(ha::kuka_post_kernel<K, SOA, kPostNS>, grid, ha::kPostThreads, sizeof(S), st, *p, *b, mode),
@@ -110,7 +112,8 @@ int launch_post(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStr
 template <int K>
 int launch_post2(const HaKukaParams* p, const HaKukaBuffers* b, int mode, cudaStream_t st) {
   using S = ha::Kuka2PostSmem<K>;
-  static bool configured = false;
+  static ha::PerDeviceFlag flag;
+  bool& configured = flag.here();
   if (!configured) {
     int rc = ha::check_cuda(cudaFuncSetAttribute(ha::kuka2_post_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S)),
                             "cudaFuncSetAttribute(kuka2_post_kernel)");

@@ -62,12 +62,7 @@ int ha_dr_noise_apply(const HaNoiseParams* p, const float* x, const float* corr,
   HA_REQUIRE_ALIGNED16(out);
   if (ext_white) HA_REQUIRE_ALIGNED16(ext_white);
   if (count == 0) return HA_OK;
-  static int sm_count = 0;
-  if (sm_count == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-  }
+  const int sm_count = ha::device_sm_count();
   const size_t want = ((count >> 2) + 255) / 256 + 1;
   const int grid = (int)(want < (size_t)sm_count * 8 ? want : (size_t)sm_count * 8);      // persistent: 8 CTAs of 256 threads per SM
   return ha::check_cuda(ha::launch(ha::dr_noise_kernel, grid, 256, 0, (cudaStream_t)stream, *p, x, corr, out, count,

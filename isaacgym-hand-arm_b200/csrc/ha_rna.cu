@@ -163,12 +163,7 @@ int ha_rna_bias_act(float* x, const float* bias, const float* mask, int32_t relu
   if (mask) HA_REQUIRE_ALIGNED16(mask);
   if (rows == 0) return HA_OK;
   const size_t nvec = rows * (size_t)(cols / 4);
-  static int sm_count = 0;
-  if (sm_count == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-  }
+  const int sm_count = ha::device_sm_count();
   const size_t want = (nvec + 255) / 256;
   const int grid = (int)(want < (size_t)sm_count * 8 ? want : (size_t)sm_count * 8);
   return ha::check_cuda(ha::launch(ha::rna_bias_act_kernel, grid, 256, 0, (cudaStream_t)stream, x, bias, mask, (int)relu, nvec, (int)(cols / 4)),

@@ -422,7 +422,8 @@ int launch_tc_tiles(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, 
   if ((rc = make_map(&ma_lo, a_lo, g.M, g.K))) return rc;
   if ((rc = make_map(&mw_hi, w_hi, g.N, g.K))) return rc;
   if ((rc = make_map(&mw_lo, w_lo, g.N, g.K))) return rc;
-  static bool configured = false;
+  static ha::PerDeviceFlag flag;
+  bool& configured = flag.here();
   if (!configured) {
     rc = ha::check_cuda(cudaFuncSetAttribute(ha::rna_gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ha::kTcSmemBytes),
                         "cudaFuncSetAttribute(rna_gemm_tc_kernel)");
@@ -460,15 +461,13 @@ int launch_tc(const ha::RnaTcArgs& g, const void* a_hi, const void* a_lo, const 
   if ((rc = make_map(&ma_lo, a_lo, g.M, g.K, ha::kBM, ha::kPBK))) return rc;
   if ((rc = make_map(&mw_hi, w_hi, g.N, g.K, ha::kPBN, ha::kPBK))) return rc;
   if ((rc = make_map(&mw_lo, w_lo, g.N, g.K, ha::kPBN, ha::kPBK))) return rc;
-  static bool configured = false;
-  static int sm_count = 0;
+  static ha::PerDeviceFlag flag;
+  bool& configured = flag.here();
+  const int sm_count = ha::device_sm_count();
   if (!configured) {
     rc = ha::check_cuda(cudaFuncSetAttribute(ha::rna_gemm_tc_persistent_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ha::kTcPSmemBytes),
                         "cudaFuncSetAttribute(rna_gemm_tc_persistent_kernel)");
     if (rc) return rc;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
     configured = true;
   }
   const int n_tiles = (g.N / ha::kPBN) * ((g.M + ha::kBM - 1) / ha::kBM);

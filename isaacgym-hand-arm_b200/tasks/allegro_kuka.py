@@ -371,6 +371,12 @@ class AllegroKukaBase(VecTask):
         """Seed of the in-kernel Philox stream (fast mode); the step counter restarts at 0."""
         self._write_dynamic(seed=int(seed))
 
+    def set_post_grid(self, ctas: int):
+        """Test / tuning hook (HaKukaParams.post_grid): force the CTA count of the persistent post grid; 0 restores one full wave.
+        A small grid makes a small env block walk many tiles per CTA, the regime of the 32768-env headline size."""
+        self._params.post_grid = int(ctas)
+        self._observe_params.post_grid = int(ctas)
+
     def _stream(self) -> ctypes.c_void_p:
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 

@@ -61,10 +61,11 @@ def assert_state_close(got, want, keys_exact=EXACT, keys_float=FLOAT, ctx=""):
         assert not bad.any(), f"{ctx}{k}: {int(bad.sum())} of {g.numel()} beyond tolerance, worst |d|={(g - w).abs().max():.3e}"
 
 
-def run_both(n, seed, fresh, steps=2, overrides=None, consts=None):
+def run_both(n, seed, fresh, steps=2, overrides=None, consts=None, post_grid=0):
     c = consts or ko.KukaConsts()
     st = ks.make_state(n, seed=seed, c=c, fresh=fresh)
     task = kh.make_task(n, overrides=overrides)
+    task.set_post_grid(post_grid)
     kh.load_state(task, st)
     for step in range(steps):
         act, rnd = ks.make_actions(n, seed + step), ks.make_rnd(n, seed + step)
@@ -100,6 +101,43 @@ def run_both(n, seed, fresh, steps=2, overrides=None, consts=None):
 @pytest.mark.parametrize("fresh", [True, False])
 def test_kuka_step_matches_oracle(n, fresh):
     run_both(n, seed=11 + n, fresh=fresh, steps=3)
+
+
+# ---- the persistent multi-tile regime of K_post (the one the 32768-env benchmark runs) ----------------------------------
+# grid = min(tiles, 4 CTAs x 148 SMs): every case above is one tile per CTA.  At the headline size 432 of 592 CTAs walk two
+# tiles (second cp.async stage, prefetch under the first tile's compute, reuse of the observation tile, statistics carried
+# across tiles); a forced small grid (HaKukaParams.post_grid) drives many tiles through each CTA, both stage parities, with a
+# ragged last tile.
+@pytest.mark.parametrize("n", [32768, 32768 + 17])
+@pytest.mark.parametrize("fresh", [True, False])
+def test_kuka_headline_size_matches_oracle(n, fresh):
+    run_both(n, seed=3 + n, fresh=fresh, steps=2)
+
+
+@pytest.mark.parametrize("n,grid", [(4096, 8), (4096 + 5, 3), (2048 + 31, 5), (1000, 1), (65536 + 3, 0)])
+def test_kuka_many_tiles_per_cta(n, grid):
+    """16 / 43 / 13 / 32 tiles per CTA (even and odd counts, ragged last tile in either stage), and four waves of the default grid."""
+    run_both(n, seed=17 + n + grid, fresh=False, steps=2, post_grid=grid)
+
+
+def test_kuka_post_grid_does_not_change_results():
+    """The same state through grids of 1, 7, 64 CTAs and the default: bit-identical outputs and statistics (order-independent sums)."""
+    n = 3000
+    c = ko.KukaConsts()
+    outs = []
+    for grid in (0, 1, 7, 64):
+        st = ks.make_state(n, seed=77, c=c, fresh=False)
+        task = kh.make_task(n)
+        task.set_post_grid(grid)
+        kh.load_state(task, st)
+        task.ext_rand = ks.make_rnd(n, 5).cuda()
+        task.pre_physics_step(ks.make_actions(n, 5).cuda())
+        task.post_physics_step()
+        task.finalize_stats()
+        outs.append(kh.dump_state(task))
+    for o in outs[1:]:
+        for k in EXACT + FLOAT + ["stats"]:
+            assert torch.equal(o[k], outs[0][k]), k
 
 
 def test_kuka_success_steps_and_no_forces():

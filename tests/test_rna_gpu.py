@@ -21,8 +21,14 @@ def _load(net, w):
     net._wt = None
 
 
-@pytest.mark.parametrize("impl", ["tc", "fp32"])
-@pytest.mark.parametrize("n", [1, 33, 1000, 4096])
+# (n, impl).  The persistent tcgen05 kernel runs grid = min(tiles, SMs) CTAs over 128 x 256 tiles: up to 4096 envs every CTA owns at
+# most one tile; 5000 envs (40 row tiles: 80 / 160 / 80 tiles per layer, 160 % 148 != 0: twelve CTAs take a second tile) and
+# cfg 5's 16384 envs (128 row tiles: 256 / 512 tiles, 2-4 per CTA) exercise the TMEM accumulator ping-pong, the operand ring running
+# through tile boundaries and the mbarrier phase wrap.
+CASES = [(n, impl) for impl in ("tc", "fp32") for n in (1, 33, 1000, 4096)] + [(5000, "tc"), (16384, "tc"), (16384 + 77, "tc")]
+
+
+@pytest.mark.parametrize("n,impl", CASES)
 def test_rna_matches_oracle(n, impl):
     from handarm_b200.rna import RandomNetworkAdversary
     g = torch.Generator().manual_seed(5)
