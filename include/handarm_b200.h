@@ -796,6 +796,19 @@ typedef struct HaAdrQueueBuffers {
 size_t ha_sizeof_adr_queue_buffers(void);
 int ha_adr_queue_step(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_t all_envs, const HaAdrQueueBuffers* b, ha_stream_t stream);
 
+/* Allocation-free variant of ha_adr_queue_step.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and results as ha_adr_queue_step, but the three scratch fields of HaAdrQueueBuffers (list,
+ * state, block_counts) are IGNORED (may be NULL): the scratch is a file-scope static __device__ array inside the library
+ * (sizeof = 32 + 8 * HA_OBSERVER_MAX_CTAS + 4 * HA_ADR_STATIC_MAX_ENVS bytes, about 261 KB; every GPU that loads the library
+ * holds it until the process exits).  The call makes no cudaMalloc / cudaFree / allocating library call: one cudaMemsetAsync
+ * of the scratch's scan state (which must start at zero; the array keeps the previous call's contents) and the same two launches,
+ * all stream-ordered.  n_envs > HA_ADR_STATIC_MAX_ENVS returns HA_ERR_INVALID with a message naming the limit.
+ * All calls on one device share the one array: calls that overlap on the GPU (different streams, or graph branches) race --
+ * serialise them, or use ha_adr_queue_step with separate caller-provided scratch. */
+#define HA_ADR_STATIC_MAX_ENVS 65536
+int ha_adr_queue_step_static(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_t all_envs, const HaAdrQueueBuffers* b, ha_stream_t stream);
+
 
 /* =====================================================================================================
  * Cross-rank episode statistics over NVLink peer memory.  The env shards of a box never exchange data; the only

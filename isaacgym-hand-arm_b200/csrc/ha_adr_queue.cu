@@ -128,11 +128,79 @@ adr_extend_kernel(const int cap, const __grid_constant__ HaAdrQueueBuffers b) {
   }
 }
 
+// ---- scratch of ha_adr_queue_step_static: lives in the module image, so every GPU that loads the library holds it until exit ----
+struct AdrStaticScratch {
+  int64_t state[4];                              // scan state (list length, epoch, ticket, unused)
+  int64_t block_counts[HA_OBSERVER_MAX_CTAS];    // per-CTA counts tagged with the epoch
+  int32_t list[HA_ADR_STATIC_MAX_ENVS];          // finished boundary workers in env order
+};
+constexpr size_t kAdrStaticZeroBytes = offsetof(AdrStaticScratch, list);   // state + block_counts must start at zero for every call
+
 }  // namespace ha
+
+// File scope.  In host code this name is only a stand-in for the symbol (NOT a device address): the device address comes from
+// cudaGetSymbolAddress below, once per device.
+static __device__ __align__(256) unsigned char g_adr_static_scratch[sizeof(ha::AdrStaticScratch)];
+
+namespace {
+
+int adr_queue_launch(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_t all_envs, const HaAdrQueueBuffers& b, cudaStream_t stream) {
+  int grid = (n_envs + ha::kAdrThreads - 1) / ha::kAdrThreads;
+  if (grid > HA_OBSERVER_MAX_CTAS) grid = HA_OBSERVER_MAX_CTAS;
+  int per_cta = (n_envs + grid - 1) / grid;
+  per_cta = (per_cta + ha::kAdrThreads - 1) / ha::kAdrThreads * ha::kAdrThreads;
+  grid = (n_envs + per_cta - 1) / per_cta;
+  int rc = ha::check_cuda(ha::launch(ha::adr_compact_kernel, grid, ha::kAdrThreads, 0, stream, (int)n_envs, per_cta, (int)all_envs, b),
+                          "adr_compact_kernel launch");
+  if (rc) return rc;
+  return ha::check_cuda(ha::launch(ha::adr_extend_kernel, (int)n_queues, 128, 0, stream, (int)capacity, b), "adr_extend_kernel launch");
+}
+
+// device address of the static scratch on the CURRENT device; resolved once per device, with that device current
+int adr_static_scratch(ha::AdrStaticScratch** out) {
+  static ha::AdrStaticScratch* addr[ha::kMaxDevices] = {};
+  int dev = -1;
+  int rc = ha::check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+  if (rc) return rc;
+  HA_REQUIRE(dev >= 0 && dev < ha::kMaxDevices, "device ordinal %d beyond the %d the library keeps per-device state for", dev, ha::kMaxDevices);
+  if (addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    rc = ha::check_cuda(cudaGetSymbolAddress(&ptr, g_adr_static_scratch), "cudaGetSymbolAddress(g_adr_static_scratch)");
+    if (rc) return rc;
+    HA_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned a null address for the static scratch");
+    addr[dev] = static_cast<ha::AdrStaticScratch*>(ptr);
+  }
+  *out = addr[dev];
+  return HA_OK;
+}
+
+}  // namespace
 
 extern "C" {
 
 size_t ha_sizeof_adr_queue_buffers(void) { return sizeof(HaAdrQueueBuffers); }
+
+int ha_adr_queue_step_static(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_t all_envs, const HaAdrQueueBuffers* b, ha_stream_t stream) {
+  HA_REQUIRE(b != nullptr, "null buffers");
+  HA_REQUIRE(n_envs > 0 && n_queues > 0 && capacity > 0, "n_envs, n_queues and capacity must be positive");
+  HA_REQUIRE(n_envs <= HA_ADR_STATIC_MAX_ENVS,
+             "ha_adr_queue_step_static: n_envs %d exceeds HA_ADR_STATIC_MAX_ENVS (%d), the size of the library's static scratch; "
+             "use ha_adr_queue_step with caller-provided scratch", n_envs, HA_ADR_STATIC_MAX_ENVS);
+  HA_REQUIRE(b->reset_buf && b->worker_types && b->adr_modes && b->objective && b->queues && b->appended && b->summary,
+             "HaAdrQueueBuffers has a null input / output field (list, state and block_counts are ignored here)");
+  ha::AdrStaticScratch* scratch = nullptr;
+  int rc = adr_static_scratch(&scratch);
+  if (rc) return rc;
+  HaAdrQueueBuffers local = *b;                    // inputs and outputs stay the caller's; only the scratch pointers are ours
+  local.state = scratch->state;
+  local.block_counts = scratch->block_counts;
+  local.list = scratch->list;
+  // the array keeps the last call's contents: the scan state and the tagged counts must start at zero (the list is fully
+  // rewritten up to the length the first launch leaves in state[0]).  Stream-ordered, no allocation.
+  rc = ha::check_cuda(cudaMemsetAsync(scratch, 0, ha::kAdrStaticZeroBytes, (cudaStream_t)stream), "cudaMemsetAsync(static scratch)");
+  if (rc) return rc;
+  return adr_queue_launch(n_envs, n_queues, capacity, all_envs, local, (cudaStream_t)stream);
+}
 
 int ha_adr_queue_step(int32_t n_envs, int32_t n_queues, int32_t capacity, int32_t all_envs, const HaAdrQueueBuffers* b, ha_stream_t stream) {
   HA_REQUIRE(b != nullptr, "null buffers");
