@@ -7,8 +7,15 @@ line (see the driver contract in the task statement): ``value`` is device-reside
 ``e2e`` goes through ``VecTask.step`` with host buffers, ``roofline`` is the post-physics kernel
 against the measured HBM peak, ``cpu_baseline`` is the CPU oracle port on this box's host cores.
 
-``--impl reference`` times the reference's CPU implementation of the same path (the oracle port,
-or the real reference classes when /root/reference is present) instead of the CUDA path.
+``--impl reference`` times the reference's OWN CPU implementation of the same path instead of the CUDA path: the unmodified
+``AllegroKukaReorientation.pre_physics_step`` / ``post_physics_step`` (allegro_kuka_base.py:1355-1443), imported from
+``/root/reference`` or from the snapshot ``oracle/make_ref_snapshot.py`` leaves in ``oracle/_ref/`` at build time
+(``cpu_baseline.kind`` "reference"); only if neither exists the oracle port is timed (``kind`` "port").
+
+Timing method (whatever ``--steps`` / ``--warmup`` are): the K steps are whole CUDA-graph replays (a 16-step graph plus one
+remainder graph, never an eager tail), at least 3 replays of every graph and one statistics all-reduce run before the first
+event, and when K steps last less than 50 ms the K-step block is repeated ``reps`` times inside the timed region, each block
+between its own pair of events; ``ms_per_step`` is the median block / K, ``timed_region_s`` the whole region.
 """
 from __future__ import annotations
 
@@ -33,7 +40,7 @@ WORKLOAD = "AllegroKuka reorientation (23-DOF, keypoint reward), 32768 envs/GPU"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4000)
+    ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=200)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=32768, help="envs per GPU")
@@ -114,7 +121,35 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU arms
 # ------------------------------------------------------------------------------------------------
-def cpu_port_rate(n_envs: int, steps: int, warmup: int = 2):
+def bench_config(args):
+    """The workload description both arms print (identical keys and values, so the driver can match the two lines)."""
+    B, S, N = args.blocks, args.snapshots, args.envs
+    layout = "soa" if args.layout in ("both", "soa") else "isaacgym"
+    return {"workload": WORKLOAD, "envs_per_gpu": N, "state_layout": layout, "env_blocks": B, "snapshots_per_block": S,
+            "l2": f"inputs larger than L2: {B} env blocks x {S} simulator snapshots stepped round-robin (GPU arm; the CPU arm steps one block)",
+            "launch": "GPU arm: CUDA graphs (16 steps + one remainder graph), whole replays only; CPU arm: eager torch on all host threads",
+            "rng": "GPU arm: in-kernel Philox; CPU arm: torch's generator"}
+
+
+def _cpu_loop(step_fn, n_envs, steps, warmup, budget_s):
+    """Times ``steps`` calls of step_fn(i) after ``warmup`` untimed ones; ``steps <= 0`` or a sample that would exceed ``budget_s``
+    is cut to a bounded sample (and the actual count is returned)."""
+    step_fn(0)                                         # first call pays allocator / thread-pool / jit start-up
+    t0 = time.perf_counter()
+    step_fn(1)
+    one = max(time.perf_counter() - t0, 1e-4)
+    cap = max(3, int(budget_s / one))
+    steps = cap if steps <= 0 else min(steps, cap)
+    for i in range(max(0, warmup - 2)):
+        step_fn(i)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        step_fn(i)
+    dt = time.perf_counter() - t0
+    return n_envs * steps / dt, steps, dt
+
+
+def cpu_port_rate(n_envs: int, steps: int, warmup: int = 2, budget_s: float = 15.0):
     """env-steps/s of the CPU oracle port (torch eager on all host cores), pre + post per step."""
     from oracle import kuka_oracle as ko, kuka_state as ks
     cores = os.cpu_count() or 1
@@ -123,35 +158,77 @@ def cpu_port_rate(n_envs: int, steps: int, warmup: int = 2):
     st = ks.make_state(n_envs, seed=1, c=c, fresh=False)
     acts = [ks.make_actions(n_envs, s) for s in range(2)]
     rnds = [ks.make_rnd(n_envs, s) for s in range(2)]
-    if steps <= 0:            # bounded sample: about 15 s of CPU work
-        ko.pre_step(st, c, acts[0], rnds[0]); ko.post_step(st, c)          # first call pays allocator / thread-pool start-up
-        t0 = time.perf_counter()
-        ko.pre_step(st, c, acts[1], rnds[1]); ko.post_step(st, c)
-        one = time.perf_counter() - t0
-        steps = max(3, min(2000, int(15.0 / max(one, 1e-3))))
-    for i in range(warmup):
-        ko.pre_step(st, c, acts[i % 2], rnds[i % 2]); ko.post_step(st, c)
-    t0 = time.perf_counter()
-    for i in range(steps):
-        ko.pre_step(st, c, acts[i % 2], rnds[i % 2]); ko.post_step(st, c)
-    dt = time.perf_counter() - t0
-    return n_envs * steps / dt, cores, steps, dt
+
+    def step(i):
+        ko.pre_step(st, c, acts[i % 2], rnds[i % 2])
+        ko.post_step(st, c)
+
+    rate, steps, dt = _cpu_loop(step, n_envs, steps, warmup, budget_s)
+    return rate, cores, steps, dt
+
+
+def reference_available():
+    try:
+        from oracle import reference_loader as rl
+        return rl.reference_available()
+    except Exception:      # noqa: BLE001
+        return False
+
+
+def cpu_reference_rate(n_envs: int, steps: int, warmup: int = 2, budget_s: float = 15.0, device: str = "cpu"):
+    """env-steps/s of the reference's own classes: AllegroKukaReorientation.pre_physics_step + post_physics_step
+    (allegro_kuka_base.py:1355-1443, unmodified, torch's own generator), eager torch on all host cores (or on ``device``)."""
+    from oracle import kuka_oracle as ko, kuka_state as ks, reference_loader as rl
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    c = ko.KukaConsts()
+    st = ks.make_state(n_envs, seed=1, c=c, fresh=False)
+    env = rl.make_reference_kuka(st, c, device=device)
+    acts = [ks.make_actions(n_envs, s).to(device) for s in range(2)]
+    torch.manual_seed(1234)
+
+    def step(i):
+        env.pre_physics_step(acts[i % 2])
+        env.post_physics_step()
+        env.timeout_buf = (env.progress_buf >= env.max_episode_length - 1) & (env.reset_buf != 0)      # vec_task.py:424
+        if device != "cpu":
+            torch.cuda.synchronize()
+
+    rate, steps, dt = _cpu_loop(step, n_envs, steps, warmup, budget_s)
+    return rate, cores, steps, dt
+
+
+def cpu_arm(n_envs, steps, warmup, budget_s):
+    """(cpu_baseline dict, port dict or None): the reference's own code when it is reachable, else the oracle port."""
+    if reference_available():
+        rate, cores, k, dt = cpu_reference_rate(n_envs, steps, warmup, budget_s)
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "reference", "steps": k,
+               "sample": f"{k} steps x {n_envs} envs, the reference's own AllegroKukaReorientation.pre_physics_step + post_physics_step "
+                         f"(allegro_kuka_base.py:1355-1443, unmodified) on CPU torch, {cores} threads, {dt:.1f} s"}
+        return cpu
+    rate, cores, k, dt = cpu_port_rate(n_envs, steps, warmup, budget_s)
+    return {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "steps": k,
+            "sample": f"{k} steps x {n_envs} envs, torch-CPU oracle port of pre+post physics step, {cores} threads, {dt:.1f} s "
+                      "(reference snapshot oracle/_ref absent)"}
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    rate, cores, steps, dt = cpu_port_rate(args.envs, args.steps if args.steps < 1000 else 0, warmup=min(args.warmup, 3))
-    sample = f"{steps} steps x {args.envs} envs, torch-CPU oracle port of pre+post physics step, {dt:.1f} s"
+    warmup = max(args.warmup, 3)
+    cpu = cpu_arm(args.envs, args.steps, warmup, budget_s=90.0)
+    steps, rate = cpu["steps"], cpu["value"]
     line = {
-        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 3), "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "envs_per_gpu": args.envs},
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": warmup, "ms_per_step": 1e3 * args.envs / rate, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": bench_config(args),
+        "cpu_baseline": cpu,
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if steps != args.steps:
+        line["steps_timed"] = steps          # bounded sample: fewer steps than asked for were timed (CPU budget)
     print(json.dumps(line), flush=True)
 
 
@@ -258,21 +335,28 @@ def measure_other(key, device, steps, blocks=4, snapshots=2):
 
         per_graph = blocks * snapshots
 
-        def time_graph(g, reps):
+        def time_graph(g, region_ms=40.0):
+            """us per step: >= 3 warm replays, then as many replays as fill ``region_ms`` between one pair of events"""
             for _ in range(3):
                 g.replay()
             a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a0.record(stream)
-            for _ in range(reps):
+            g.replay()
+            a1.record(stream)
+            stream.synchronize()
+            k = int(min(20000, max(4, region_ms / max(a0.elapsed_time(a1), 1e-3))))
+            a0.record(stream)
+            for _ in range(k):
                 g.replay()
             a1.record(stream)
             stream.synchronize()
-            return a0.elapsed_time(a1) * 1e3 / (reps * per_graph)
+            time_graph.last_reps = k
+            return a0.elapsed_time(a1) * 1e3 / (k * per_graph)
 
-        reps = max(4, steps // per_graph)
-        step_us = time_graph(graph_of("step"), reps)
-        post_us = time_graph(graph_of("post"), reps)
-        pre_us = time_graph(graph_of("pre"), reps)
+        step_us = time_graph(graph_of("step"))
+        reps = time_graph.last_reps
+        post_us = time_graph(graph_of("post"))
+        pre_us = time_graph(graph_of("pre"))
         rna = None
         if has_rna:                       # DeXtreme default config: random_network_adversary.enable = True (allegro_hand_dextreme.py:864-879)
             for t in tasks:
@@ -280,7 +364,7 @@ def measure_other(key, device, steps, blocks=4, snapshots=2):
             for t, a in zip(tasks, actions):
                 one_step(t, a)
             stream.synchronize()
-            rna_step_us = time_graph(graph_of("step"), max(4, reps // 4))
+            rna_step_us = time_graph(graph_of("step"))
             net = tasks[0].rna_network
             rna_us = rna_step_us - step_us
             rna = {"ms_per_step_with_rna": rna_step_us * 1e-3, "value_with_rna": n / (rna_step_us * 1e-6), "rna_ms": rna_us * 1e-3,
@@ -350,6 +434,14 @@ def ncu_traffic(layout):
         return None
 
 
+def ncu_traffic_source():
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")
+    try:
+        return json.load(open(path)).get("_source")
+    except (OSError, ValueError):
+        return None
+
+
 def measure(args, layout, device, rank, world, local, headline=True):
     import torch.distributed as dist
     hbm_gbs, peak_src = peaks()
@@ -398,29 +490,43 @@ def measure(args, layout, device, rank, world, local, headline=True):
             if int(ok) == 0 and xchg is not None:
                 xchg, xchg_note = None, "nccl all_reduce (peer exchange failed on another rank)"
 
-    # one CUDA graph = S rounds over the B env blocks (B*S steps, 2 kernels each); the statistics exchange rides at its end
-    # (every argument of the launch lives in device memory, so the node replays as it is) on the vector the last pre step folded
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph, stream=stream):
-        for _ in range(S):
-            for t, a in zip(tasks, actions):
-                one_step(t, a)
-        if xchg is not None:
-            xchg.exchange(tasks[0].stats_folded)
+    # CUDA graphs of whole steps (2 kernels each) walking the B env blocks round-robin; every simulate() moves a block to its next
+    # snapshot.  The main graph holds B*S steps, the remainder graph steps % (B*S): K steps are always whole replays.  The
+    # statistics exchange (peer mode) rides at the end of the main graph (every argument of the launch lives in device memory).
     per_graph = B * S
+    n_graph, rest = divmod(args.steps, per_graph)
 
-    def run_steps(k):
-        n_graph, rest = divmod(k, per_graph)
-        for r in range(n_graph):
+    def capture(n_steps, with_xchg):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            for i in range(n_steps):
+                one_step(tasks[i % B], actions[i % B])
+            if with_xchg and xchg is not None:
+                xchg.exchange(tasks[0].stats_folded)
+        return g
+
+    graph = capture(per_graph, True)
+    graph_rest = capture(rest, False) if rest else None
+    replay_count = [0]
+
+    def stats_allreduce():
+        if world > 1 and xchg is None:          # one tiny all-reduce (sum half; the max half is analogous)
+            stats_sum.copy_(tasks[0].stats, non_blocking=True)
+            dist.all_reduce(stats_sum, async_op=True)
+
+    def run_block():
+        """Exactly args.steps steps: n_graph replays of the main graph + one of the remainder graph."""
+        for _ in range(n_graph):
             graph.replay()
-            for t in tasks:
-                t.advance_frames(S)
-            if world > 1 and (r + 1) % max(1, args.stats_interval) == 0:
-                if xchg is None:        # one tiny all-reduce per replay (sum half; the max half is analogous)
-                    stats_sum.copy_(tasks[0].stats, non_blocking=True)
-                    dist.all_reduce(stats_sum, async_op=True)
-        for i in range(rest):
-            one_step(tasks[i % B], actions[i % B])
+            replay_count[0] += 1
+            if replay_count[0] % max(1, args.stats_interval) == 0:
+                stats_allreduce()
+        if graph_rest is not None:
+            graph_rest.replay()
+            if n_graph == 0:                    # fewer steps than one main graph: the block is the statistics cadence
+                stats_allreduce()
+        for t in tasks:
+            t.advance_frames(max(1, args.steps // B))
 
     def barrier():
         torch.cuda.synchronize()
@@ -429,20 +535,47 @@ def measure(args, layout, device, rank, world, local, headline=True):
         torch.cuda.synchronize()
 
     with torch.cuda.stream(stream):
-        run_steps(max(args.warmup, 3))
+        # warm-up: >= 3 replays of every graph and one statistics all-reduce, whatever --warmup says; then --warmup steps' worth
+        for _ in range(3):
+            graph.replay()
+            if graph_rest is not None:
+                graph_rest.replay()
+        stats_allreduce()
+        blocks_warm = max(1, -(-max(args.warmup, 3) // max(args.steps, 1)))
+        for _ in range(blocks_warm):
+            run_block()
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # size of the timed region: one block probed with events; short blocks are repeated until the region is >= 50 ms
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record(stream)
+        run_block()
+        p1.record(stream)
+        barrier()
+        probe_ms = max(p0.elapsed_time(p1), 1e-3)
+        reps = int(min(5000, max(1, -(-60.0 // probe_ms))))
+        if world > 1:
+            treps = torch.tensor([reps], device=device)
+            dist.all_reduce(treps, op=dist.ReduceOp.MAX)
+            reps = int(treps)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+        barrier()
         with ClockSampler(local) as clk:
-            e0.record(stream)
-            run_steps(args.steps)
-            e1.record(stream)
+            t_wall = time.perf_counter()
+            ev[0].record(stream)
+            for r in range(reps):
+                run_block()
+                ev[r + 1].record(stream)
             barrier()
-        ms = e0.elapsed_time(e1)
+            t_wall = time.perf_counter() - t_wall
+        block_ms = sorted(ev[r].elapsed_time(ev[r + 1]) for r in range(reps))
+        ms = block_ms[reps // 2]                                  # median K-step block
+        region_ms = ev[0].elapsed_time(ev[reps])
     if world > 1:
-        tms = torch.tensor([ms], device=device)
+        tms = torch.tensor([ms, region_ms], device=device)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-        ms = float(tms)
+        ms, region_ms = float(tms[0]), float(tms[1])
     value = world * N * args.steps / (ms * 1e-3)
+    value_mean = world * N * args.steps * reps / (region_ms * 1e-3)
 
     # ---- per-kernel device times: one CUDA graph of only pre launches, one of only post launches
     # (same round-robin over the env blocks, so inputs are as cold as in the timed region); CUDA
@@ -459,22 +592,27 @@ def measure(args, layout, device, rank, world, local, headline=True):
                         t.post_physics_step()
         return g
 
-    def time_graph(g, reps):
+    def time_graph(g, launches, region_ms=50.0):
+        """us per launch: >= 3 warm replays, then as many replays as fill ``region_ms`` between one pair of events."""
         for _ in range(3):
             g.replay()
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a0.record(stream)
-        for _ in range(reps):
+        g.replay()
+        a1.record(stream)
+        stream.synchronize()
+        k = int(min(20000, max(4, region_ms / max(a0.elapsed_time(a1), 1e-3))))
+        a0.record(stream)
+        for _ in range(k):
             g.replay()
         a1.record(stream)
         stream.synchronize()
-        return a0.elapsed_time(a1) * 1e3 / (reps * per_graph)
+        return a0.elapsed_time(a1) * 1e3 / (k * launches)
 
     with torch.cuda.stream(stream):
-        reps = max(4, min(args.steps, 800) // per_graph)
         g_post, g_pre = kernel_graph("post"), kernel_graph("pre")
-        post_avg = time_graph(g_post, reps)
-        pre_avg = time_graph(g_pre, reps)
+        post_avg = time_graph(g_post, per_graph)
+        pre_avg = time_graph(g_pre, per_graph)
     lib = tasks[0]._lib
     import ctypes
     post_bytes = int(lib.ha_kuka_post_bytes_per_env_step(ctypes.byref(tasks[0]._params)))
@@ -488,16 +626,7 @@ def measure(args, layout, device, rank, world, local, headline=True):
         with torch.cuda.graph(g1, stream=stream):
             for _ in range(S):
                 one_step(tasks[0], actions[0])
-        for _ in range(5):
-            g1.replay()
-        w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = max(1, args.steps // S)
-        w0.record(stream)
-        for _ in range(reps):
-            g1.replay()
-        w1.record(stream)
-        stream.synchronize()
-    warm_value = N * reps * S / (w0.elapsed_time(w1) * 1e-3)
+        warm_value = N / (time_graph(g1, S) * 1e-6)
 
     # ---- concurrent env blocks: the B blocks are independent jobs, so a deployment that hosts several of them on one GPU may
     # step them on a stream each; the ramp and tail of one block's launches then overlap another block's (same graph size, same
@@ -512,19 +641,10 @@ def measure(args, layout, device, rank, world, local, headline=True):
                     s_.wait_stream(stream)
                     with torch.cuda.stream(s_):
                         for _ in range(S):
-                            one_step(t, a)
+                            one_step(t, a)          # S steps of this block, back to back on its own stream
                 for s_ in side:
                     stream.wait_stream(s_)
-            for _ in range(5):
-                gc.replay()
-            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            reps = max(1, args.steps // per_graph)
-            c0.record(stream)
-            for _ in range(reps):
-                gc.replay()
-            c1.record(stream)
-            stream.synchronize()
-        conc_value = world * N * reps * per_graph / (c0.elapsed_time(c1) * 1e-3)
+            conc_value = world * N / (time_graph(gc, per_graph) * 1e-6)
 
     # ---- end to end through VecTask.step with host buffers ----
     e2e = None
@@ -546,15 +666,31 @@ def measure(args, layout, device, rank, world, local, headline=True):
             h_to.copy_(extras["time_outs"], non_blocking=True)
             torch.cuda.current_stream().synchronize()
 
+        def timed_blocks(step_fn, warm):
+            """median wall time of a k-step block (device idle on both sides of every block); blocks repeat until >= 0.3 s are timed"""
+            for i in range(warm):
+                step_fn(i)
+            barrier()
+            times, total = [], 0.0
+            while total < 0.3 and len(times) < 200:
+                t_start = time.perf_counter()
+                for i in range(k):
+                    step_fn(i)
+                torch.cuda.synchronize()
+                times.append(time.perf_counter() - t_start)
+                total += times[-1]
+                if world > 1:                   # every rank runs the same number of blocks
+                    flag = torch.tensor([1.0 if (total < 0.3 and len(times) < 200) else 0.0], device=device)
+                    dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+                    if float(flag) > 0:
+                        total = min(total, 0.29)
+                    else:
+                        break
+            barrier()
+            return sorted(times)[len(times) // 2], len(times)
+
         with torch.cuda.stream(stream):
-            for i in range(5):
-                e2e_step(i)
-            barrier()
-            t_start = time.perf_counter()
-            for i in range(k):
-                e2e_step(i)
-            barrier()
-            dt_serial = time.perf_counter() - t_start
+            dt_serial, _ = timed_blocks(e2e_step, 8)
 
         # the same calls with one stream and one set of pinned result buffers per env block: the copies of one block overlap the
         # kernels and copies of the others (PCIe is full duplex); a block's results are read on the host after its own stream drained
@@ -573,53 +709,65 @@ def measure(args, layout, device, rank, world, local, headline=True):
                 h_out[blk][3].copy_(extras["time_outs"], non_blocking=True)
 
         stream.synchronize()
-        for i in range(2 * B):
-            e2e_step_pipelined(i)
-        barrier()
-        t_start = time.perf_counter()
-        for i in range(k):
-            e2e_step_pipelined(i)
-        barrier()
-        dt = time.perf_counter() - t_start
+        dt, e2e_blocks = timed_blocks(e2e_step_pipelined, 2 * B)
         if world > 1:
             tdt = torch.tensor([dt, dt_serial], device=device)
             dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
             dt, dt_serial = float(tdt[0]), float(tdt[1])
         v_multi, v_one = world * N * k / dt, world * N * k / dt_serial
         e2e = {"value": max(v_multi, v_one), "unit": UNIT, "h2d_bytes_per_step": N * 23 * 4,
-               "d2h_bytes_per_step": N * (t0.num_obs * 4 + 4 + 8 + 1), "steps": k,
+               "d2h_bytes_per_step": N * (t0.num_obs * 4 + 4 + 8 + 1), "steps": k, "blocks_timed": e2e_blocks,
                "mode": ("VecTask.step per env block on its own stream" if v_multi >= v_one else "VecTask.step on one stream, host sync every step")
-                       + f" ({B} blocks round-robin), pinned host actions in, obs / reward / reset / time_outs out every step",
+                       + f" ({B} blocks round-robin), pinned host actions in, obs / reward / reset / time_outs out every step; "
+                         "median wall time of a block of `steps` calls",
                "value_stream_per_block": v_multi, "value_one_stream": v_one}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline and headline:
-        rate, cores, csteps, cdt = cpu_port_rate(N, args.cpu_steps)
-        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{csteps} steps x {N} envs, torch-CPU oracle port of pre+post physics step, {cdt:.1f} s"}
+        cpu = cpu_arm(N, args.cpu_steps, 3, budget_s=15.0)
+        if cpu["kind"] == "reference":                       # the oracle port beside it (second figure), and the reference's eager
+            rate, cores, csteps, cdt = cpu_port_rate(N, 0, budget_s=6.0)      # path on this GPU as a context number
+            cpu["port"] = {"value": rate, "unit": UNIT, "cores": cores, "sample": f"{csteps} steps x {N} envs, torch-CPU oracle port, {cdt:.1f} s"}
+
+    ref_cuda = None
+    if rank == 0 and world == 1 and headline and not args.no_cpu_baseline and reference_available():
+        try:
+            rate, _, csteps, cdt = cpu_reference_rate(N, 0, 5, budget_s=4.0, device=device)
+            ref_cuda = {"value": rate, "unit": UNIT, "ms_per_step": 1e3 * N / rate, "steps": csteps,
+                        "what": "the reference's own classes stepped eagerly on this GPU (torch ATen launches, device-resident state, "
+                                "host-synchronised every step): the 'before' of the production path, a context number"}
+        except Exception as e:      # noqa: BLE001 -- context only
+            ref_cuda = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
 
     if rank == 0:
+        cfg = bench_config(args)
+        cfg["state_layout"] = layout
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
-            "config": {"workload": WORKLOAD, "envs_per_gpu": N, "state_layout": layout, "env_blocks": B, "snapshots_per_block": S,
-                       "l2": f"inputs larger than L2: {B} env blocks stepped round-robin, {B}x{N * (post_bytes + pre_bytes) / 1e6:.0f} MB "
-                             "algorithmic bytes per round", "launch": f"CUDA graph of {per_graph} steps", "rng": "in-kernel Philox", "stats_exchange": xchg_note},
+            "data": "synthetic", "config": cfg,
+            "reps": reps, "timed_region_s": region_ms * 1e-3, "value_mean_over_region": value_mean,
+            "timing": f"median of {reps} blocks of {args.steps} steps, each between its own CUDA events on the launching stream; "
+                      f"{n_graph} x {per_graph}-step graph + {rest}-step remainder graph per block; warm-up: 3 replays of every graph, "
+                      f"one statistics all-reduce, {blocks_warm} block(s); max over ranks",
+            "stats_exchange": xchg_note,
             "roofline": {"bound": "hbm", "kernel": f"kuka_post_kernel<K=4, SOA={int(layout == 'soa')}, NS=2>", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
-                         "frac": achieved / hbm_gbs, "traffic": ncu_traffic(layout), "peak_source": peak_src, "kernel_us": post_avg,
+                         "frac": achieved / hbm_gbs, "traffic": ncu_traffic(layout), "traffic_source": ncu_traffic_source(), "peak_source": peak_src, "kernel_us": post_avg,
                          "bytes_per_env": post_bytes, "pre_kernel_us": pre_avg, "pre_in_step_us": ms * 1e3 / args.steps - post_avg, "pre_bytes_per_env": pre_bytes,
-                         "step_frac": step_frac, "kernel_timing": "CUDA events around graph replays of only-post / only-pre launches; the only-pre replays see no resets "
+                         "step_frac": step_frac, "kernel_timing": "CUDA events around >= 50 ms of graph replays of only-post / only-pre launches; the only-pre replays see no resets "
                                           "(the masks are consumed by the first launch), pre_in_step_us = step - post is the pre launch with the step's resets"},
             "value_l2_warm": warm_value,
             "value_concurrent_blocks": conc_value,
             "clocks": clk.summary(),
-            "gpu_launches": 2 * args.steps,
+            "gpu_launches": 2 * args.steps * reps,
+            "gpu_launches_per_step": 2,
         }
         if e2e is not None:
             line["e2e"] = e2e
         if cpu is not None:
             line["cpu_baseline"] = cpu
+        if ref_cuda is not None:
+            line["reference_eager_cuda"] = ref_cuda
         return line
     return None
 

@@ -9,7 +9,7 @@ namespace ha {
 
 // thread = 4 consecutive elements: 128-bit loads / stores, one Philox block for the four white draws
 __global__ void __launch_bounds__(256)
-dr_noise_kernel(const __grid_constant__ HaNoiseParams p, const float* __restrict__ x, const float* __restrict__ corr, float* __restrict__ out,
+dr_noise_kernel(const __grid_constant__ HaNoiseParams p, const float* x, const float* __restrict__ corr, float* out,      // x may alias out (in place)
                 const size_t count, const float* __restrict__ ext_white) {
   Rng rng;
   rng.seed = p.rng_seed;
@@ -24,7 +24,7 @@ dr_noise_kernel(const __grid_constant__ HaNoiseParams p, const float* __restrict
   };
   const size_t nvec = count >> 2, stride = (size_t)gridDim.x * blockDim.x;
   for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) {
-    const float4 xv = __ldg(reinterpret_cast<const float4*>(x) + q), cv = __ldg(reinterpret_cast<const float4*>(corr) + q);
+    const float4 xv = reinterpret_cast<const float4*>(x)[q], cv = __ldg(reinterpret_cast<const float4*>(corr) + q);
     float4 w;
     if (ext_white) w = __ldg(reinterpret_cast<const float4*>(ext_white) + q);
     else {
@@ -39,7 +39,7 @@ dr_noise_kernel(const __grid_constant__ HaNoiseParams p, const float* __restrict
     float w;
     if (ext_white) w = __ldg(ext_white + tail);
     else w = gaussian ? rng.normal((int)(tail & 0x7fffffffu), 7) : rng.uniform((int)(tail & 0x7fffffffu), 7);
-    out[tail] = one(__ldg(x + tail), __ldg(corr + tail), w);
+    out[tail] = one(x[tail], __ldg(corr + tail), w);
   }
 }
 

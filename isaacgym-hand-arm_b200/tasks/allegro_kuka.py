@@ -282,9 +282,7 @@ class AllegroKukaBase(VecTask):
             p.dof_lower[d], p.dof_upper[d], p.dof_default[d] = float(lo[d]), float(hi[d]), float(dflt[d])
             p.dof_reset_noise[d] = self.reset_dof_pos_noise_arm if d % self.num_hand_arm_dofs < 7 else self.reset_dof_pos_noise_fingers
         self._lib.ha_kuka_fill_derived(ctypes.byref(p))
-        clamp = self.clamp_abs_observations if self.clamp_abs_observations > 0 else math.inf
-        clamp = min(clamp, self.clip_obs)            # clamp_obs (:1174-1176) then the VecTask clip (vec_task.py:432)
-        p.clamp_abs_obs = clamp if math.isfinite(clamp) else 0.0
+        p.clamp_abs_obs = self._kernel_clamp(True)
         p.lifting_bonus_threshold, p.lifting_bonus, p.lifting_rew_scale = self.lifting_bonus_threshold, self.lifting_bonus, self.lifting_rew_scale
         p.keypoint_rew_scale = self.keypoint_rew_scale
         p.distance_delta_rew_scale = self.distance_delta_rew_scale
@@ -370,6 +368,16 @@ class AllegroKukaBase(VecTask):
     def seed_rng(self, seed: int):
         """Seed of the in-kernel Philox stream (fast mode); the step counter restarts at 0."""
         self._write_dynamic(seed=int(seed))
+
+    def _kernel_clamp(self, with_vec_task_clip: bool) -> float:
+        clamp = self.clamp_abs_observations if self.clamp_abs_observations > 0 else math.inf
+        if with_vec_task_clip:
+            clamp = min(clamp, self.clip_obs)        # clamp_obs (:1174-1176) then the VecTask clip (vec_task.py:432)
+        return clamp if math.isfinite(clamp) else 0.0
+
+    def _set_in_kernel_obs_clip(self, on: bool) -> None:
+        if self._params is not None:
+            self._params.clamp_abs_obs = self._kernel_clamp(on)
 
     def set_post_grid(self, ctas: int):
         """Test / tuning hook (HaKukaParams.post_grid): force the CTA count of the persistent post grid; 0 restores one full wave.
@@ -533,6 +541,8 @@ class AllegroKukaReorientation(AllegroKukaBase):
         return [[1, 1, 1], [1, 1, -1], [-1, -1, 1], [-1, -1, -1]]
 
     def _extra_curriculum(self):
+        if torch.device(self.device).type == "cuda" and torch.cuda.is_current_stream_capturing():
+            return      # the rule reads a device mean on the host: it waits for the next eager step / advance_frames()
         tol, self.last_curriculum_update = tolerance_curriculum(
             self.last_curriculum_update, self.frame_since_restart, self.tolerance_curriculum_interval, self.prev_episode_successes,
             self.success_tolerance, self.initial_tolerance, self.target_tolerance, self.tolerance_curriculum_increment)

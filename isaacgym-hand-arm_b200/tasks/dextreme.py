@@ -481,6 +481,7 @@ class AllegroHandDextremeADR(VecTask):
         """The per-env tensor half of ADR ``apply_randomizations`` (adr_vec_task.py:740-758, :666-730 via :915-917;
         allegro_hand_dextreme.py:1392-1416) as one launch on the envs in ``reset_buf & ~apply_reset_buf`` (every env on the first
         call, like ``first_randomization``).  ``randomize_buf`` is accepted for signature parity; the kernel derives the same mask."""
+        self.last_step = self.control_steps          # adr_vec_task.py:939: self.last_step = self.gym.get_frame_count(self.sim)
         if self._adr_table is None:
             return
         self._require_engine()

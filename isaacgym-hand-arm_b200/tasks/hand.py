@@ -246,6 +246,10 @@ class _HandTask(VecTask):
         """Seed of the in-kernel Philox stream (fast mode); the step counter restarts at 0."""
         self._dynamic.copy_(torch.tensor([int(seed), 0], dtype=torch.int64))
 
+    def _set_in_kernel_obs_clip(self, on: bool) -> None:
+        if self._params is not None:
+            self._params.clip_obs = self.clip_obs if (on and math.isfinite(self.clip_obs)) else 0.0
+
     def _stream(self) -> ctypes.c_void_p:
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 

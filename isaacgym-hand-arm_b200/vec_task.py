@@ -139,6 +139,8 @@ class VecTask(Env):
         self.last_step = -1
         self.last_rand_step = -1
         self.control_steps = 0
+        self._obs_noise_active = False
+        self.return_obs_copy = bool(config["env"].get("returnObsCopy", False))
         self.create_sim()
         self.allocate_buffers()
         self.obs_dict: Dict[str, Any] = {}
@@ -173,8 +175,18 @@ class VecTask(Env):
         return torch.clamp(self.states_buf, -self.clip_obs, self.clip_obs).to(self.rl_device)
 
     def _obs_out(self) -> torch.Tensor:
-        # the clip of vec_task.py:432 happened inside the post-physics kernel; obs_buf is returned as is
-        return self.obs_buf if self.rl_device == self.device else self.obs_buf.to(self.rl_device)
+        """The clip of vec_task.py:432 happened inside the post-physics kernel (or with the noise).  ``obs_dict["obs"]`` ALIASES
+        ``obs_buf`` when rl_device == device: the next step overwrites it, where the reference hands out a fresh clamped tensor
+        every call.  rl_games copies the observation into its experience buffer before stepping again, so the 15 MB copy per step
+        is not paid by default; ``env.returnObsCopy: True`` (or ``task.return_obs_copy = True``) restores the reference's
+        semantics for callers that keep the tensor across steps."""
+        if self.rl_device != self.device:
+            return self.obs_buf.to(self.rl_device)
+        return self.obs_buf.clone() if self.return_obs_copy else self.obs_buf
+
+    def _set_in_kernel_obs_clip(self, on: bool) -> None:
+        """Task hook: fold the VecTask clip (vec_task.py:432) into the post kernel's store (``on``) or leave it to the caller
+        (``off``: observation noise is active and the reference clips after the noise)."""
 
     def step(self, actions: torch.Tensor) -> Tuple[Dict[str, torch.Tensor], torch.Tensor, torch.Tensor, Dict[str, Any]]:
         """vec_task.py:390-441."""
@@ -183,6 +195,10 @@ class VecTask(Env):
         if actions.device != torch.device(self.device):
             actions = actions.to(self.device, non_blocking=True)
         action_tensor = actions if not np.isfinite(self.clip_actions) else torch.clamp(actions, -self.clip_actions, self.clip_actions)
+        obs_noise = self.dr_randomizations.get("observations", None)
+        if bool(obs_noise) != self._obs_noise_active:      # the reference clips AFTER the noise: the in-kernel clip is off while it is on
+            self._obs_noise_active = bool(obs_noise)
+            self._set_in_kernel_obs_clip(not self._obs_noise_active)
         self.pre_physics_step(action_tensor)
         for _ in range(self.control_freq_inv):
             self.sim.simulate()
@@ -191,8 +207,11 @@ class VecTask(Env):
         if finalize is not None:          # extras of THIS step are exact when step() returns (a raw pre/post loop folds them one launch later)
             finalize()
         self.control_steps += 1
-        if self.dr_randomizations.get("observations", None):
-            self.obs_buf = self.dr_randomizations["observations"]["noise_lambda"](self.obs_buf)
+        if obs_noise:
+            # vec_task.py:427-432: noise, then the clip.  Applied IN PLACE: obs_buf stays the tensor the kernels are bound to (the
+            # reference rebinds self.obs_buf to the closure's result; rebinding here would leave the kernels writing elsewhere)
+            clip = float(self.clip_obs) if np.isfinite(self.clip_obs) else 0.0
+            obs_noise["noise_lambda"](self.obs_buf, out=self.obs_buf, clip=clip)
         self.extras["time_outs"] = self.timeout_buf.to(self.rl_device)
         self.obs_dict["obs"] = self._obs_out()
         if self.num_states > 0:

@@ -6,7 +6,8 @@ that ``isaacgymenvs/tasks/allegro_kuka/*.py`` import *from where they lie*, then
 with ``object.__new__`` + attribute injection and a recording fake ``gym``.  The reference's own
 ``pre_physics_step`` / ``post_physics_step`` then run on CPU torch on our synthetic state.
 
-Only usable where ``/root/reference`` exists (this container).  Nothing in the product imports it.
+Usable where ``/root/reference`` exists (the build container) or where ``oracle/_ref/`` holds the snapshot of the same files
+written by ``oracle/make_ref_snapshot.py`` (the GPU box).  Nothing in the product imports it.
 """
 from __future__ import annotations
 
@@ -20,7 +21,15 @@ from typing import Dict, List, Optional
 import numpy as np
 import torch
 
-REFERENCE_ROOT = os.environ.get("HANDARM_REFERENCE_ROOT", "/root/reference")
+def _default_root() -> str:
+    """``/root/reference`` in the build container; on the GPU box (where it does not exist) the snapshot of the same unmodified
+    files that ``oracle/make_ref_snapshot.py`` wrote to ``oracle/_ref/`` at build time (git-ignored, travels with the repo copy)."""
+    if os.path.isdir("/root/reference/isaacgymenvs/tasks"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = os.environ.get("HANDARM_REFERENCE_ROOT") or _default_root()
 
 
 def reference_available() -> bool:
@@ -147,19 +156,23 @@ KUKA_EPISODE_KEYS = ["raw_fingertip_delta_rew", "raw_hand_delta_penalty", "raw_l
                      "allegro_actions_penalty"]
 
 
-def make_reference_kuka(st: Dict[str, torch.Tensor], c) -> object:
+def make_reference_kuka(st: Dict[str, torch.Tensor], c, device: str = "cpu") -> object:
     """An ``AllegroKukaReorientation`` instance (reference class) aliasing the tensors of ``st``.
 
     ``st`` is the dict layout of ``oracle/kuka_state.py``; ``c`` a ``KukaConsts``.  The instance owns
     views of the same storage wherever the reference keeps views (``arm_hand_dof_pos`` ...).
+    ``device`` other than "cpu" moves the state there first (the reference's eager GPU path, a context number of ``bench.py``);
+    ``st`` then no longer aliases the instance's tensors.
     """
     mods = load_reference()
+    if device != "cpu":
+        st = {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in st.items()}
     env = object.__new__(mods["akr"].AllegroKukaReorientation)
     N = st["reset_buf"].shape[0]
     K = st["object_keypoint_offsets"].shape[1]
     e = env.__dict__
     e.update(
-        gym=FakeGym(), sim=None, device="cpu", rl_device="cpu", num_environments=N, viewer=None, debug_viz=False, headless=True,
+        gym=FakeGym(), sim=None, device=device, rl_device=device, num_environments=N, viewer=None, debug_viz=False, headless=True,
         num_arm_dofs=c.n_arm_dofs, num_hand_dofs=c.n_dofs - c.n_arm_dofs, num_hand_arm_dofs=c.n_dofs, num_finger_dofs=4,
         num_allegro_fingertips=c.n_tips, num_keypoints=K, obs_type="full_state", with_fingertip_force_sensors=False,
         with_dof_force_sensors=False, num_observations=st["obs_buf"].shape[1], privileged_actions=False, use_relative_control=False,
@@ -179,16 +192,16 @@ def make_reference_kuka(st: Dict[str, torch.Tensor], c) -> object:
         set_actor_root_state_object_indices=[], randomization_params={},
     )
     env.full_state_size = st["obs_buf"].shape[1]
-    env.force_decay = torch.tensor(c.force_decay, dtype=torch.float32)
-    env.force_prob_range = torch.tensor(c.force_prob_range, dtype=torch.float32)
+    env.force_decay = torch.tensor(c.force_decay, dtype=torch.float32, device=device)
+    env.force_prob_range = torch.tensor(c.force_prob_range, dtype=torch.float32, device=device)
     env.palm_offset = np.array(c.palm_offset, dtype=np.float32)
     env.fingertip_offsets = np.array(c.tip_offsets, dtype=np.float32)
-    env.target_volume_origin = torch.tensor(c.target_volume_origin, dtype=torch.float32)
-    env.target_volume_extent = torch.tensor(c.target_volume_extent, dtype=torch.float32)
+    env.target_volume_origin = torch.tensor(c.target_volume_origin, dtype=torch.float32, device=device)
+    env.target_volume_extent = torch.tensor(c.target_volume_extent, dtype=torch.float32, device=device)
     env.allegro_palm_handle = c.palm_body
-    env.allegro_fingertip_handles = torch.tensor(list(c.tip_bodies), dtype=torch.long)
-    env.object_rb_handles = torch.tensor([c.object_body], dtype=torch.long)
-    env.object_rb_masses = torch.tensor([c.object_mass], dtype=torch.float32)
+    env.allegro_fingertip_handles = torch.tensor(list(c.tip_bodies), dtype=torch.long, device=device)
+    env.object_rb_handles = torch.tensor([c.object_body], dtype=torch.long, device=device)
+    env.object_rb_masses = torch.tensor([c.object_mass], dtype=torch.float32, device=device)
     # simulator tensors and the reference's views of them (allegro_kuka_base.py:280-295)
     env.root_state_tensor = st["root_state"]
     env.rigid_body_states = st["rigid_body_state"].view(N, -1, 13)
@@ -206,11 +219,11 @@ def make_reference_kuka(st: Dict[str, torch.Tensor], c) -> object:
     env.arm_hand_dof_lower_limits = st["dof_lower"]
     env.arm_hand_dof_upper_limits = st["dof_upper"]
     env.hand_arm_default_dof_pos = st["dof_default"]
-    env.obj_keypoint_pos = torch.zeros(N, K, 3)
-    env.goal_keypoint_pos = torch.zeros(N, K, 3)
+    env.obj_keypoint_pos = torch.zeros(N, K, 3, device=device)
+    env.goal_keypoint_pos = torch.zeros(N, K, 3, device=device)
     env.action_torques = torch.zeros_like(st["rb_forces"])
     env.rewards_episode = {k: st["rewards_episode"][i] for i, k in enumerate(KUKA_EPISODE_KEYS)}
-    env.timeout_buf = torch.zeros(N, dtype=torch.long)
+    env.timeout_buf = torch.zeros(N, dtype=torch.long, device=device)
     return env
 
 

@@ -54,3 +54,47 @@ def test_step_applies_noise_closures():
     obs, rew, done, info = task.step(torch.zeros(256, 23, device="cuda:0"))
     assert torch.isfinite(obs["obs"]).all() and obs["obs"].shape == (256, 117)
     assert float(task.actions.abs().max()) > 0.0                   # the zero action arrived with noise
+
+
+def test_noised_observations_track_the_kernel_over_steps():
+    """Several steps with observation noise on: the returned observations follow the kernel's fresh observations every step (the
+    closure is applied in place on the tensor the kernels are bound to), stay within clip_obs, and the order is the reference's
+    (clamp_obs -> noise -> clip, vec_task.py:427-432)."""
+    from tests import kuka_harness as kh
+    n = 512
+    task = kh.make_task(n, device="cuda:0", snapshots=4)
+    twin = kh.make_task(n, device="cuda:0", snapshots=4)          # same seeds, no noise
+    for t in (task, twin):
+        t.sim.fill_kuka(goal_states=None)
+        t.seed_rng(5)
+    task.apply_randomizations({"frequency": 1, "observations": {"range": [0.0, 0.02], "operation": "additive", "distribution": "gaussian"}})
+    bound = task.obs_buf.data_ptr()
+    act = torch.zeros(n, 23, device="cuda:0")
+    prev = None
+    for step in range(4):
+        obs = task.step(act)[0]["obs"]
+        clean = twin.step(act)[0]["obs"]
+        assert task.obs_buf.data_ptr() == bound                   # never rebound
+        assert float(obs.abs().max()) <= task.clip_obs + 1e-6
+        inside = clean.abs() < task.clip_obs - 0.2                # away from the clip the difference is the noise alone
+        diff = (obs - clean)[inside]
+        assert abs(float(diff.mean())) < 2e-3 and abs(float(diff.std()) - 0.02) < 2e-3, (step, float(diff.mean()), float(diff.std()))
+        if prev is not None:
+            assert not torch.equal(prev, clean)                   # the simulator snapshots differ from step to step
+        prev = clean.clone()
+
+
+def test_step_can_return_a_fresh_observation_tensor():
+    """obs_dict["obs"] aliases obs_buf by default (documented); return_obs_copy restores the reference's fresh tensor per call."""
+    from tests import kuka_harness as kh
+    task = kh.make_task(128, device="cuda:0", snapshots=2)
+    task.sim.fill_kuka(goal_states=None)
+    act = torch.zeros(128, 23, device="cuda:0")
+    a = task.step(act)[0]["obs"]
+    assert a.data_ptr() == task.obs_buf.data_ptr()
+    task.return_obs_copy = True
+    b = task.step(act)[0]["obs"]
+    kept = b.clone()
+    c = task.step(act)[0]["obs"]
+    assert b.data_ptr() != task.obs_buf.data_ptr() and c.data_ptr() != b.data_ptr()
+    assert torch.equal(b, kept)                                   # last step's observation did not mutate

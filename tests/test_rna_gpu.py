@@ -74,3 +74,21 @@ def test_rna_feeds_the_dextreme_pre_step():
     assert task.rna_perturbation is not None and task.rna_perturbation.shape == (512, 16)
     lo, hi = task.discretised_dofs[:, 0], task.discretised_dofs[:, -1]
     assert (task.rna_perturbation >= lo - 1e-6).all() and (task.rna_perturbation <= hi + 1e-6).all()
+
+
+def test_rna_weights_are_resampled_at_the_configured_frequency():
+    """allegro_hand_dextreme.py:868 + adr_vec_task.py:939: last_step follows the frame count, so the adversary's weights and dropout
+    masks are re-drawn every weight_sample_freq steps (the attribute used to stay at -1 here)."""
+    from oracle import dextreme_oracle as dx
+    from tests.test_dextreme_parity_gpu import make_task
+    task = make_task(256, dx.DexConsts())
+    task.run_rna = True
+    task.adr_resample_on_step = True
+    task.random_adversary_weight_sample_freq = 3
+    calls = []
+    orig = task.rna_network._refresh
+    task.rna_network._refresh = lambda: (calls.append(task.last_step), orig())[1]
+    for _ in range(8):
+        task.step(torch.zeros(256, 16, device="cuda:0"))
+    assert task.last_step == 7
+    assert calls == [3, 6]
