@@ -231,7 +231,8 @@ typedef struct HaKukaBuffers {
   float* prev_targets;        /* [n_envs, dofs_per_env] */
   float* cur_targets;         /* [n_envs, dofs_per_env] */
   float* actions;             /* [n_envs, n_dofs] task-owned copy */
-  float* rb_forces;           /* [n_envs, n_bodies, 3] */
+  float* rb_forces;           /* HA_STATE_ISAACGYM: [n_envs, n_bodies, 3] (apply_rigid_body_force_tensors layout);
+                                 HA_STATE_SOA: [n_bodies, 3, n_envs] component planes like the state tensors */
   float* random_force_prob;   /* [n_envs] */
   /* ---- outputs for the simulator's *_indexed setters ---- */
   int32_t* root_reset_indices;  /* [2*n_envs] ascending actor rows */

@@ -154,6 +154,25 @@ __device__ __forceinline__ float ldg(const float* p) { return __ldg(p); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ---- in-kernel timeline (diagnostic builds only: -DHA_TRACE; see tools/trace_kernels.py) ----
+// Thread 0 of every CTA records the SM clock at named points and %globaltimer at CTA start / end into a device array that
+// ha_debug_trace_read copies out.  Compiles to nothing in the product build.
+#ifdef HA_TRACE
+struct HaTraceRec { unsigned long long gt0, gt1; long long c[14]; int smid, n; };
+constexpr int kTraceMaxCtas = 4096;
+static __device__ HaTraceRec g_ha_trace[2][kTraceMaxCtas];     // [0] pre kernel, [1] post kernel (one copy per translation unit; ha_kuka.cu's is read)
+__device__ __forceinline__ unsigned long long ha_globaltimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ int ha_smid() { int s; asm volatile("mov.u32 %0, %%smid;" : "=r"(s)); return s; }
+#define HA_TRACE_BEGIN(k) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas) { ha::HaTraceRec& r_ = ha::g_ha_trace[k][blockIdx.x]; \
+  r_.gt0 = ha::ha_globaltimer(); r_.smid = ha::ha_smid(); r_.n = 1; _Pragma("unroll") for (int i_ = 1; i_ < 14; ++i_) r_.c[i_] = 0; r_.c[0] = clock64(); } } while (0)
+#define HA_TRACE_POINT(k, i) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas && (i) < 14) ha::g_ha_trace[k][blockIdx.x].c[i] = clock64(); } while (0)   /* stores only: nothing the warp waits for */
+#define HA_TRACE_END(k) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas) ha::g_ha_trace[k][blockIdx.x].gt1 = ha::ha_globaltimer(); } while (0)
+#else
+#define HA_TRACE_BEGIN(k) do { } while (0)
+#define HA_TRACE_POINT(k, i) do { } while (0)
+#define HA_TRACE_END(k) do { } while (0)
+#endif
+
 // ---- cp.async (LDGSTS) ----
 __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");

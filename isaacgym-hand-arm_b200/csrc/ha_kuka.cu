@@ -9,6 +9,14 @@
 #include "ha_kuka2_post.cuh"
 #include "ha_kuka2_pre.cuh"
 
+#ifdef HA_TRACE
+// diagnostic builds only (not declared in the header): copies the records of the last pre / post launch to the host
+extern "C" int ha_debug_trace_read(void* dst, size_t bytes) {
+  if (bytes > sizeof(ha::HaTraceRec) * 2 * ha::kTraceMaxCtas) bytes = sizeof(ha::HaTraceRec) * 2 * ha::kTraceMaxCtas;
+  return ha::check_cuda(cudaMemcpyFromSymbol(dst, ha::g_ha_trace, bytes), "cudaMemcpyFromSymbol(g_ha_trace)");
+}
+#endif
+
 namespace {
 
 int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {

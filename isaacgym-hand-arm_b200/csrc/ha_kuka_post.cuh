@@ -257,12 +257,9 @@ __device__ __forceinline__ void kuka_fold_warp(const KukaStatFold& f, const int 
   }
   if ((tid & 31) == 0) red[tid >> 5] = v;
 }
-// after a CTA barrier: one thread writes stats[stat] and the value derived from it for extras (allegro_kuka_base.py:903-910)
-__device__ __forceinline__ void kuka_fold_finish(const HaKukaBuffers& b, const int stat, const int n_envs, const long long* red) {
+// one thread writes stats[stat] of the folded value and the value derived from it for extras (allegro_kuka_base.py:903-910)
+__device__ __forceinline__ void kuka_fold_store(const HaKukaBuffers& b, const int stat, const int n_envs, const long long v) {
   const bool is_max = stat_is_max(stat);
-  long long v = red[0];
-#pragma unroll
-  for (int w = 1; w < kThreads / 32; ++w) v = is_max ? (red[w] > v ? red[w] : v) : v + red[w];
   if (is_max) {
     if (v == kStatMaxInit) return;                      // no post step has run yet
     const float x = key_float(v);
@@ -276,6 +273,14 @@ __device__ __forceinline__ void kuka_fold_finish(const HaKukaBuffers& b, const i
   if (stat == HA_KUKA_STAT_SUM_REWARD) b.stats[HA_KUKA_STAT_MEAN_REWARD] = x * inv_n;
   if (stat == HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES) b.stats[HA_KUKA_STAT_MEAN_PREV_EP_SUCCESSES] = x * inv_n;
   if (stat == HA_KUKA_STAT_SUM_TRUE_OBJECTIVE) b.stats[HA_KUKA_STAT_MEAN_TRUE_OBJECTIVE] = x * inv_n;
+}
+// after a CTA barrier: one thread combines the warps' values (kuka_fold_warp) and stores the statistic
+__device__ __forceinline__ void kuka_fold_finish(const HaKukaBuffers& b, const int stat, const int n_envs, const long long* red) {
+  const bool is_max = stat_is_max(stat);
+  long long v = red[0];
+#pragma unroll
+  for (int w = 1; w < kThreads / 32; ++w) v = is_max ? (red[w] > v ? red[w] : v) : v + red[w];
+  kuka_fold_store(b, stat, n_envs, v);
 }
 
 __global__ void __launch_bounds__(kThreads) kuka_stats_finalize_kernel(const __grid_constant__ HaKukaBuffers b, const int n_envs) {
@@ -453,6 +458,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   const int stride = gridDim.x;
   int tile = blockIdx.x;
 
+  HA_TRACE_BEGIN(1);
   pdl_launch_dependents();      // the next kernel in the stream may start launching as our CTAs retire
   pdl_wait();                   // everything below reads what the previous kernel wrote
   float keypoint_tol = 0.f, tobj_scale = 0.f, tobj_offset = 0.f;
@@ -487,6 +493,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
 
   if (tile < n_tiles) kuka_post_issue<K, SOA>(p, b, sm.st[0], tile * kTile, min(kTile, n - tile * kTile), tid, &sm.mbar[0], sm.rowp);
   cp_async_commit();
+  HA_TRACE_POINT(1, 1);         // prologue done, first tile's copies issued
 
   for (int it = 0; tile < n_tiles; ++it, tile += stride) {
     ST& S = sm.st[NS == 2 ? (it & 1) : 0];
@@ -505,6 +512,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     cp_async_wait<(NS == 2 && !HA_LATE_PREFETCH) ? 1 : 0>();
     if (kuka_post_bulk_tile(SOA, n, env0)) mbar_wait(&sm.mbar[NS == 2 ? (it & 1) : 0], NS == 2 ? (it >> 1) & 1 : it & 1);
     __syncthreads();                                    // B1: this tile's inputs are in shared memory
+    HA_TRACE_POINT(1, 2 + 4 * it);
     if constexpr (NS == 2 && HA_LATE_PREFETCH) {
       // The next tile's reads start now, so they share the memory system with this tile's stores instead of with this tile's own
       // reads: issued up front, both stages of every CTA land together (the whole input, ~3.5 us) and only then do the stores start.
@@ -591,6 +599,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
       for (int c = 0; c < 3; ++c) W(L.scales + c, S.scales[lane * 3 + c]);
     }
     __syncthreads();                                    // B2: distances, kp_max and |vel| sums are visible to warp 3
+    HA_TRACE_POINT(1, 3 + 4 * it);
 
     // Observation tile store, split in two: every 128-bit word that holds none of the columns the state warp still has to write
     // (closest_kp .. reward, the last 9 of a row) is complete now and leaves through the three other warps while the state warp
@@ -741,7 +750,9 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     }
     const bool bulk_store = HA_BULK_STORE && (nvalid == kTile);   // 14976 contiguous bytes, 16-byte aligned on both sides
     if (bulk_store) fence_proxy_async_smem();           // the tile's generic-proxy writes, before the async proxy reads them
+    HA_TRACE_POINT(1, 4 + 4 * it);                     // this warp's work between B2 and B3 is done (early stores / reward chain)
     __syncthreads();                                    // B3: the observation tile is complete
+    HA_TRACE_POINT(1, 5 + 4 * it);
     if (bulk_store) {
       if (tid == 0) {                                   // the whole [32, OBS] tile leaves as one bulk copy
         bulk_s2g(b.obs_buf + (size_t)env0 * OBS, sm.obs, kTile * OBS * 4);
@@ -774,6 +785,11 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   cp_async_wait<0>();
   if (HA_BULK_STORE && tid == 0) bulk_wait_read0();     // shared memory must outlive the last bulk store's reads
   if (warp == 3 && mode == kPostFull) kuka_post_store_partials(b, acc, lane);   // every CTA of the grid fills its slot
+  HA_TRACE_POINT(1, 12);
+#ifdef HA_TRACE
+  if (tid == 0 && blockIdx.x < kTraceMaxCtas) g_ha_trace[1][blockIdx.x].c[13] = warp;      // role of the recording warp
+#endif
+  HA_TRACE_END(1);
 }
 
 }  // namespace ha

@@ -219,7 +219,13 @@ class AllegroKukaBase(VecTask):
         u0 = torch.rand(N, generator=gen).to(dev)
         self.random_force_prob = torch.exp((torch.log(self.force_prob_range_t[0]) - torch.log(self.force_prob_range_t[1])) * u0
                                            + torch.log(self.force_prob_range_t[1]))
-        self.rb_forces = torch.zeros((N, self.num_bodies, 3), **f)
+        if self.sim.state_layout == "soa" and self.num_arms == 1:
+            # component planes like the simulator state: [n_bodies, 3, N]; rb_forces keeps the reference's [N, n_bodies, 3] indexing as a view
+            self._rb_forces_planes = torch.zeros((self.num_bodies, 3, N), **f)
+            self.rb_forces = self._rb_forces_planes.permute(2, 0, 1)
+        else:
+            self._rb_forces_planes = None
+            self.rb_forces = torch.zeros((N, self.num_bodies, 3), **f)
         self.near_goal_steps = torch.zeros(N, dtype=torch.int, device=dev)
         self.lifted_object = torch.zeros(N, dtype=torch.bool, device=dev)
         self.closest_keypoint_max_dist = -torch.ones(N, **f)
@@ -341,7 +347,8 @@ class AllegroKukaBase(VecTask):
             lifted_object=self.lifted_object, closest_keypoint_max_dist=self.closest_keypoint_max_dist,
             closest_fingertip_dist=self.closest_fingertip_dist, furthest_hand_dist=self.furthest_hand_dist,
             rewards_episode=self._rewards_episode, episode_cumulative=self._episode_cumulative, prev_targets=self.prev_targets,
-            cur_targets=self.cur_targets, actions=self.actions, rb_forces=self.rb_forces, random_force_prob=self.random_force_prob,
+            cur_targets=self.cur_targets, actions=self.actions,
+            rb_forces=self.rb_forces if self._rb_forces_planes is None else self._rb_forces_planes, random_force_prob=self.random_force_prob,
             root_reset_indices=self.root_reset_indices, hand_reset_indices=self.hand_reset_indices, reset_counts=self.reset_counts,
             stats=self._stats, stat_accum=self._stat_accum, tickets=self._tickets, dynamic=self._dynamic)
         for name, t in self._bound.items():
