@@ -166,10 +166,12 @@ __device__ __forceinline__ int ha_smid() { int s; asm volatile("mov.u32 %0, %%sm
 #define HA_TRACE_BEGIN(k) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas) { ha::HaTraceRec& r_ = ha::g_ha_trace[k][blockIdx.x]; \
   r_.gt0 = ha::ha_globaltimer(); r_.smid = ha::ha_smid(); r_.n = 1; _Pragma("unroll") for (int i_ = 1; i_ < 14; ++i_) r_.c[i_] = 0; r_.c[0] = clock64(); } } while (0)
 #define HA_TRACE_POINT(k, i) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas && (i) < 14) ha::g_ha_trace[k][blockIdx.x].c[i] = clock64(); } while (0)   /* stores only: nothing the warp waits for */
+#define HA_TRACE_POINT_IF(k, i, cond) do { if ((cond) && blockIdx.x < ha::kTraceMaxCtas && (i) < 14) ha::g_ha_trace[k][blockIdx.x].c[i] = clock64(); } while (0)
 #define HA_TRACE_END(k) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas) ha::g_ha_trace[k][blockIdx.x].gt1 = ha::ha_globaltimer(); } while (0)
 #else
 #define HA_TRACE_BEGIN(k) do { } while (0)
 #define HA_TRACE_POINT(k, i) do { } while (0)
+#define HA_TRACE_POINT_IF(k, i, cond) do { } while (0)
 #define HA_TRACE_END(k) do { } while (0)
 #endif
 

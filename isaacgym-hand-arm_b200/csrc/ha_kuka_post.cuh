@@ -512,7 +512,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     cp_async_wait<(NS == 2 && !HA_LATE_PREFETCH) ? 1 : 0>();
     if (kuka_post_bulk_tile(SOA, n, env0)) mbar_wait(&sm.mbar[NS == 2 ? (it & 1) : 0], NS == 2 ? (it >> 1) & 1 : it & 1);
     __syncthreads();                                    // B1: this tile's inputs are in shared memory
-    HA_TRACE_POINT(1, 2 + 4 * it);
+    HA_TRACE_POINT(1, it == 0 ? 2 : (it == 1 ? 10 : 13));
     if constexpr (NS == 2 && HA_LATE_PREFETCH) {
       // The next tile's reads start now, so they share the memory system with this tile's stores instead of with this tile's own
       // reads: issued up front, both stages of every CTA land together (the whole input, ~3.5 us) and only then do the stores start.
@@ -598,8 +598,9 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
 #pragma unroll
       for (int c = 0; c < 3; ++c) W(L.scales + c, S.scales[lane * 3 + c]);
     }
+    HA_TRACE_POINT_IF(1, 3 + warp, it == 0 && lane == 0);   // role `warp` of tile 0 done
     __syncthreads();                                    // B2: distances, kp_max and |vel| sums are visible to warp 3
-    HA_TRACE_POINT(1, 3 + 4 * it);
+    HA_TRACE_POINT(1, it == 0 ? 7 : (it == 1 ? 11 : 13));
 
     // Observation tile store, split in two: every 128-bit word that holds none of the columns the state warp still has to write
     // (closest_kp .. reward, the last 9 of a row) is complete now and leaves through the three other warps while the state warp
@@ -750,9 +751,9 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     }
     const bool bulk_store = HA_BULK_STORE && (nvalid == kTile);   // 14976 contiguous bytes, 16-byte aligned on both sides
     if (bulk_store) fence_proxy_async_smem();           // the tile's generic-proxy writes, before the async proxy reads them
-    HA_TRACE_POINT(1, 4 + 4 * it);                     // this warp's work between B2 and B3 is done (early stores / reward chain)
+    HA_TRACE_POINT_IF(1, 8, it == 0 && warp == 3 && lane == 0);   // reward chain of tile 0 done
     __syncthreads();                                    // B3: the observation tile is complete
-    HA_TRACE_POINT(1, 5 + 4 * it);
+    HA_TRACE_POINT(1, it == 0 ? 9 : (it == 1 ? 12 : 13));
     if (bulk_store) {
       if (tid == 0) {                                   // the whole [32, OBS] tile leaves as one bulk copy
         bulk_s2g(b.obs_buf + (size_t)env0 * OBS, sm.obs, kTile * OBS * 4);
@@ -785,10 +786,7 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   cp_async_wait<0>();
   if (HA_BULK_STORE && tid == 0) bulk_wait_read0();     // shared memory must outlive the last bulk store's reads
   if (warp == 3 && mode == kPostFull) kuka_post_store_partials(b, acc, lane);   // every CTA of the grid fills its slot
-  HA_TRACE_POINT(1, 12);
-#ifdef HA_TRACE
-  if (tid == 0 && blockIdx.x < kTraceMaxCtas) g_ha_trace[1][blockIdx.x].c[13] = warp;      // role of the recording warp
-#endif
+  HA_TRACE_POINT(1, 13);
   HA_TRACE_END(1);
 }
 

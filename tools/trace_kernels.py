@@ -73,8 +73,8 @@ def pct(x):
 
 
 names = {0: ["start", "loads issued+spec draws", "masks in", "reset prefetch issued", "DOF rerand done", "barrier", "element pass stored", "apply: stores issued", "apply: atomic result in", "end"],
-         1: ["start", "prologue+issue", "t0 B1 inputs", "t0 B2 roles", "t0 pre-B3", "t0 B3", "t1 B1 inputs", "t1 B2 roles", "t1 pre-B3", "t1 B3",
-             "t2 B1", "t2 B2", "end"]}
+         1: ["start", "prologue+issue", "t0 B1 inputs", "t0 role0 tips done", "t0 role1 keypoints done", "t0 role2 dofs done", "t0 role3 copies done",
+             "t0 B2", "t0 reward chain done", "t0 B3", "t1 B1 inputs", "t1 B2", "t1 B3", "end"]}
 spans = {}
 for k, label in ((0, "kuka_pre_kernel"), (1, "kuka_post_kernel")):
     r = buf[k]
@@ -92,14 +92,14 @@ for k, label in ((0, "kuka_pre_kernel"), (1, "kuka_post_kernel")):
         kind = r["c"][:, 13]
         cats += [("no reset", kind == 0), ("goal reset only", kind == 1), ("full reset", kind == 2)]
     else:
-        ntile = np.where(r["c"][:, 6] > 0, 2, 1)
+        ntile = np.where(r["c"][:, 10] > 0, 2, 1)
         cats += [("1 tile", ntile == 1), ("2+ tiles", ntile == 2)]
     for cname, m in cats:
         if m.sum() == 0:
             continue
         print(f"   -- {cname}: {int(m.sum())} CTAs; time since CTA start [us at {a.ghz} GHz]")
         for i, nm in enumerate(names[k]):
-            idx = i if not (k == 1 and nm == "end") else 12
+            idx = i
             v = r["c"][m][:, idx]
             ok = v > 0
             if i == 0 or ok.sum() == 0:
