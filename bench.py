@@ -48,8 +48,10 @@ def parse_args():
     ap.add_argument("--snapshots", type=int, default=4, help="rotating simulator snapshots per env block")
     ap.add_argument("--cpu-steps", type=int, default=0, help="steps of the CPU baseline sample (0 = auto, about 10-20 s)")
     ap.add_argument("--stats-interval", type=int, default=1, help="N > 1: graph replays between two all-reduces of the episode statistics")
-    ap.add_argument("--peer-stats", action="store_true", help="N > 1: exchange the episode statistics with ha_stats_exchange (NVLink peer "
-                    "stores, in the step graph) instead of an asynchronous nccl all_reduce; couples the ranks, see DESIGN.md 5")
+    ap.add_argument("--stats", default="auto", choices=["auto", "peer", "nccl"],
+                    help="N > 1: how the episode statistics cross the ranks.  peer: wait-free exchange over NVLink peer memory INSIDE the "
+                         "post-physics kernel (HaKukaBuffers.xchg, no launch; checked against nccl at start-up); nccl: asynchronous "
+                         "all_reduce once per graph replay; auto (default): peer if the symmetric-memory rendezvous and the check succeed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--layout", default="both", choices=["both", "isaacgym", "soa"],
@@ -467,7 +469,7 @@ def measure(args, layout, device, rank, world, local, headline=True):
     if world > 1:
         from handarm_b200.stats import PeerStatsExchange, _MAX_SLOTS
         xchg_note = "nccl all_reduce, async, once per graph replay"
-        if args.peer_stats:
+        if args.stats in ("auto", "peer"):
             try:
                 xchg = PeerStatsExchange.connect(device=device)
                 probe = torch.arange(16, device=device, dtype=torch.float32) * (rank + 1) + 0.25
@@ -482,13 +484,16 @@ def measure(args, layout, device, rank, world, local, headline=True):
                 torch.cuda.synchronize()
                 if not torch.allclose(got, want, rtol=1e-6, atol=0) or xchg.status() != 0:
                     raise RuntimeError(f"peer exchange disagrees with nccl: {got.tolist()} vs {want.tolist()}")
-                xchg_note = "ha_stats_exchange: peer stores over NVLink (torch symmetric memory), checked against nccl all_reduce"
+                xchg_note = (f"in-kernel exchange (HaKukaBuffers.xchg): peer stores over NVLink from one warp of the post-physics kernel, once "
+                             f"per {B * S} steps, no launch; protocol checked against nccl all_reduce at start-up")
             except Exception as e:       # noqa: BLE001 -- any rendezvous / IPC failure: fall back, and say so
                 xchg, xchg_note = None, f"nccl all_reduce (peer exchange unavailable: {type(e).__name__}: {e})"[:240]
             ok = torch.tensor([1 if xchg is not None else 0], device=device)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
             if int(ok) == 0 and xchg is not None:
                 xchg, xchg_note = None, "nccl all_reduce (peer exchange failed on another rank)"
+            if xchg is not None:
+                xchg.attach(tasks[0], interval=S)      # before the graphs are captured: the exchange rides inside tasks[0]'s post kernel, once per B*S steps (rl_games' epoch)
 
     # CUDA graphs of whole steps (2 kernels each) walking the B env blocks round-robin; every simulate() moves a block to its next
     # snapshot.  The main graph holds B*S steps, the remainder graph steps % (B*S): K steps are always whole replays.  The
@@ -501,8 +506,6 @@ def measure(args, layout, device, rank, world, local, headline=True):
         with torch.cuda.graph(g, stream=stream):
             for i in range(n_steps):
                 one_step(tasks[i % B], actions[i % B])
-            if with_xchg and xchg is not None:
-                xchg.exchange(tasks[0].stats_folded)
         return g
 
     graph = capture(per_graph, True)

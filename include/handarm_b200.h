@@ -250,6 +250,13 @@ typedef struct HaKukaBuffers {
   uint32_t* tickets;            /* [8], zero-initialised once by the caller */
   /* ---- dynamic scalars ---- */
   HaKukaDynamic* dynamic;       /* device */
+  /* ---- optional: cross-rank statistics exchange inside ha_kuka_post_step (single arm), no extra launch ----
+   * xchg: NULL, or a HaStatsExchange (see the end of this header) that lives in DEVICE memory.  The last CTA of the post grid (it
+   * owns the fewest tiles) then runs one exchange per launch in one of its warps: it publishes stats[] as the preceding
+   * ha_kuka_pre_step folded it (the statistics of the previous post step) to every peer over NVLink and leaves the newest
+   * whole-box reduction in xchg_reduced [HA_STATS_LEN] (device).  Same wait-free protocol as ha_stats_exchange. */
+  const void* xchg;
+  float* xchg_reduced;
 } HaKukaBuffers;
 
 /* per-CTA statistic slots of the single-arm post kernel (its persistent grid never exceeds this) */
@@ -815,22 +822,30 @@ int ha_adr_queue_step_static(int32_t n_envs, int32_t n_queues, int32_t capacity,
  * Cross-rank episode statistics over NVLink peer memory.  The env shards of a box never exchange data; the only
  * cross-rank quantities are the <= 16 partial statistics of a step (sums, counts, [max, -min]).  A library all-reduce for 64
  * bytes puts a collective kernel next to the persistent step kernels every few steps (measured: 8 GPUs at 92 % of linear with it,
- * 99.6 % without).  ha_stats_exchange is one single-CTA launch instead, wait-free on both sides: every rank stores its vector
- * into slot (exchange number % HA_XCHG_RING) of every peer's exchange buffer (peer pointers from CUDA IPC / torch symmetric
- * memory; slot tag = -number while under construction, = number when complete, then head[rank] = number), and reduces the newest
- * exchange that every rank has published (min over head[]), reading its W vectors between two looks at their tags.  SUM in rank
- * order (the same bits on every rank), MAX for the slots in max_mask.  A late rank delays the exchange number the others reduce,
- * never the others; a rank more than HA_XCHG_RING - 2 exchanges behind makes the others skip (status = 2) until it catches up.
+ * 99.6 % without).  The exchange here is wait-free on both sides and needs no fence: every rank stores its vector into slot
+ * (exchange number % HA_XCHG_RING) of every peer's exchange buffer (peer pointers from CUDA IPC / torch symmetric memory) as 16
+ * aligned 8-byte words (exchange number << 32 | float bits) -- one store is atomic, so a value never travels without its tag --
+ * then head[rank] = number; it reduces the newest exchange every rank claims to have published (min over head[]) if all of its
+ * W x 16 words carry that number, otherwise it leaves `reduced` alone and looks again at the next call.  SUM in rank order (the
+ * same bits on every rank), MAX for the slots in max_mask.  A late rank delays the exchange number the others reduce, never the
+ * others; while a rank is more than HA_XCHG_RING - 2 exchanges behind the others skip (status |= 2); a rank that finds itself
+ * lapped rejoins at the fastest rank's exchange number (status |= 1).  One warp runs an exchange: as a launch of its own
+ * (ha_stats_exchange) or inside the single-arm post-physics kernel (HaKukaBuffers.xchg, no launch).
  * ===================================================================================================== */
 #define HA_XCHG_RING 16
 #define HA_XCHG_MAX_RANKS 16
 typedef struct HaStatsExchange {
   float** peer_bufs;         /* device array [world]: exchange buffer of every rank (own one included), each
-                                ha_stats_exchange_bytes(world) bytes, zero-initialised before the first exchange of any rank */
+                                ha_stats_exchange_bytes(world) bytes, 8-byte aligned, zero-initialised before the first exchange
+                                of any rank */
   int32_t rank, world;
   uint32_t max_mask;         /* bit i: statistic i is MAX-reduced, otherwise SUM */
-  int64_t* seq;              /* [2]: exchanges done by this rank, number of the last exchange reduced; zero-initialised */
-  int32_t* status;           /* [1]: 2 = a peer fell a whole ring behind at some point; zero-initialised */
+  int32_t interval;          /* in-kernel path (HaKukaBuffers.xchg) only: exchange on every interval-th post step (<= 1: every one);
+                                the same value on every rank */
+  int64_t* seq;              /* [4]: exchanges done by this rank, number of the last exchange reduced, post steps seen by the
+                                in-kernel path, unused; zero-initialised */
+  int32_t* status;           /* [1]: bit 1 (2) = a peer fell a whole ring behind at some point, bit 0 (1) = this rank was lapped
+                                and rejoined; zero-initialised */
 } HaStatsExchange;
 size_t ha_sizeof_stats_exchange(void);
 size_t ha_stats_exchange_bytes(int32_t world);

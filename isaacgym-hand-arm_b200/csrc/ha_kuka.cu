@@ -41,6 +41,8 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
     HA_REQUIRE(p->tip_body[t] >= 0 && p->tip_body[t] < p->n_bodies, "tip_body[%d] out of range", t);
   HA_REQUIRE(p->success_steps >= 1, "success_steps must be >= 1");
   HA_REQUIRE(p->post_grid >= 0, "post_grid must be >= 0 (got %d)", p->post_grid);
+  HA_REQUIRE(b->xchg == nullptr || (b->xchg_reduced != nullptr && p->n_arms == 1),
+             "HaKukaBuffers.xchg needs xchg_reduced and the single-arm task (the in-kernel exchange lives in its post kernel)");
   const void* need[] = {b->root_state, b->rigid_body_state, b->dof_state, b->object_actor, b->goal_actor, b->hand_actor,
                         b->object_init_state, b->object_keypoint_offsets, b->object_scales, b->goal_states,
                         b->obs_buf, b->rew_buf, b->reset_buf, b->reset_goal_buf, b->progress_buf, b->timeout_buf, b->successes,

@@ -32,6 +32,7 @@
 #pragma once
 #include "ha_device.cuh"
 #include "../../include/handarm_b200.h"
+#include "ha_stats_xchg.cuh"
 
 // tuning switches (A/B builds): which transfers of K_post go through the bulk-copy engine (cp.async.bulk, SASS UBLKCP).
 // Measured on B200, 32768 envs, component planes (K_post us): none 13.4 | store 13.9 | images + store 13.8 | rows + images + store 15.0.
@@ -784,6 +785,16 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     }
   }
   cp_async_wait<0>();
+  // cross-rank statistics without a launch (HaKukaBuffers.xchg): the last CTA of the grid owns the fewest tiles and is done first;
+  // after its tiles one of its warps publishes the statistics vector the preceding pre step folded (nobody writes stats[] during
+  // this launch) and reduces the newest complete exchange.  Remote stores and local loads only, nothing waits for a peer.
+  if (b.xchg != nullptr && mode == kPostFull && blockIdx.x == gridDim.x - 1 && (tid >> 5) == 0) {
+    const HaStatsExchange& x = *reinterpret_cast<const HaStatsExchange*>(b.xchg);
+    const long long calls = x.seq[2] + 1;
+    __syncwarp();
+    if (lane == 0) x.seq[2] = calls;
+    if (x.interval <= 1 || calls % x.interval == 0) stats_exchange_warp(x, b.stats, b.xchg_reduced, lane);
+  }
   if (HA_BULK_STORE && tid == 0) bulk_wait_read0();     // shared memory must outlive the last bulk store's reads
   if (warp == 3 && mode == kPostFull) kuka_post_store_partials(b, acc, lane);   // every CTA of the grid fills its slot
   HA_TRACE_POINT(1, 13);

@@ -102,7 +102,7 @@ class PeerStatsExchange:
             assert t.dtype == torch.float32 and t.numel() >= need and t.is_contiguous()
         self._peer_buffers = list(peer_buffers)
         self._ptrs = torch.tensor([t.data_ptr() for t in peer_buffers], dtype=torch.int64, device=self.device)
-        self._seq = torch.zeros(2, dtype=torch.int64, device=self.device)
+        self._seq = torch.zeros(4, dtype=torch.int64, device=self.device)
         self._status = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._reduced = torch.zeros(C["HA_STATS_LEN"], dtype=torch.float32, device=self.device)
         self._first = True
@@ -110,6 +110,7 @@ class PeerStatsExchange:
         x.peer_bufs = self._ptrs.data_ptr()
         x.rank, x.world = rank, world
         x.max_mask = sum(1 << i for i in _MAX_SLOTS)
+        x.interval = 1
         x.seq = self._seq.data_ptr()
         x.status = self._status.data_ptr()
         self._x = x
@@ -150,6 +151,24 @@ class PeerStatsExchange:
     def reduced(self) -> torch.Tensor:
         """Derived whole-box vector of the last completed exchange."""
         return derive(self._reduced)
+
+    def attach(self, task, interval: int = 1) -> None:
+        """Run the exchange INSIDE the task's post-physics kernel from now on (``HaKukaBuffers.xchg``): no launch of its own.  Every
+        ``interval``-th ``post_physics_step`` publishes the statistics vector the preceding ``pre_physics_step`` folded and updates
+        ``reduced()`` (``interval`` must be the same on every rank)."""
+        ct = self._ctypes
+        if getattr(self, "_x_dev", None) is None or self._x.interval != int(interval):
+            self._x.interval = int(interval)
+            raw = ct.string_at(ct.addressof(self._x), ct.sizeof(self._x))
+            self._x_dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
+        task._buffers.xchg = self._x_dev.data_ptr()
+        task._buffers.xchg_reduced = self._reduced.data_ptr()
+        task._stats_exchange = self          # keeps the device struct alive
+
+    @staticmethod
+    def detach(task) -> None:
+        task._buffers.xchg = None
+        task._buffers.xchg_reduced = None
 
     def status(self) -> int:
         return int(self._status.item())
