@@ -92,3 +92,23 @@ def test_rna_weights_are_resampled_at_the_configured_frequency():
         task.step(torch.zeros(256, 16, device="cuda:0"))
     assert task.last_step == 7
     assert calls == [3, 6]
+
+
+def test_rna_tc_is_deterministic():
+    """The persistent tcgen05 chain twice on the same input at cfg 5's size: identical bins and perturbations (a race in the mbarrier
+    ring or between the TMEM accumulator buffers would show as run-to-run differences)."""
+    from handarm_b200.rna import RandomNetworkAdversary
+    n = 16384
+    g = torch.Generator().manual_seed(11)
+    w = ro.make_weights(n, seed=3)
+    net = RandomNetworkAdversary(n, 23, 16, 32, "cuda:0", impl="tc")
+    _load(net, w)
+    dof_state = torch.randn(n, 16, 2, generator=g).cuda()
+    pose = torch.randn(n, 7, generator=g).cuda()
+    disc = torch.stack([torch.linspace(-0.5, 1.7, steps=32) for _ in range(16)]).cuda()
+    outs = []
+    for _ in range(3):
+        outs.append((net.perturbation(dof_state, pose, disc).clone(), net.bins.clone()))
+    torch.cuda.synchronize()
+    for o in outs[1:]:
+        assert torch.equal(o[0], outs[0][0]) and torch.equal(o[1], outs[0][1])
