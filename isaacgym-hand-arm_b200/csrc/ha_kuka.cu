@@ -41,6 +41,8 @@ int validate_kuka(const HaKukaParams* p, const HaKukaBuffers* b) {
     HA_REQUIRE(p->tip_body[t] >= 0 && p->tip_body[t] < p->n_bodies, "tip_body[%d] out of range", t);
   HA_REQUIRE(p->success_steps >= 1, "success_steps must be >= 1");
   HA_REQUIRE(p->post_grid >= 0, "post_grid must be >= 0 (got %d)", p->post_grid);
+  HA_REQUIRE(p->subtask == HA_KUKA_REORIENTATION || p->subtask == HA_KUKA_REGRASPING || p->subtask == HA_KUKA_THROW, "unknown subtask %d",
+             p->subtask);
   HA_REQUIRE(b->xchg == nullptr || (b->xchg_reduced != nullptr && p->n_arms == 1),
              "HaKukaBuffers.xchg needs xchg_reduced and the single-arm task (the in-kernel exchange lives in its post kernel)");
   const void* need[] = {b->root_state, b->rigid_body_state, b->dof_state, b->object_actor, b->goal_actor, b->hand_actor,

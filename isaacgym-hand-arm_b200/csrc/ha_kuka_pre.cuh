@@ -92,23 +92,44 @@ __device__ __forceinline__ int kuka_object_row(const HaKukaParams& p, const HaKu
   return p.root_regular ? env * p.actors_per_env + p.object_slot : b.object_actor[env];
 }
 
-// goal pose (reset_target_pose :1191-1196 -> _reset_target, allegro_kuka_reorientation.py:104-128).  An env that is in both sets
-// is drawn twice by the reference and the reset_idx draw wins.  The caller clears reset_goal_buf.
+// goal of one env: reset_target_pose (:1191-1196) with the subtask's _reset_target.  An env that is in both sets is drawn twice by
+// the reference and the reset_idx draw wins: `rst` selects the RESET_GOAL slots.
+//   reorientation  allegro_kuka_reorientation.py:104-128  position in the target volume + random rotation, goal row velocities = 0
+//   regrasping     allegro_kuka_regrasping.py:76-100      position only (the goal ball keeps its rotation)
+//   throw          allegro_kuka_throw.py:90-117           bucket left / right of the table (4 draws), goal = bucket + 5 cm
+// (regrasping / throw also put the object back on the table: the caller runs kuka_object_reset and clears lifted_object)
 __device__ __noinline__ void kuka_goal_reset(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env, bool rst) {
   const float4 u_gp = kuka_draw4(R, env, rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS);
-  const float4 u_gr = kuka_draw4(R, env, rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT);
-  float g[7];
-  g[0] = p.target_min[0] + u_gp.x * p.target_size[0];
-  g[1] = p.target_min[1] + u_gp.y * p.target_size[1];
-  g[2] = p.target_min[2] + u_gp.z * p.target_size[2];
-  const f4 q = random_quat(u_gr.x, u_gr.y, u_gr.z);
-  g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
   float* gs = b.goal_states + (size_t)env * 13;
   const RootRow rr = root_row(p, b, kuka_goal_row(p, b, env), env, p.goal_slot);
+  if (p.subtask == HA_KUKA_THROW) {
+    // torch_rand_float(lo, hi) = (hi - lo) * u + lo
+    const float left_right = 2.0f * u_gp.x + -1.0f;
+    float x = left_right > 0.0f ? 0.5f : -0.5f;
+    const float sgn = left_right > 0.0f ? 1.0f : (left_right < 0.0f ? -1.0f : 0.0f);
+    x = x + sgn * (0.4f * u_gp.y + 0.0f);
+    const float y = 1.7f * u_gp.z + -1.0f;
+    const float z = 1.0f * u_gp.w + 0.0f;
+    rr.at(0) = x; rr.at(1) = y; rr.at(2) = z;
+    gs[0] = x; gs[1] = y; gs[2] = z + 0.05f;
+  } else {
+    float g[7];
+    g[0] = p.target_min[0] + u_gp.x * p.target_size[0];
+    g[1] = p.target_min[1] + u_gp.y * p.target_size[1];
+    g[2] = p.target_min[2] + u_gp.z * p.target_size[2];
+    if (p.subtask == HA_KUKA_REORIENTATION) {
+      const float4 u_gr = kuka_draw4(R, env, rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT);
+      const f4 q = random_quat(u_gr.x, u_gr.y, u_gr.z);
+      g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
 #pragma unroll
-  for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr.at(c) = g[c]; }
+      for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr.at(c) = g[c]; }
 #pragma unroll
-  for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
+      for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { gs[c] = g[c]; rr.at(c) = g[c]; }
+    }
+  }
   b.reset_goal_buf[env] = 0;
   b.near_goal_steps[env] = 0;
   b.closest_keypoint_max_dist[env] = -1.0f;
@@ -230,6 +251,10 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   HA_TRACE_POINT(0, 2);                                 // masks in
   // warp 3 of a tile with a reset: the list-slot atomic and the bookkeeping loads go in flight now and are consumed at the very end
   const unsigned m_goal_only = m_any & ~m_rst;
+  // regrasping / throw: a new goal also puts the object back on the table (_reset_target of those subtasks), so a goal-only reset
+  // touches the object row, the fingertip distances and lifted_object too and contributes two actor rows instead of one
+  const bool goal_moves_object = p.subtask != HA_KUKA_REORIENTATION;
+  const int rows_goal_only = goal_moves_object ? 2 : 1;
   unsigned long long list_old = 0;
   float succ = 0.f, tobj = 0.f;
   int hand_row = 0;
@@ -238,7 +263,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     // The four counters share one L2 line: one returning 64-bit add for the two list bases and one fire-and-forget add for the
     // two plain counts (reset_counts is 8-byte aligned; < 2^31 each)
     if (lane == 0) {
-      const int n_root = 2 * __popc(m_rst) + __popc(m_goal_only), n_hand = __popc(m_rst);
+      const int n_root = 2 * __popc(m_rst) + rows_goal_only * __popc(m_goal_only), n_hand = __popc(m_rst);
       unsigned long long* rc = reinterpret_cast<unsigned long long*>(b.reset_counts);
       list_old = atomicAdd(rc + 0, (unsigned long long)(unsigned)n_root | ((unsigned long long)(unsigned)n_hand << 32));
       atomicAdd(rc + 1, (unsigned long long)(unsigned)n_hand | ((unsigned long long)(unsigned)__popc(m_any) << 32));
@@ -365,23 +390,25 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     if (warp == 0) {
       if (rst || grst) kuka_goal_reset(p, b, R, env, rst);
     } else if (warp == 2) {
+      if (rst || (grst && goal_moves_object)) kuka_object_reset(p, b, R, env);
       if (rst) {
-        kuka_object_reset(p, b, R, env);
 #pragma unroll
         for (int k = 0; k < HA_KUKA_N_EPISODE_TERMS; k += 2) b.rewards_episode[(size_t)k * n + env] = 0.0f;   // (:1341-1342)
       }
     } else if (warp == 3) {
-      if (rst) {
-        // episode bookkeeping (:1323-1347)
+      if (rst || (grst && goal_moves_object)) {          // reset_object_pose's tail (:1221-1224) + lifted_object of the subtasks
         *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
         b.furthest_hand_dist[env] = -1.0f;
+        b.lifted_object[env] = 0;
+      }
+      if (rst) {
+        // episode bookkeeping (:1323-1347)
         b.progress_buf[env] = 0;
         b.reset_buf[env] = 0;
         b.prev_episode_successes[env] = succ;
         b.successes[env] = 0.0f;
         b.prev_episode_true_objective[env] = tobj;
         b.true_objective[env] = 0.0f;
-        b.lifted_object[env] = 0;
 #pragma unroll
         for (int k = 1; k < HA_KUKA_N_EPISODE_TERMS; k += 2) b.rewards_episode[(size_t)k * n + env] = 0.0f;
       }
@@ -391,11 +418,9 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       const int root_base = (int)(unsigned)(old & 0xffffffffULL), hand_base = (int)(unsigned)(old >> 32);
       if (rst || grst) {
         const unsigned below = (1u << lane) - 1u;
-        int k = root_base + 2 * __popc(m_rst & below) + __popc(m_goal_only & below);
-        if (rst) {
-          b.root_reset_indices[k++] = kuka_object_row(p, b, env);
-          b.hand_reset_indices[hand_base + __popc(m_rst & below)] = hand_row;
-        }
+        int k = root_base + 2 * __popc(m_rst & below) + rows_goal_only * __popc(m_goal_only & below);
+        if (rst || goal_moves_object) b.root_reset_indices[k++] = kuka_object_row(p, b, env);
+        if (rst) b.hand_reset_indices[hand_base + __popc(m_rst & below)] = hand_row;
         b.root_reset_indices[k] = kuka_goal_row(p, b, env);
       }
       HA_TRACE_POINT(0, 8);

@@ -1,5 +1,6 @@
 """Task registry (subset of ``isaacgymenvs/tasks/__init__.py:66-123`` that lies on the hot path)."""
-from .allegro_kuka import AllegroKukaBase, AllegroKukaReorientation, AllegroKukaTwoArmsRegrasping
+from .allegro_kuka import (AllegroKukaBase, AllegroKukaRegrasping, AllegroKukaReorientation, AllegroKukaThrow,
+                           AllegroKukaTwoArmsRegrasping)
 from .dextreme import AllegroHandDextremeADR
 from .hand import AllegroHand, ShadowHand
 
@@ -7,7 +8,7 @@ from .hand import AllegroHand, ShadowHand
 def resolve_allegro_kuka(cfg, *args, **kwargs):
     """``tasks/__init__.py:66-76``: dispatch on ``env.subtask``."""
     subtask = cfg["env"]["subtask"]
-    table = {"reorientation": AllegroKukaReorientation}
+    table = {"reorientation": AllegroKukaReorientation, "regrasping": AllegroKukaRegrasping, "throw": AllegroKukaThrow}
     if subtask not in table:
         raise ValueError(f"Unknown subtask={subtask} in {list(table)}")
     return table[subtask](cfg, *args, **kwargs)

@@ -558,6 +558,26 @@ class AllegroKukaReorientation(AllegroKukaBase):
             self._write_dynamic()
 
 
+class AllegroKukaRegrasping(AllegroKukaReorientation):
+    """allegro_kuka_regrasping.py:40-123: grasp, lift and hold the object at a target position.  One keypoint (the object centre,
+    99-wide observation); a new goal (`_reset_target` :76-100) draws a position only and puts the object back on the table
+    (reset_object_pose, lifted_object = False); no far-fingertip reset rule; same tolerance curriculum and true objective."""
+    subtask_id = C["HA_KUKA_REGRASPING"]
+
+    def _object_keypoint_offsets(self):
+        return [[0, 0, 0]]
+
+
+class AllegroKukaThrow(AllegroKukaRegrasping):
+    """allegro_kuka_throw.py:40-124: throw the object into a bucket.  The bucket takes the goal actor's slot; `_reset_target`
+    (:90-117) places it left / right of the table (4 draws), the goal is 5 cm above it, the object goes back to the table.  The
+    class does not override `_extra_curriculum` (allegro_kuka_base.py:468-469: no curriculum)."""
+    subtask_id = C["HA_KUKA_THROW"]
+
+    def _extra_curriculum(self):
+        pass
+
+
 class AllegroKukaTwoArmsRegrasping(AllegroKukaReorientation):
     """allegro_kuka_two_arms.py (``AllegroKukaTwoArmsBase``) + allegro_kuka_two_arms_regrasping.py:40-135: two Kuka-Allegro arms pass
     the object between them; 46 DOFs all position-controlled, one keypoint (the object centre), 169-wide observation."""

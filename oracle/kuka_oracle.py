@@ -93,6 +93,7 @@ class KukaConsts:
     target_volume_origin: Tuple[float, ...] = (0, 0.05, 0.8)
     target_volume_extent: Tuple[Tuple[float, float], ...] = ((-0.4, 0.4), (-0.05, 0.3), (-0.12, 0.25))
     extra_far_reset: bool = True          # reorientation's _extra_reset_rules
+    subtask: str = "reorientation"        # "reorientation" | "regrasping" | "throw" (env.subtask; the task classes of the same names)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -137,17 +138,57 @@ def true_objective_coeffs(tol: float, initial: float, target: float) -> Tuple[fl
 # ---------------------------------------------------------------------------------------------
 # pre-physics step
 # ---------------------------------------------------------------------------------------------
-def _reset_target(st: Dict[str, Tensor], c: KukaConsts, ids: Tensor, pos_u: Tensor, rot_u: Tensor) -> None:
-    """allegro_kuka_reorientation.py:104-128 + allegro_kuka_base.py:1191-1196 for env ids ``ids``."""
-    org = torch.tensor(c.target_volume_origin, dtype=torch.float32)
-    ext = torch.tensor(c.target_volume_extent, dtype=torch.float32)
-    lo = org + ext[:, 0]
-    size = (org + ext[:, 1]) - lo
-    pose = torch.cat((lo + pos_u * size, random_quat(rot_u)), dim=-1)
-    st["goal_states"][ids, 0:7] = pose
+def _reset_object_pose(st: Dict[str, Tensor], c: KukaConsts, ids: Tensor, rnd: Tensor) -> None:
+    """allegro_kuka_base.py:1198-1224 for env ids ``ids`` (draws: RND_OBJ_POS, RND_OBJ_ROT)."""
+    rows = st["object_indices"][ids]
+    noise = 2.0 * rnd[ids, RND_OBJ_POS:RND_OBJ_POS + 3] + (-1.0)
+    new_row = st["object_init_state"][ids].clone()
+    for k in range(3):
+        new_row[:, k] = st["object_init_state"][ids, k] + c.reset_position_noise[k] * noise[:, k]
+    new_row[:, 3:7] = random_quat(rnd[ids, RND_OBJ_ROT:RND_OBJ_ROT + 3])
+    new_row[:, 7:13] = 0.0
+    st["root_state"][rows] = new_row
+    st["closest_fingertip_dist"][ids] = -1.0
+    st["furthest_hand_dist"][ids] = -1.0
+
+
+def _reset_target(st: Dict[str, Tensor], c: KukaConsts, ids: Tensor, rnd: Tensor, slot: int) -> None:
+    """reset_target_pose (allegro_kuka_base.py:1191-1196) with the subtask's ``_reset_target`` for env ids ``ids``; ``slot`` is the
+    first of the (up to six) raw draws of the goal: RND_GOAL_POS for a goal-only reset, RND_RESET_GOAL_POS inside reset_idx.
+      reorientation  allegro_kuka_reorientation.py:104-128: position in the target volume + random rotation
+      regrasping     allegro_kuka_regrasping.py:76-100: position only; the object goes back to the table, lifted_object = False
+      throw          allegro_kuka_throw.py:90-117: bucket left / right of the table; goal = bucket + 5 cm; object back to the table"""
     rows = st["goal_object_indices"][ids]
-    st["root_state"][rows, 0:7] = pose
-    st["root_state"][rows, 7:13] = 0.0
+    if c.subtask == "throw":
+        u = rnd[ids, slot:slot + 4]
+        left_right = 2.0 * u[:, 0:1] + (-1.0)
+        x_pos = torch.where(left_right > 0, 0.5 * torch.ones_like(left_right), -0.5 * torch.ones_like(left_right))
+        x_pos = x_pos + torch.sign(left_right) * (0.4 * u[:, 1:2] + 0.0)
+        y_pos = (0.7 - (-1.0)) * u[:, 2:3] + (-1.0)
+        z_pos = (1.0 - 0.0) * u[:, 3:4] + 0.0
+        st["root_state"][rows, 0:1] = x_pos
+        st["root_state"][rows, 1:2] = y_pos
+        st["root_state"][rows, 2:3] = z_pos
+        st["goal_states"][ids, 0:1] = x_pos
+        st["goal_states"][ids, 1:2] = y_pos
+        st["goal_states"][ids, 2:3] = z_pos + 0.05
+    else:
+        org = torch.tensor(c.target_volume_origin, dtype=torch.float32)
+        ext = torch.tensor(c.target_volume_extent, dtype=torch.float32)
+        lo = org + ext[:, 0]
+        size = (org + ext[:, 1]) - lo
+        pos = lo + rnd[ids, slot:slot + 3] * size
+        if c.subtask == "reorientation":
+            pose = torch.cat((pos, random_quat(rnd[ids, slot + 3:slot + 6])), dim=-1)
+            st["goal_states"][ids, 0:7] = pose
+            st["root_state"][rows, 0:7] = pose
+            st["root_state"][rows, 7:13] = 0.0
+        else:
+            st["goal_states"][ids, 0:3] = pos
+            st["root_state"][rows, 0:3] = pos
+    if c.subtask != "reorientation":
+        _reset_object_pose(st, c, ids, rnd)
+        st["lifted_object"][ids] = False
     st["reset_goal_buf"][ids] = 0
     st["near_goal_steps"][ids] = 0
     st["closest_keypoint_max_dist"][ids] = -1.0
@@ -163,26 +204,18 @@ def pre_step(st: Dict[str, Tensor], c: KukaConsts, actions: Tensor, rnd: Tensor)
     root_lists: List[Tensor] = []
 
     # goal-only resets (always executed, also for an empty id list)
-    _reset_target(st, c, goal_ids, rnd[goal_ids, RND_GOAL_POS:RND_GOAL_POS + 3], rnd[goal_ids, RND_GOAL_ROT:RND_GOAL_ROT + 3])
+    _reset_target(st, c, goal_ids, rnd, RND_GOAL_POS)
     root_lists.append(st["goal_object_indices"][goal_ids])
+    if c.subtask != "reorientation":
+        root_lists.append(st["object_indices"][goal_ids])
 
     hand_rows = torch.zeros(0, dtype=torch.int32)
     if len(reset_ids) > 0:
         ids = reset_ids
-        _reset_target(st, c, ids, rnd[ids, RND_RESET_GOAL_POS:RND_RESET_GOAL_POS + 3], rnd[ids, RND_RESET_GOAL_ROT:RND_RESET_GOAL_ROT + 3])
+        _reset_target(st, c, ids, rnd, RND_RESET_GOAL_POS)
         root_lists.append(st["goal_object_indices"][ids])
         st["rb_forces"][ids] = 0.0
-        # object pose (allegro_kuka_base.py:1198-1224)
-        rows = st["object_indices"][ids]
-        noise = 2.0 * rnd[ids, RND_OBJ_POS:RND_OBJ_POS + 3] + (-1.0)
-        new_row = st["object_init_state"][ids].clone()
-        for k in range(3):
-            new_row[:, k] = st["object_init_state"][ids, k] + c.reset_position_noise[k] * noise[:, k]
-        new_row[:, 3:7] = random_quat(rnd[ids, RND_OBJ_ROT:RND_OBJ_ROT + 3])
-        new_row[:, 7:13] = 0.0
-        st["root_state"][rows] = new_row
-        st["closest_fingertip_dist"][ids] = -1.0
-        st["furthest_hand_dist"][ids] = -1.0
+        _reset_object_pose(st, c, ids, rnd)      # (the object draws a regrasping / throw _reset_target made just before are overwritten)
         hand_rows = st["allegro_hand_indices"][ids].to(torch.int32)
         # force probability (:1265-1269)
         pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
@@ -367,7 +400,7 @@ def post_step(st: Dict[str, Tensor], c: KukaConsts) -> Dict[str, Tensor]:
         st["progress_buf"] = torch.where(is_success, torch.zeros_like(st["progress_buf"]), st["progress_buf"])
         resets = torch.where(st["successes"] >= c.max_consecutive_successes, ones, resets)
     resets = torch.where(st["progress_buf"] >= c.max_episode_length - 1, ones, resets)
-    if c.extra_far_reset:
+    if c.extra_far_reset and c.subtask == "reorientation":      # allegro_kuka_reorientation.py:97-102 only
         resets = torch.where(cur.max(dim=-1).values > 1.5, ones, resets)
     st["reset_buf"][:] = resets
 

@@ -31,6 +31,9 @@ def make_state(n: int, seed: int = 0, c: KukaConsts = KukaConsts(), n_keypoints:
                fresh: bool = False) -> Dict[str, torch.Tensor]:
     """``fresh=True`` gives the just-constructed state (reset_buf all ones); otherwise a random mid-episode one."""
     gen = torch.Generator().manual_seed(seed)
+    single_keypoint = getattr(c, "subtask", "reorientation") != "reorientation"      # regrasping / throw: one keypoint at the object centre
+    if single_keypoint:
+        n_keypoints = 1
     D, T, K = c.n_dofs, c.n_tips, n_keypoints
     obs_dim = 2 * D + 3 + 10 + 10 + 3 * T + 6 * K + 3 + 1 + T + 4
     U = lambda *s: torch.rand(*s, generator=gen)
@@ -54,6 +57,8 @@ def make_state(n: int, seed: int = 0, c: KukaConsts = KukaConsts(), n_keypoints:
     scales = torch.tensor([[1.0, 1.0, 1.0], [4.0, 0.75, 1.0], [1.0, 2.5, 1.0], [1.25, 0.66, 3.0], [0.5, 2.0, 1.5]])
     st["object_scales"] = scales[torch.arange(n) % len(scales)].contiguous()
     corners = torch.tensor([[1, 1, 1], [1, 1, -1], [-1, -1, 1], [-1, -1, -1]], dtype=torch.float32)[:K]
+    if single_keypoint:
+        corners = torch.zeros(1, 3)
     st["object_keypoint_offsets"] = (corners[None] * (st["object_scales"][:, None, :] * 0.05 * c.keypoint_scale / 2)).contiguous()
     st["finger_rew_coeffs"] = torch.ones(n, T)
 

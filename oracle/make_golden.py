@@ -34,6 +34,11 @@ SCENARIOS = {
     "kuka_reorient_mid": (40, 202, False, 3, {}),
     "kuka_reorient_hold30_noforce": (24, 303, False, 2, dict(success_steps=30, max_episode_length=300, force_scale=0.0)),
     "kuka_reorient_tighter_tol": (24, 404, False, 2, dict(success_tolerance=0.04)),
+    # the sibling subtasks of the single-arm task (allegro_kuka_regrasping.py, allegro_kuka_throw.py; env/regrasping.yaml, env/throw.yaml)
+    "kuka_regrasp_fresh": (32, 505, True, 2, dict(subtask="regrasping", success_steps=30, max_episode_length=300)),
+    "kuka_regrasp_mid": (40, 606, False, 3, dict(subtask="regrasping", success_steps=30, max_episode_length=300)),
+    "kuka_throw_mid": (40, 707, False, 3, dict(subtask="throw", success_steps=5, max_episode_length=300, force_scale=0.0,
+                                               success_tolerance=0.075, initial_tolerance=0.075, target_tolerance=0.075)),
 }
 
 # rigid_body_state is read-only on this path: only the input copy is stored
@@ -63,7 +68,7 @@ def generate(name: str) -> str:
     out: Dict[str, np.ndarray] = {"meta/n": np.int64(n), "meta/seed": np.int64(seed), "meta/fresh": np.int64(fresh),
                                   "meta/steps": np.int64(steps)}
     for k, v in over.items():
-        out[f"consts/{k}"] = np.float64(v)
+        out[f"consts/{k}"] = np.str_(v) if isinstance(v, str) else np.float64(v)
     for k, v in st.items():
         out[f"in/{k}"] = v.numpy().copy()
     env = rl.make_reference_kuka(st, c)
@@ -96,7 +101,8 @@ def main():
     if not rl.reference_available():
         raise SystemExit("the reference is not present here; golden vectors can only be generated in the build container")
     torch.manual_seed(0)
-    for name in SCENARIOS:
+    only = sys.argv[1:]                       # optional: names of the fixtures to (re)generate; default all
+    for name in (only or SCENARIOS):
         p = generate(name)
         print(f"{name}: {os.path.getsize(p) / 1024:.0f} KiB")
 

@@ -100,6 +100,8 @@ def load_reference() -> Dict[str, types.ModuleType]:
     _loaded["akb"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_base")
     _loaded["akr"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_reorientation")
     _loaded["aku"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_utils")
+    _loaded["akg"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_regrasping")
+    _loaded["akt"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_throw")
     _loaded["vt"] = importlib.import_module("isaacgymenvs.tasks.base.vec_task")
     _loaded["ak2"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms")
     _loaded["ak2g"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms_regrasping")
@@ -167,7 +169,10 @@ def make_reference_kuka(st: Dict[str, torch.Tensor], c, device: str = "cpu") -> 
     mods = load_reference()
     if device != "cpu":
         st = {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in st.items()}
-    env = object.__new__(mods["akr"].AllegroKukaReorientation)
+    subtask = getattr(c, "subtask", "reorientation")
+    cls = {"reorientation": lambda: mods["akr"].AllegroKukaReorientation, "regrasping": lambda: mods["akg"].AllegroKukaRegrasping,
+           "throw": lambda: mods["akt"].AllegroKukaThrow}[subtask]()
+    env = object.__new__(cls)
     N = st["reset_buf"].shape[0]
     K = st["object_keypoint_offsets"].shape[1]
     e = env.__dict__
@@ -210,6 +215,8 @@ def make_reference_kuka(st: Dict[str, torch.Tensor], c, device: str = "cpu") -> 
     env.arm_hand_dof_pos = env.arm_hand_dof_state[..., 0]
     env.arm_hand_dof_vel = env.arm_hand_dof_state[..., 1]
     env.num_bodies = env.rigid_body_states.shape[1]
+    if subtask == "throw":
+        env.bucket_object_indices = st["goal_object_indices"]          # the bucket takes the goal actor's slot
     for name in ("object_indices", "goal_object_indices", "allegro_hand_indices", "goal_states", "object_init_state",
                  "object_keypoint_offsets", "object_scales", "finger_rew_coeffs", "obs_buf", "rew_buf", "reset_buf", "reset_goal_buf",
                  "progress_buf", "randomize_buf", "successes", "prev_episode_successes", "true_objective",
@@ -250,7 +257,7 @@ def scripted_randoms(queue: List[torch.Tensor]):
         return pop(shape)
 
     saved = {}
-    patched = [k for k in ("akb", "akr", "sh", "ah", "ak2", "ak2g", "dx") if k in mods and hasattr(mods[k], "torch_rand_float")]
+    patched = [k for k in ("akb", "akr", "akg", "akt", "sh", "ah", "ak2", "ak2g", "dx") if k in mods and hasattr(mods[k], "torch_rand_float")]
     for key in patched:
         saved[key] = mods[key].torch_rand_float
         mods[key].torch_rand_float = fake_rand_float
@@ -271,11 +278,22 @@ def kuka_random_queue(st: Dict[str, torch.Tensor], c, rnd: torch.Tensor) -> List
     D = c.n_dofs
     goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
     ids = st["reset_buf"].nonzero(as_tuple=False).squeeze(-1)
-    q = [rnd[goal_ids, ko.RND_GOAL_POS:ko.RND_GOAL_POS + 3], rnd[goal_ids, ko.RND_GOAL_ROT:ko.RND_GOAL_ROT + 3]]
+    subtask = getattr(c, "subtask", "reorientation")
+
+    def target_draws(who, slot):
+        """the draws of one reset_target_pose(who) in the reference's order"""
+        obj = [rnd[who, ko.RND_OBJ_POS:ko.RND_OBJ_POS + 3], rnd[who, ko.RND_OBJ_ROT:ko.RND_OBJ_ROT + 3]]      # reset_object_pose
+        if subtask == "reorientation":
+            return [rnd[who, slot:slot + 3], rnd[who, slot + 3:slot + 6]]
+        if subtask == "regrasping":
+            return [rnd[who, slot:slot + 3]] + obj
+        return [rnd[who, slot + k:slot + k + 1] for k in range(4)] + obj                                          # throw: 4 x (len, 1)
+
+    q = target_draws(goal_ids, ko.RND_GOAL_POS)
     prob = st["random_force_prob"].clone()
     if len(ids) > 0:
-        q += [rnd[ids, ko.RND_RESET_GOAL_POS:ko.RND_RESET_GOAL_POS + 3], rnd[ids, ko.RND_RESET_GOAL_ROT:ko.RND_RESET_GOAL_ROT + 3],
-              rnd[ids, ko.RND_OBJ_POS:ko.RND_OBJ_POS + 3], rnd[ids, ko.RND_OBJ_ROT:ko.RND_OBJ_ROT + 3], rnd[ids, ko.RND_FORCE_PROB],
+        q += target_draws(ids, ko.RND_RESET_GOAL_POS)
+        q += [rnd[ids, ko.RND_OBJ_POS:ko.RND_OBJ_POS + 3], rnd[ids, ko.RND_OBJ_ROT:ko.RND_OBJ_ROT + 3], rnd[ids, ko.RND_FORCE_PROB],
               rnd[ids, ko.RND_DOF_POS:ko.RND_DOF_POS + D], rnd[ids, ko.RND_DOF_POS + D:ko.RND_DOF_POS + 2 * D]]
         pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
         prob[ids] = torch.exp((torch.log(pr[0]) - torch.log(pr[1])) * rnd[ids, ko.RND_FORCE_PROB] + torch.log(pr[1]))

@@ -25,7 +25,7 @@ def load_fixture(name: str):
     for k in z.files:
         if k.startswith("consts/"):
             key = k.split("/", 1)[1]
-            over[key] = int(z[k]) if key in INT_CONSTS else float(z[k])
+            over[key] = str(z[k]) if z[k].dtype.kind in "US" else (int(z[k]) if key in INT_CONSTS else float(z[k]))
     c = ko.KukaConsts(**over)
     st = {k.split("/", 1)[1]: torch.from_numpy(z[k].copy()) for k in z.files if k.startswith("in/")}
     steps = []

@@ -7,7 +7,9 @@ import torch
 
 import handarm_b200.config as hcfg
 from handarm_b200.sim import KUKA_LAYOUT, SyntheticSim
-from handarm_b200.tasks.allegro_kuka import AllegroKukaReorientation
+from handarm_b200.tasks.allegro_kuka import AllegroKukaRegrasping, AllegroKukaReorientation, AllegroKukaThrow
+
+SUBTASK_CLASSES = {"reorientation": AllegroKukaReorientation, "regrasping": AllegroKukaRegrasping, "throw": AllegroKukaThrow}
 
 # state-dict key -> task attribute holding the same tensor
 DIRECT = ["goal_states", "object_init_state", "object_keypoint_offsets", "object_scales", "finger_rew_coeffs", "obs_buf", "rew_buf",
@@ -19,10 +21,12 @@ DIRECT = ["goal_states", "object_init_state", "object_keypoint_offsets", "object
 STATE_LAYOUT = "isaacgym"      # tests switch this to "soa" to run the same cases on the component-major producer layout
 
 
-def make_task(n: int, device: str = "cuda:0", overrides=None, snapshots: int = 1, state_layout=None) -> AllegroKukaReorientation:
-    cfg = hcfg.load_task_config("AllegroKuka", num_envs=n, sim_device=device, overrides=overrides)
+def make_task(n: int, device: str = "cuda:0", overrides=None, snapshots: int = 1, state_layout=None,
+              subtask: str = "reorientation") -> AllegroKukaReorientation:
+    cfg = hcfg.load_task_config("AllegroKuka", num_envs=n, sim_device=device, overrides=overrides,
+                                subtask=None if subtask == "reorientation" else subtask)
     sim = SyntheticSim(n, KUKA_LAYOUT, device, seed=1, snapshots=snapshots, state_layout=state_layout or STATE_LAYOUT)
-    return AllegroKukaReorientation(cfg, device, device, 0, True, sim=sim)
+    return SUBTASK_CLASSES[subtask](cfg, device, device, 0, True, sim=sim)
 
 
 def load_state(task, st: Dict[str, torch.Tensor]) -> None:

@@ -64,7 +64,7 @@ def assert_state_close(got, want, keys_exact=EXACT, keys_float=FLOAT, ctx=""):
 def run_both(n, seed, fresh, steps=2, overrides=None, consts=None, post_grid=0):
     c = consts or ko.KukaConsts()
     st = ks.make_state(n, seed=seed, c=c, fresh=fresh)
-    task = kh.make_task(n, overrides=overrides)
+    task = kh.make_task(n, overrides=overrides, subtask=c.subtask)
     task.set_post_grid(post_grid)
     kh.load_state(task, st)
     for step in range(steps):
@@ -138,6 +138,24 @@ def test_kuka_post_grid_does_not_change_results():
     for o in outs[1:]:
         for k in EXACT + FLOAT + ["stats"]:
             assert torch.equal(o[k], outs[0][k]), k
+
+
+# ---- sibling subtasks of the single-arm task through the same kernels (allegro_kuka_regrasping.py, allegro_kuka_throw.py) -------
+SUBTASK_CONSTS = {
+    "regrasping": (ko.KukaConsts(subtask="regrasping", success_steps=30, max_episode_length=300), {}),
+    "throw": (ko.KukaConsts(subtask="throw", success_steps=5, max_episode_length=300, force_scale=0.0, success_tolerance=0.075,
+                            initial_tolerance=0.075, target_tolerance=0.075), {}),
+}
+
+
+@pytest.mark.parametrize("subtask", list(SUBTASK_CONSTS))
+@pytest.mark.parametrize("n,fresh", [(33, True), (1000, False), (8192 + 7, False)])
+def test_kuka_subtasks_match_oracle(subtask, n, fresh):
+    """One keypoint (99-wide rows, kuka_post_kernel<1>), goal resets that put the object back on the table, the bucket of the throw
+    task; the task reads env/regrasping.yaml / env/throw.yaml on top of AllegroKuka.yaml like the reference's registry does."""
+    c, over = SUBTASK_CONSTS[subtask]
+    task, st = run_both(n, seed=31 + n, fresh=fresh, steps=3, consts=c, overrides=over)
+    assert task.num_obs == 99 and task.num_keypoints == 1
 
 
 def test_kuka_success_steps_and_no_forces():

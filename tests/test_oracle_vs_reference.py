@@ -12,9 +12,19 @@ pytestmark = [pytest.mark.reference,
               pytest.mark.skipif(not rl.reference_available(), reason="reference tree not present on this machine")]
 
 
+SUBTASKS = {
+    "reorientation": ko.KukaConsts(),
+    # env/regrasping.yaml, env/throw.yaml on top of AllegroKuka.yaml
+    "regrasping": ko.KukaConsts(subtask="regrasping", success_steps=30, max_episode_length=300),
+    "throw": ko.KukaConsts(subtask="throw", success_steps=5, max_episode_length=300, force_scale=0.0, success_tolerance=0.075,
+                           initial_tolerance=0.075, target_tolerance=0.075),
+}
+
+
+@pytest.mark.parametrize("subtask", list(SUBTASKS))
 @pytest.mark.parametrize("n,seed,fresh", [(257, 3, True), (257, 4, False), (1024, 5, False)])
-def test_restatement_is_bit_exact_against_reference(n, seed, fresh):
-    c = ko.KukaConsts()
+def test_restatement_is_bit_exact_against_reference(n, seed, fresh, subtask):
+    c = SUBTASKS[subtask]
     st = ks.make_state(n, seed=seed, c=c, fresh=fresh)
     st_ref = ks.clone_state(st)
     env = rl.make_reference_kuka(st_ref, c)
