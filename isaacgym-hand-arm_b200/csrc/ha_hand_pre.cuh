@@ -45,6 +45,12 @@ __device__ __forceinline__ f4 hand_random_rotation(float r0, float r1) {
   return quat_mul(quat_axis_angle(r0 * pi, 0), quat_axis_angle(r1 * pi, 1));
 }
 
+// randomize_rotation_pen (shadow_hand.py:809-814, max_angle = 0.3): quat_mul(aa(pi / 2 + r0 * 0.3, x), aa(r0 * pi, z))
+__device__ __forceinline__ f4 hand_random_rotation_pen(float r0) {
+  const float pi = 3.1415927410125732f, half_pi = 1.5707963705062866f;   // float32(np.pi), float32(0.5 * np.pi)
+  return quat_mul(quat_axis_angle(half_pi + r0 * 0.3f, 0), quat_axis_angle(r0 * pi, 2));
+}
+
 struct HandPreSmem {
   float pos[kEnvsPerCta][HA_HAND_MAX_DOFS];   // re-randomised DOF positions of the tile's reset envs
   long long fold[8];                          // statistics fold of the CTAs below kHandNPart (hand_fold_*)
@@ -200,7 +206,7 @@ hand_pre_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__ 
       const float v0 = __ldg(init + c);
       rr[c] = (c < 2 || c == p.up_axis_idx) ? v0 + p.reset_position_noise * r[c] : v0;
     }
-    const f4 q = hand_random_rotation(r[3], r[4]);
+    const f4 q = p.ignore_z_rot ? hand_random_rotation_pen(r[3]) : hand_random_rotation(r[3], r[4]);   // objectType "pen" (:626-629)
     rr[3] = q.x; rr[4] = q.y; rr[5] = q.z; rr[6] = q.w;
 #pragma unroll
     for (int c = 7; c < 13; ++c) rr[c] = 0.0f;

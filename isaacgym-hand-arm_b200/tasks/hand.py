@@ -70,8 +70,6 @@ class _HandTask(VecTask):
         self.av_factor = env.get("averFactor", 0.1)
         self.object_type = env["objectType"]
         assert self.object_type in ["block", "egg", "pen"]
-        if self.object_type == "pen":
-            raise NotImplementedError("objectType 'pen' (randomize_rotation_pen) is not built; block and egg are")
         self.ignore_z = self.object_type == "pen"
         self.obs_type = env["observationType"]
         if self.obs_type not in self.num_obs_dict:

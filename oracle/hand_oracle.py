@@ -149,6 +149,15 @@ def randomize_rotation(rand0: Tensor, rand1: Tensor) -> Tensor:
     return quat_mul(quat_from_angle_axis(rand0 * np.pi, x_unit), quat_from_angle_axis(rand1 * np.pi, y_unit))
 
 
+def randomize_rotation_pen(rand0: Tensor, rand1: Tensor) -> Tensor:
+    """shadow_hand.py:809-814 as reset_idx calls it (:626-629, max_angle = tensor(0.3)); rand1 is unused by the reference too."""
+    n = rand0.shape[0]
+    x_unit = torch.tensor([1.0, 0.0, 0.0]).repeat(n, 1)
+    z_unit = torch.tensor([0.0, 0.0, 1.0]).repeat(n, 1)
+    max_angle = torch.tensor(0.3)
+    return quat_mul(quat_from_angle_axis(0.5 * np.pi + rand0 * max_angle, x_unit), quat_from_angle_axis(rand0 * np.pi, z_unit))
+
+
 # ---------------------------------------------------------------------------------------------
 # pre-physics step
 # ---------------------------------------------------------------------------------------------
@@ -176,7 +185,8 @@ def _reset_idx(st: Dict[str, Tensor], c: HandConsts, ids: Tensor, rnd: Tensor) -
     st["root_state"][rows] = init.clone()
     st["root_state"][rows, 0:2] = init[:, 0:2] + c.reset_position_noise * r[:, 0:2]
     st["root_state"][rows, c.up_axis_idx] = init[:, c.up_axis_idx] + c.reset_position_noise * r[:, c.up_axis_idx]
-    st["root_state"][rows, 3:7] = randomize_rotation(r[:, 3], r[:, 4])
+    # objectType == "pen" (ignore_z_rot): the pen starts roughly upright (shadow_hand.py:626-629)
+    st["root_state"][rows, 3:7] = randomize_rotation_pen(r[:, 3], r[:, 4]) if c.ignore_z_rot else randomize_rotation(r[:, 3], r[:, 4])
     st["root_state"][rows, 7:13] = 0.0
     pr = torch.tensor(c.force_prob_range, dtype=torch.float32)
     st["random_force_prob"][ids] = torch.exp((torch.log(pr[0]) - torch.log(pr[1])) * rnd[ids, RND_FORCE_PROB] + torch.log(pr[1]))

@@ -24,7 +24,8 @@ def overrides_from_consts(c) -> Dict[str, object]:
             "env.actionsMovingAverage": c.act_moving_average, "env.forceScale": c.force_scale, "env.forceDecay": c.force_decay,
             "env.forceDecayInterval": c.force_decay_interval, "env.forceProbRange": list(c.force_prob_range),
             "env.resetPositionNoise": c.reset_position_noise, "env.resetDofPosRandomInterval": c.reset_dof_pos_noise,
-            "env.resetDofVelRandomInterval": c.reset_dof_vel_noise, "env.clipObservations": c.clip_obs, "sim.dt": c.dt}
+            "env.resetDofVelRandomInterval": c.reset_dof_vel_noise, "env.clipObservations": c.clip_obs, "sim.dt": c.dt,
+            "env.objectType": "pen" if c.ignore_z_rot else "block"}
 
 
 def make_task(n: int, c, device: str = "cuda:0"):

@@ -16,6 +16,7 @@ CASES = {
     "shadow_openai_asym_forces": ho.HandConsts(obs_type="openai", asymmetric=True, force_scale=1.0, max_consecutive_successes=50,
                                                fall_penalty=-50.0, act_moving_average=0.3),
     "shadow_relative": ho.HandConsts(obs_type="full", use_relative_control=True, reset_dof_vel_noise=0.1),
+    "shadow_pen": ho.HandConsts(ignore_z_rot=True),        # objectType "pen": randomize_rotation_pen + doubled success tolerance
     "allegro_full_state": ho.allegro_consts(),
     "allegro_full": ho.allegro_consts(obs_type="full", force_scale=2.0, max_consecutive_successes=10, fall_penalty=-10.0),
     "allegro_no_vel_asym": ho.allegro_consts(obs_type="full_no_vel", asymmetric=True, act_moving_average=0.5),
