@@ -64,11 +64,14 @@ __device__ __forceinline__ float clipf(float x, float lo, float hi) { return fmi
 __device__ __forceinline__ f4 random_quat(float u, float v, float w) {
   const float two_pi = 6.2831854820251465f;  // float32(2*pi)
   const float s1 = sqrtf(1.0f - u), s2 = sqrtf(u);
+  float sv, cv, sw, cw;
+  sincosf(two_pi * v, &sv, &cv);          // one range reduction per angle; same values as sinf / cosf
+  sincosf(two_pi * w, &sw, &cw);
   f4 q;
-  q.w = s1 * sinf(two_pi * v);
-  q.x = s1 * cosf(two_pi * v);
-  q.y = s2 * sinf(two_pi * w);
-  q.z = s2 * cosf(two_pi * w);
+  q.w = s1 * sv;
+  q.x = s1 * cv;
+  q.y = s2 * sw;
+  q.z = s2 * cw;
   return q;
 }
 

@@ -98,7 +98,7 @@ __device__ __forceinline__ int kuka_object_row(const HaKukaParams& p, const HaKu
 //   regrasping     allegro_kuka_regrasping.py:76-100      position only (the goal ball keeps its rotation)
 //   throw          allegro_kuka_throw.py:90-117           bucket left / right of the table (4 draws), goal = bucket + 5 cm
 // (regrasping / throw also put the object back on the table: the caller runs kuka_object_reset and clears lifted_object)
-__device__ __noinline__ void kuka_goal_reset(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env, bool rst) {
+__device__ __noinline__ void kuka_goal_reset(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand R, int env, bool rst) {
   const float4 u_gp = kuka_draw4(R, env, rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS);
   float* gs = b.goal_states + (size_t)env * 13;
   const RootRow rr = root_row(p, b, kuka_goal_row(p, b, env), env, p.goal_slot);
@@ -136,7 +136,7 @@ __device__ __noinline__ void kuka_goal_reset(const HaKukaParams& p, const HaKuka
 }
 
 // reset_object_pose (:1198-1224); torch_rand_float(-1, 1) = 2 u - 1
-__device__ __noinline__ void kuka_object_reset(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand& R, int env) {
+__device__ __noinline__ void kuka_object_reset(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand R, int env) {
   const float* init = b.object_init_state + (size_t)env * 13;
   const float init0 = __ldg(init + 0), init1 = __ldg(init + 1), init2 = __ldg(init + 2);
   const float4 u_op = kuka_draw4(R, env, HA_KUKA_RND_OBJ_POS), u_or = kuka_draw4(R, env, HA_KUKA_RND_OBJ_ROT);
