@@ -48,25 +48,6 @@ struct KukaPreSmem {
   long long fold[kThreads / 32];   // statistics fold of the CTAs below kNPart (kuka_fold_*)
 };
 
-// reset_idx DOF re-randomisation of ONE (env, dof) element (:1271-1290): returns (position, velocity)
-__device__ __forceinline__ float2 kuka_reset_dof(const KukaRand& R, const KukaPreSmem& s, float vel_noise, int env, int d) {
-  constexpr int D = 23;
-  float u_pos, u_vel;
-  if (R.ext) {
-    u_pos = __ldg(R.ext + (size_t)env * R.stride + HA_KUKA_RND_DOF_POS + d);
-    u_vel = __ldg(R.ext + (size_t)env * R.stride + HA_KUKA_RND_DOF_POS + D + d);
-  } else {
-    const float2 u = R.rng.uniform2(env, 64 + d);     // one Philox block per DOF: (.x, .y) = (pos, vel) draws
-    u_pos = u.x; u_vel = u.y;
-  }
-  const float lo = s.lim[d].x, hi = s.lim[d].y, dflt = s.dflt[d], noise = s.noise[d];
-  const float delta_max = hi - dflt, delta_min = lo - dflt;
-  const float rand_delta = delta_min + (delta_max - delta_min) * u_pos;
-  const float pos = dflt + noise * rand_delta;
-  const float vel = vel_noise * (2.0f * u_vel + -1.0f);
-  return make_float2(pos, vel);
-}
-
 __device__ __forceinline__ float4 kuka_draw4(const KukaRand& R, int env, int slot) {   // inlined: independent Philox chains overlap
   if (R.ext) {
     const float* r = R.ext + (size_t)env * R.stride + slot;
@@ -92,64 +73,6 @@ __device__ __forceinline__ int kuka_object_row(const HaKukaParams& p, const HaKu
   return p.root_regular ? env * p.actors_per_env + p.object_slot : b.object_actor[env];
 }
 
-// goal of one env: reset_target_pose (:1191-1196) with the subtask's _reset_target.  An env that is in both sets is drawn twice by
-// the reference and the reset_idx draw wins: `rst` selects the RESET_GOAL slots.
-//   reorientation  allegro_kuka_reorientation.py:104-128  position in the target volume + random rotation, goal row velocities = 0
-//   regrasping     allegro_kuka_regrasping.py:76-100      position only (the goal ball keeps its rotation)
-//   throw          allegro_kuka_throw.py:90-117           bucket left / right of the table (4 draws), goal = bucket + 5 cm
-// (regrasping / throw also put the object back on the table: the caller runs kuka_object_reset and clears lifted_object)
-__device__ __noinline__ void kuka_goal_reset(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand R, int env, bool rst) {
-  const float4 u_gp = kuka_draw4(R, env, rst ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS);
-  float* gs = b.goal_states + (size_t)env * 13;
-  const RootRow rr = root_row(p, b, kuka_goal_row(p, b, env), env, p.goal_slot);
-  if (p.subtask == HA_KUKA_THROW) {
-    // torch_rand_float(lo, hi) = (hi - lo) * u + lo
-    const float left_right = 2.0f * u_gp.x + -1.0f;
-    float x = left_right > 0.0f ? 0.5f : -0.5f;
-    const float sgn = left_right > 0.0f ? 1.0f : (left_right < 0.0f ? -1.0f : 0.0f);
-    x = x + sgn * (0.4f * u_gp.y + 0.0f);
-    const float y = 1.7f * u_gp.z + -1.0f;
-    const float z = 1.0f * u_gp.w + 0.0f;
-    rr.at(0) = x; rr.at(1) = y; rr.at(2) = z;
-    gs[0] = x; gs[1] = y; gs[2] = z + 0.05f;
-  } else {
-    float g[7];
-    g[0] = p.target_min[0] + u_gp.x * p.target_size[0];
-    g[1] = p.target_min[1] + u_gp.y * p.target_size[1];
-    g[2] = p.target_min[2] + u_gp.z * p.target_size[2];
-    if (p.subtask == HA_KUKA_REORIENTATION) {
-      const float4 u_gr = kuka_draw4(R, env, rst ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT);
-      const f4 q = random_quat(u_gr.x, u_gr.y, u_gr.z);
-      g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
-#pragma unroll
-      for (int c = 0; c < 7; ++c) { gs[c] = g[c]; rr.at(c) = g[c]; }
-#pragma unroll
-      for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
-    } else {
-#pragma unroll
-      for (int c = 0; c < 3; ++c) { gs[c] = g[c]; rr.at(c) = g[c]; }
-    }
-  }
-  b.reset_goal_buf[env] = 0;
-  b.near_goal_steps[env] = 0;
-  b.closest_keypoint_max_dist[env] = -1.0f;
-}
-
-// reset_object_pose (:1198-1224); torch_rand_float(-1, 1) = 2 u - 1
-__device__ __noinline__ void kuka_object_reset(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand R, int env) {
-  const float* init = b.object_init_state + (size_t)env * 13;
-  const float init0 = __ldg(init + 0), init1 = __ldg(init + 1), init2 = __ldg(init + 2);
-  const float4 u_op = kuka_draw4(R, env, HA_KUKA_RND_OBJ_POS), u_or = kuka_draw4(R, env, HA_KUKA_RND_OBJ_ROT);
-  const RootRow rr = root_row(p, b, kuka_object_row(p, b, env), env, p.object_slot);
-  rr.at(0) = init0 + p.reset_pos_noise[0] * (2.0f * u_op.x + -1.0f);
-  rr.at(1) = init1 + p.reset_pos_noise[1] * (2.0f * u_op.y + -1.0f);
-  rr.at(2) = init2 + p.reset_pos_noise[2] * (2.0f * u_op.z + -1.0f);
-  const f4 q = random_quat(u_or.x, u_or.y, u_or.z);
-  rr.at(3) = q.x; rr.at(4) = q.y; rr.at(5) = q.z; rr.at(6) = q.w;
-#pragma unroll
-  for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
-}
-
 // action -> DOF target of one element (:1377-1397): absolute control with a moving average for the hand DOFs, relative control
 // for the 7 arm DOFs
 __device__ __forceinline__ float kuka_dof_target(float av, float pv, int d, float2 lh, float ema, float one_m_ema, float gain) {
@@ -164,15 +87,123 @@ __device__ __forceinline__ float kuka_dof_target(float av, float pv, int d, floa
   return x;
 }
 
+// The whole re-randomisation of ONE env by ONE warp, one independent piece per lane: every piece starts with one Philox block (or
+// its row of the parity table), so a single pass of the generator serves all of them and the dependent chain of the reset -- which
+// bounds the launch, the tiles with a reset are its last ones to finish -- is one generator pass + one random_quat + a few stores.
+//   lanes 0..22  DOF d: reset_idx DOF re-randomisation (:1271-1290), prev_targets = cur_targets = pos (:1289-1290), then the
+//                action pass on that position                                                          [full resets only]
+//   lane 23      goal position, reset_target_pose (:1191-1196) with the subtask's _reset_target:
+//                  reorientation  allegro_kuka_reorientation.py:104-128  position in the target volume (+ rotation: lane 24)
+//                  regrasping     allegro_kuka_regrasping.py:76-100      position only (the goal ball keeps its rotation)
+//                  throw          allegro_kuka_throw.py:90-117           bucket left / right of the table (4 draws), goal = bucket + 5 cm
+//                an env that is in both sets is drawn twice by the reference and the reset_idx draw wins:
+//                `full` selects the RESET_GOAL slots
+//   lane 24      goal rotation (reorientation), goal row velocities = 0
+//   lane 25      object position, reset_object_pose (:1198-1224) and its tail (:1221-1224) + lifted_object
+//   lane 26      object rotation, object row velocities = 0
+//                (regrasping / throw also put the object back on the table on a goal-only reset)
+__device__ __forceinline__ void kuka_reset_env(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand R, const KukaPreSmem& s,
+                                            const float* __restrict__ actions, const int env, const int lane, const bool full,
+                                            const bool reset_only) {
+  constexpr int D = 23;
+  enum { kGoalPos = D, kGoalRot = D + 1, kObjPos = D + 2, kObjRot = D + 3 };
+  const bool reorient = p.subtask == HA_KUKA_REORIENTATION;
+  const bool with_object = full || !reorient;
+  bool active;
+  int slot = 0;
+  if (lane < D) active = full;
+  else if (lane == kGoalPos) { active = true; slot = full ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS; }
+  else if (lane == kGoalRot) { active = reorient; slot = full ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT; }
+  else if (lane == kObjPos) { active = with_object; slot = HA_KUKA_RND_OBJ_POS; }
+  else if (lane == kObjRot) { active = with_object; slot = HA_KUKA_RND_OBJ_ROT; }
+  else active = false;
+  if (!active) return;
+  // the two loads of the chain go first (object_init_state is cold: a DRAM round trip)
+  float act_v = 0.f, init0 = 0.f, init1 = 0.f, init2 = 0.f;
+  if (lane < D) {
+    if (!reset_only) act_v = __ldg(actions + (size_t)env * D + lane);
+  } else if (lane == kObjPos) {
+    const float* init = b.object_init_state + (size_t)env * 13;
+    init0 = __ldg(init + 0); init1 = __ldg(init + 1); init2 = __ldg(init + 2);
+  }
+  float4 u;
+  if (R.ext) {
+    const float* r = R.ext + (size_t)env * R.stride;
+    if (lane < D) u = make_float4(__ldg(r + HA_KUKA_RND_DOF_POS + lane), __ldg(r + HA_KUKA_RND_DOF_POS + D + lane), 0.f, 0.f);
+    else u = make_float4(__ldg(r + slot), __ldg(r + slot + 1), __ldg(r + slot + 2), __ldg(r + slot + 3));
+  } else {
+    u = R.rng.uniform4(env, lane < D ? 64 + lane : 32 + slot);   // DOF d: block 64 + d, (.x, .y) = (pos, vel) draws
+  }
+  HA_TRACE_POINT_IF(0, 4, threadIdx.x == 23);            // draws in hand
+  if (lane < D) {
+    const int d = lane;
+    const size_t idx = (size_t)env * D + d;
+    const float lo = s.lim[d].x, hi = s.lim[d].y, dflt = s.dflt[d], noise = s.noise[d];
+    const float delta_max = hi - dflt, delta_min = lo - dflt;
+    const float rand_delta = delta_min + (delta_max - delta_min) * u.x;
+    const float pos = dflt + noise * rand_delta;
+    const float vel = p.reset_dof_vel_noise * (2.0f * u.y + -1.0f);
+    *reinterpret_cast<float2*>(b.dof_state + 2 * idx) = make_float2(pos, vel);
+    const float x = reset_only ? pos : kuka_dof_target(act_v, pos, d, s.lim[d], p.act_moving_average,
+                                                         p.one_minus_act_moving_average, p.arm_action_gain);
+    b.cur_targets[idx] = x;
+    b.prev_targets[idx] = x;
+    HA_TRACE_POINT_IF(0, 3, threadIdx.x == 0);           // DOF rows stored
+    return;
+  }
+  const bool goal_lane = lane == kGoalPos || lane == kGoalRot;
+  const RootRow rr = goal_lane ? root_row(p, b, kuka_goal_row(p, b, env), env, p.goal_slot)
+                               : root_row(p, b, kuka_object_row(p, b, env), env, p.object_slot);
+  float* gs = b.goal_states + (size_t)env * 13;
+  if (lane == kGoalRot || lane == kObjRot) {
+    const f4 q = random_quat(u.x, u.y, u.z);
+    rr.at(3) = q.x; rr.at(4) = q.y; rr.at(5) = q.z; rr.at(6) = q.w;
+#pragma unroll
+    for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
+    if (lane == kGoalRot) { gs[3] = q.x; gs[4] = q.y; gs[5] = q.z; gs[6] = q.w; }
+    HA_TRACE_POINT_IF(0, 11, threadIdx.x == 24);         // rotations stored
+  } else if (lane == kGoalPos) {
+    float x, y, z, gz;
+    if (p.subtask == HA_KUKA_THROW) {
+      // torch_rand_float(lo, hi) = (hi - lo) * u + lo
+      const float left_right = 2.0f * u.x + -1.0f;
+      x = left_right > 0.0f ? 0.5f : -0.5f;
+      const float sgn = left_right > 0.0f ? 1.0f : (left_right < 0.0f ? -1.0f : 0.0f);
+      x = x + sgn * (0.4f * u.y + 0.0f);
+      y = 1.7f * u.z + -1.0f;
+      z = 1.0f * u.w + 0.0f;
+      gz = z + 0.05f;
+    } else {
+      x = p.target_min[0] + u.x * p.target_size[0];
+      y = p.target_min[1] + u.y * p.target_size[1];
+      z = p.target_min[2] + u.z * p.target_size[2];
+      gz = z;
+    }
+    rr.at(0) = x; rr.at(1) = y; rr.at(2) = z;
+    gs[0] = x; gs[1] = y; gs[2] = gz;
+    b.reset_goal_buf[env] = 0;
+    b.near_goal_steps[env] = 0;
+    b.closest_keypoint_max_dist[env] = -1.0f;
+  } else {   // kObjPos; torch_rand_float(-1, 1) = 2 u - 1
+    HA_TRACE_POINT_IF(0, 12, threadIdx.x == 25 && init0 != 123456.f);   // object_init_state arrived
+    rr.at(0) = init0 + p.reset_pos_noise[0] * (2.0f * u.x + -1.0f);
+    rr.at(1) = init1 + p.reset_pos_noise[1] * (2.0f * u.y + -1.0f);
+    rr.at(2) = init2 + p.reset_pos_noise[2] * (2.0f * u.z + -1.0f);
+    *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
+    b.furthest_hand_dist[env] = -1.0f;
+    b.lifted_object[env] = 0;
+  }
+}
+
 // CTA = tile of 32 envs, 4 warps.
 //   element pass (all threads): the contiguous [32, 23] tiles of actions / prev_targets / cur_targets as 128-bit vectors, loads
-//   issued before the masks are known, no branch on the masks.  In a tile with a full reset the rows of the reset envs are redone
-//   afterwards, one warp per env with lane = DOF (DOF re-randomisation :1271-1290 feeds the action pass), behind a second barrier
-//   that only those tiles execute.
-//   per-env work, lane = env, one part per warp so that no warp carries a long dependent chain:
-//     warp 1   random forces on the object body (every step), random_force_prob of reset envs
-//     tiles with a reset only:  0 goal pose   2 object pose + half of the accumulators   3 actor-row lists (the returning atomic
-//     is issued right after the ballots and consumed last) + episode bookkeeping + the other half
+//   issued before the masks are known, no branch on the masks in the tiles without a reset (9 of 10 at the benchmark's reset rate).
+//   warp 1: random forces on the object body (every step), random_force_prob of reset envs.
+//   Tiles with a reset (uniform branch): the re-randomisation runs FIRST, one warp per env with one independent piece per lane
+//   (kuka_reset_env: inlined, so that the kernel parameters stay constant-bank operands -- behind a call they become generic
+//   loads from the parameter space, a dependent chain of L2 round trips that used to dominate these tiles), then the element pass,
+//   which leaves the rows of the full resets alone; what stays per tile with lane = env: warp 2 half of the accumulators, warp 3
+//   episode bookkeeping + the other half + the actor-row lists (returning atomic issued right after the ballots, consumed last).
 //   One CTA barrier, right after the ballots: it publishes the per-DOF tables and marks the point from which the masks may be
 //   cleared (every warp holds its ballots).
 __global__ void __launch_bounds__(kThreads, 8)
@@ -275,7 +306,6 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     }
   }
   if (fold) kuka_fold_warp(sf, blockIdx.x, tid, s.fold);
-  HA_TRACE_POINT(0, 3);
   __syncthreads();       // tables and fold partials visible; every warp holds its ballots: the masks may be cleared from here on
   HA_TRACE_POINT(0, 5);                                 // barrier
   if (fold && tid == kThreads - 1) kuka_fold_finish(b, blockIdx.x, n, s.fold);
@@ -287,57 +317,69 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
 
   // ---------------- all threads: DOF targets, 4 consecutive elements per float4 ----------------
   const float ema = p.act_moving_average, one_m_ema = p.one_minus_act_moving_average, gain = p.arm_action_gain;
-  if (!reset_only) {
-    const bool copy_actions = (actions != b.actions);
+  const bool copy_actions = (actions != b.actions);
+  // `skip`: envs of the tile whose rows kuka_reset_env writes (full reset); 0 in all but a few tiles -> plain 128-bit stores
+  auto element_pass = [&](const unsigned skip) {
 #pragma unroll
     for (int i = 0; i < kIters; ++i) {
       const int q = tid + i * kThreads;
       if (q >= nvec) continue;
       const int f0 = 4 * q;
-      {
-        int d = f0 - (f0 / D) * D;
-        float4 o;
-        o.x = kuka_dof_target(a[i].x, prev[i].x, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
-        o.y = kuka_dof_target(a[i].y, prev[i].y, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
-        o.z = kuka_dof_target(a[i].z, prev[i].z, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
-        o.w = kuka_dof_target(a[i].w, prev[i].w, d, s.lim[d], ema, one_m_ema, gain);
+      const int e0 = f0 / D;
+      const int d0 = f0 - e0 * D;
+      int d = d0;
+      float4 o;
+      o.x = kuka_dof_target(a[i].x, prev[i].x, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
+      o.y = kuka_dof_target(a[i].y, prev[i].y, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
+      o.z = kuka_dof_target(a[i].z, prev[i].z, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
+      o.w = kuka_dof_target(a[i].w, prev[i].w, d, s.lim[d], ema, one_m_ema, gain);
+      if (skip == 0u) {
         *(reinterpret_cast<float4*>(b.cur_targets + base) + q) = o;
         *(reinterpret_cast<float4*>(b.prev_targets + base) + q) = o;       // (:1397)
-        if (copy_actions) *(reinterpret_cast<float4*>(b.actions + base) + q) = a[i];   // self.actions = actions.clone() (:1357)
+      } else {
+        const float ov[4] = {o.x, o.y, o.z, o.w};
+        int e = e0, dd = d0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (!((skip >> e) & 1u)) {
+            b.cur_targets[base + f0 + j] = ov[j];
+            b.prev_targets[base + f0 + j] = ov[j];
+          }
+          if (++dd == D) { dd = 0; ++e; }
+        }
       }
+      if (copy_actions) *(reinterpret_cast<float4*>(b.actions + base) + q) = a[i];   // self.actions = actions.clone() (:1357)
     }
     // ragged last tile: up to 3 trailing elements
     const int f = (nvec << 2) + tid;
     if (f < total) {
-      const int d = f - (f / D) * D;
+      const int e = f / D, d = f - e * D;
       const float av = __ldg(actions + base + f);
-      const float x = kuka_dof_target(av, b.prev_targets[base + f], d, s.lim[d], ema, one_m_ema, gain);
-      b.cur_targets[base + f] = x;
-      b.prev_targets[base + f] = x;
+      if (!((skip >> e) & 1u)) {
+        const float x = kuka_dof_target(av, b.prev_targets[base + f], d, s.lim[d], ema, one_m_ema, gain);
+        b.cur_targets[base + f] = x;
+        b.prev_targets[base + f] = x;
+      }
       if (copy_actions) b.actions[base + f] = av;
     }
-  }
-  HA_TRACE_POINT(0, 6);                                 // element pass stored
-  if (m_rst != 0u) {
-    // rows of the reset envs again (uniform over the CTA): one warp per env, lane = DOF.  The barrier orders these stores behind
-    // the element pass's; the actions come back from L1 / L2.
-    __syncthreads();
-    unsigned m = m_rst;
+  };
+  if (m_any == 0u) {
+    if (!reset_only) element_pass(0u);
+    HA_TRACE_POINT(0, 6);                               // element pass stored
+  } else {
+    // tiles with a reset (uniform over the CTA): the re-randomisation FIRST -- it is the longest dependent chain of the launch --
+    // one warp per env (kuka_reset_env), envs of rank 0, 1, 2, 3 -> warps 0, 2, 3, 1 (warp 1 carries the forces, warp 3 the
+    // lists); then the element pass, which leaves the rows of the full resets alone, so the two need no ordering.
+    unsigned m = m_any;
     int rank = 0;
     while (m) {
       const int e = __ffs(m) - 1;
       m &= m - 1;
-      if ((rank++ & (kThreads / 32 - 1)) == warp && lane < D) {
-        const int d = lane;
-        const size_t idx = base + (size_t)e * D + d;
-        const float2 pvel = kuka_reset_dof(R, s, p.reset_dof_vel_noise, env0 + e, d);
-        *reinterpret_cast<float2*>(b.dof_state + 2 * idx) = pvel;
-        // prev_targets = cur_targets = pos (:1289-1290), then the action pass on that position
-        const float x = reset_only ? pvel.x : kuka_dof_target(__ldg(actions + idx), pvel.x, d, s.lim[d], ema, one_m_ema, gain);
-        b.cur_targets[idx] = x;
-        b.prev_targets[idx] = x;
-      }
+      if (((0x1320 >> ((rank++ & 3) * 4)) & 3) == warp) kuka_reset_env(p, b, R, s, actions, env0 + e, lane, (m_rst >> e) & 1u, reset_only);
     }
+    HA_TRACE_POINT(0, 10);                              // warp 0: its envs are done
+    if (!reset_only) element_pass(m_rst);
+    HA_TRACE_POINT(0, 6);                               // element pass stored
   }
 
   // ---------------- warp 1: random forces on the object body, random_force_prob of reset envs ----------------
@@ -385,22 +427,14 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     }
   }
 
-  // ---------------- tiles with a reset: one part of the scalar reset work per warp, lane = env ----------------
+  // ---------------- tiles with a reset: what stays per tile (lane = env) -- accumulators, episode bookkeeping, actor-row lists ----------------
   if (m_any) {
-    if (warp == 0) {
-      if (rst || grst) kuka_goal_reset(p, b, R, env, rst);
-    } else if (warp == 2) {
-      if (rst || (grst && goal_moves_object)) kuka_object_reset(p, b, R, env);
+    if (warp == 2) {
       if (rst) {
 #pragma unroll
         for (int k = 0; k < HA_KUKA_N_EPISODE_TERMS; k += 2) b.rewards_episode[(size_t)k * n + env] = 0.0f;   // (:1341-1342)
       }
     } else if (warp == 3) {
-      if (rst || (grst && goal_moves_object)) {          // reset_object_pose's tail (:1221-1224) + lifted_object of the subtasks
-        *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
-        b.furthest_hand_dist[env] = -1.0f;
-        b.lifted_object[env] = 0;
-      }
       if (rst) {
         // episode bookkeeping (:1323-1347)
         b.progress_buf[env] = 0;
@@ -412,7 +446,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
 #pragma unroll
         for (int k = 1; k < HA_KUKA_N_EPISODE_TERMS; k += 2) b.rewards_episode[(size_t)k * n + env] = 0.0f;
       }
-      HA_TRACE_POINT(0, 7);
+      HA_TRACE_POINT_IF(0, 7, tid == 96);
       // list slots: the atomic issued before the barrier is consumed here, as the last thing this warp does
       const unsigned long long old = __shfl_sync(0xffffffffu, list_old, 0);
       const int root_base = (int)(unsigned)(old & 0xffffffffULL), hand_base = (int)(unsigned)(old >> 32);
@@ -423,7 +457,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
         if (rst) b.hand_reset_indices[hand_base + __popc(m_rst & below)] = hand_row;
         b.root_reset_indices[k] = kuka_goal_row(p, b, env);
       }
-      HA_TRACE_POINT(0, 8);
+      HA_TRACE_POINT_IF(0, 8, tid == 96);
     }
   }
   HA_TRACE_POINT(0, 9);

@@ -72,7 +72,8 @@ def pct(x):
     return f"med {np.median(x):7.2f}  p90 {np.percentile(x, 90):7.2f}  max {x.max():7.2f}"
 
 
-names = {0: ["start", "loads issued, masks in", "ballots", "list atomic issued", "reset w0: goal reset done", "barrier", "element pass stored", "reset w3: rows + bookkeeping stored", "reset w3: lists written", "end"],
+names = {0: ["start", "loads issued, masks in", "ballots", "reset w0: DOF rows stored", "reset w0: draws in hand", "barrier", "element pass stored", "reset w3: bookkeeping stored", "reset w3: lists written", "end",
+             "reset w0: its envs done", "reset w0: rotations stored", "reset w0: object_init_state arrived"],
          1: ["start", "prologue+issue", "t0 B1 inputs", "t0 role0 tips done", "t0 role1 keypoints done", "t0 role2 dofs done", "t0 role3 copies done",
              "t0 B2", "t0 reward chain done", "t0 B3", "t1 B1 inputs", "t1 B2", "t1 B3", "end"]}
 spans = {}
