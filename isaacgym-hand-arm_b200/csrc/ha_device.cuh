@@ -125,6 +125,11 @@ struct Rng {
     __sincosf(two_pi * u32_to_unit(r.w), &s1, &c1);
     return make_float4(r0 * c0, r0 * s0, r1 * c1, r1 * s1);
   }
+  // three standard normals of one env from ONE counter block (the kicked object's force components)
+  __device__ __forceinline__ void normal3(int env, uint32_t block, float (&o)[3]) const {
+    const float4 g = normal4(env, 0x10000000u | block);
+    o[0] = g.x; o[1] = g.y; o[2] = g.z;
+  }
   // standard normal for (env, slot): Box-Muller over an independent counter block
   __device__ __forceinline__ float normal(int env, int slot) const {
     const uint4 r = philox4x32_10(make_uint4((uint32_t)env, 0x80000000u | (uint32_t)(slot >> 1), (uint32_t)step, (uint32_t)(step >> 32)),
@@ -167,10 +172,11 @@ static __device__ HaTraceRec g_ha_trace[2][kTraceMaxCtas];     // [0] pre kernel
 __device__ __forceinline__ unsigned long long ha_globaltimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ int ha_smid() { int s; asm volatile("mov.u32 %0, %%smid;" : "=r"(s)); return s; }
 #define HA_TRACE_BEGIN(k) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas) { ha::HaTraceRec& r_ = ha::g_ha_trace[k][blockIdx.x]; \
-  r_.gt0 = ha::ha_globaltimer(); r_.smid = ha::ha_smid(); r_.n = 1; _Pragma("unroll") for (int i_ = 1; i_ < 14; ++i_) r_.c[i_] = 0; r_.c[0] = clock64(); } } while (0)
+  r_.gt0 = ha::ha_globaltimer(); r_.gt1 = 0; r_.smid = ha::ha_smid(); r_.n = 1; _Pragma("unroll") for (int i_ = 1; i_ < 14; ++i_) r_.c[i_] = 0; r_.c[0] = clock64(); } } while (0)
 #define HA_TRACE_POINT(k, i) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas && (i) < 14) ha::g_ha_trace[k][blockIdx.x].c[i] = clock64(); } while (0)   /* stores only: nothing the warp waits for */
 #define HA_TRACE_POINT_IF(k, i, cond) do { if ((cond) && blockIdx.x < ha::kTraceMaxCtas && (i) < 14) ha::g_ha_trace[k][blockIdx.x].c[i] = clock64(); } while (0)
-#define HA_TRACE_END(k) do { if (threadIdx.x == 0 && blockIdx.x < ha::kTraceMaxCtas) ha::g_ha_trace[k][blockIdx.x].gt1 = ha::ha_globaltimer(); } while (0)
+/* CTA end = the LAST warp's end (every warp's lane 0 takes part) */
+#define HA_TRACE_END(k) do { if ((threadIdx.x & 31) == 0 && blockIdx.x < ha::kTraceMaxCtas) atomicMax(&ha::g_ha_trace[k][blockIdx.x].gt1, ha::ha_globaltimer()); } while (0)
 #else
 #define HA_TRACE_BEGIN(k) do { } while (0)
 #define HA_TRACE_POINT(k, i) do { } while (0)

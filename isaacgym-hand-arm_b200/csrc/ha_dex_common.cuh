@@ -30,6 +30,15 @@ struct DexRand {
     }
     return rng.normal4(env, (uint32_t)(space + slot));
   }
+  // the three normals slot .. slot+2 of one env: the table's entries, or ONE counter block in fast mode
+  __device__ __forceinline__ void nrm3(int env, int slot, float (&o)[3]) const {
+    if (ext) {
+      const float* r = ext + (size_t)env * stride + slot;
+      o[0] = __ldg(r); o[1] = __ldg(r + 1); o[2] = __ldg(r + 2);
+    } else {
+      rng.normal3(env, (uint32_t)(space + slot), o);
+    }
+  }
   // uniforms of slots slot .. slot+3
   __device__ __forceinline__ float4 u4(int env, int slot) const {
     if (ext) {

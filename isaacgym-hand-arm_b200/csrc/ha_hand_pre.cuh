@@ -26,6 +26,15 @@ struct HandRand {
   __device__ __forceinline__ float nrm(int env, int slot, int j) const {
     return ext ? __ldg(ext + (size_t)env * stride + slot + j) : rng.normal(env, j);
   }
+  // the three normals slot .. slot+2 of one env: its row of the parity table, or ONE counter block in fast mode
+  __device__ __forceinline__ void nrm3(int env, int slot, float (&o)[3]) const {
+    if (ext) {
+      const float* r = ext + (size_t)env * stride + slot;
+      o[0] = __ldg(r); o[1] = __ldg(r + 1); o[2] = __ldg(r + 2);
+    } else {
+      rng.normal3(env, (uint32_t)slot, o);
+    }
+  }
 };
 
 // quat_from_angle_axis(angle, unit axis e_k) (torch_jit_utils.py:118-123): normalize([axis * sin(a/2), cos(a/2)])
@@ -146,12 +155,16 @@ hand_pre_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__ 
       if (valid) {
         float prob = b.random_force_prob[env];
         if (rst) prob = expf(p.force_log_c0 * R.u(env, HA_HAND_RND_FORCE_PROB) + p.force_log_c1);   // drawn in reset_idx, used below
+        float f[3] = {0.f, 0.f, 0.f};                // rb_forces[env_ids] = 0 (:614)
+        if (!rst) { f[0] = frow[0]; f[1] = frow[1]; f[2] = frow[2]; }          // in flight under the generator pass
         const bool hit = R.u(env, HA_HAND_RND_FORCE_TEST) < prob;
+        float kick[3] = {0.f, 0.f, 0.f};
+        if (hit) R.nrm3(env, HA_HAND_RND_FORCE_NORMAL, kick);                  // one counter block in fast mode
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          float v = rst ? 0.0f : frow[c];            // rb_forces[env_ids] = 0 (:614)
+          float v = f[c];
           v *= p.force_decay_pow;
-          if (hit) v = R.nrm(env, HA_HAND_RND_FORCE_NORMAL, c) * p.force_gain[0] * p.force_gain[1];
+          if (hit) v = kick[c] * p.force_gain[0] * p.force_gain[1];
           frow[c] = v;
         }
       }

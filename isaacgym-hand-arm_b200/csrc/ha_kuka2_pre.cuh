@@ -137,12 +137,16 @@ kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     if (p.force_enabled && !reset_only) {
       float prob = b.random_force_prob[env];
       if (rst) prob = force_prob_from(p, R.u(env, HA_KUKA2_RND_FORCE_PROB));
-      const bool hit = R.u(env, HA_KUKA2_RND_FORCE_TEST) < prob;
+      float f[3] = {0.f, 0.f, 0.f};
+      if (!rst) { f[0] = frow[0]; f[1] = frow[1]; f[2] = frow[2]; }          // in flight under the generator pass
+      const bool hit = R.ui(env, HA_KUKA2_RND_FORCE_TEST) < prob;
+      float kick[3] = {0.f, 0.f, 0.f};
+      if (hit) R.nrm3(env, HA_KUKA2_RND_FORCE_NORMAL, kick);                  // one counter block in fast mode
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        float v = rst ? 0.0f : frow[c];
+        float v = f[c];                                                       // rb_forces[env_ids] = 0 on reset
         v *= p.force_decay_pow;
-        if (hit) v = R.nrm(env, HA_KUKA2_RND_FORCE_NORMAL, c) * p.force_gain[0] * p.force_gain[1];
+        if (hit) v = kick[c] * p.force_gain[0] * p.force_gain[1];
         frow[c] = v;
       }
     } else if (rst) {

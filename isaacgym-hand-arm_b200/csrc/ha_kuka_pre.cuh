@@ -16,6 +16,9 @@
 namespace ha {
 
 enum { kPreFull = 0, kPreResetOnly = 1 };
+#ifndef HA_PRE_SPLIT_ROT
+#define HA_PRE_SPLIT_ROT 0   // 1: two warps per reset env (measured slower in-step, kept for the trace tool)
+#endif
 
 struct KukaRand {
   const float* ext;   // [n_envs, stride] or nullptr
@@ -34,6 +37,19 @@ struct KukaRand {
   }
   __device__ __noinline__ float nrm(int env, int slot, int j) const {
     return ext ? __ldg(ext + (size_t)env * stride + slot + j) : rng.normal(env, j);
+  }
+  // inlined single draw (the every-step Bernoulli test of the random forces)
+  __device__ __forceinline__ float ui(int env, int slot) const {
+    return ext ? __ldg(ext + (size_t)env * stride + slot) : rng.uniform(env, slot);
+  }
+  // the three normals slot .. slot+2 of one env: its row of the parity table, or ONE counter block in fast mode
+  __device__ __forceinline__ void nrm3(int env, int slot, float (&o)[3]) const {
+    if (ext) {
+      const float* r = ext + (size_t)env * stride + slot;
+      o[0] = __ldg(r); o[1] = __ldg(r + 1); o[2] = __ldg(r + 2);
+    } else {
+      rng.normal3(env, (uint32_t)slot, o);
+    }
   }
 };
 
@@ -104,19 +120,19 @@ __device__ __forceinline__ float kuka_dof_target(float av, float pv, int d, floa
 //                (regrasping / throw also put the object back on the table on a goal-only reset)
 __device__ __forceinline__ void kuka_reset_env(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand R, const KukaPreSmem& s,
                                             const float* __restrict__ actions, const int env, const int lane, const bool full,
-                                            const bool reset_only) {
+                                            const bool reset_only, const int part) {
   constexpr int D = 23;
   enum { kGoalPos = D, kGoalRot = D + 1, kObjPos = D + 2, kObjRot = D + 3 };
   const bool reorient = p.subtask == HA_KUKA_REORIENTATION;
   const bool with_object = full || !reorient;
-  bool active;
-  int slot = 0;
-  if (lane < D) active = full;
-  else if (lane == kGoalPos) { active = true; slot = full ? HA_KUKA_RND_RESET_GOAL_POS : HA_KUKA_RND_GOAL_POS; }
-  else if (lane == kGoalRot) { active = reorient; slot = full ? HA_KUKA_RND_RESET_GOAL_ROT : HA_KUKA_RND_GOAL_ROT; }
-  else if (lane == kObjPos) { active = with_object; slot = HA_KUKA_RND_OBJ_POS; }
-  else if (lane == kObjRot) { active = with_object; slot = HA_KUKA_RND_OBJ_ROT; }
-  else active = false;
+  // lane roles without branches: special lanes r = 0..3 (goal position, goal rotation, object position, object rotation)
+  static_assert(HA_KUKA_RND_GOAL_POS == 0 && HA_KUKA_RND_GOAL_ROT == 3 && HA_KUKA_RND_RESET_GOAL_POS == 6 && HA_KUKA_RND_RESET_GOAL_ROT == 9 &&
+                HA_KUKA_RND_OBJ_POS == 12 && HA_KUKA_RND_OBJ_ROT == 15, "slot arithmetic below");
+  const int r = lane - D;
+  // part: 0 = the rotations (random_quat is the longest piece), 1 = everything else, 2 = both
+  const bool rot_lane = r == 1 || r == 3;
+  const bool active = (part == 2 || rot_lane == (part == 0)) && (lane < D ? full : ((unsigned)r < 4u && (r == 0 || (r == 1 ? reorient : with_object))));
+  const int slot = ((r < 2 && !full) ? 0 : 6) + 3 * r;
   if (!active) return;
   // the two loads of the chain go first (object_init_state is cold: a DRAM round trip)
   float act_v = 0.f, init0 = 0.f, init1 = 0.f, init2 = 0.f;
@@ -287,8 +303,6 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   const bool goal_moves_object = p.subtask != HA_KUKA_REORIENTATION;
   const int rows_goal_only = goal_moves_object ? 2 : 1;
   unsigned long long list_old = 0;
-  float succ = 0.f, tobj = 0.f;
-  int hand_row = 0;
   if (warp == 3 && m_any) {
     // actor rows for set_actor_root_state_tensor_indexed / set_dof_*_indexed: warp-aggregated append, rows of one env stay adjacent.
     // The four counters share one L2 line: one returning 64-bit add for the two list bases and one fire-and-forget add for the
@@ -298,11 +312,6 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       unsigned long long* rc = reinterpret_cast<unsigned long long*>(b.reset_counts);
       list_old = atomicAdd(rc + 0, (unsigned long long)(unsigned)n_root | ((unsigned long long)(unsigned)n_hand << 32));
       atomicAdd(rc + 1, (unsigned long long)(unsigned)n_hand | ((unsigned long long)(unsigned)__popc(m_any) << 32));
-    }
-    if (rst) {
-      hand_row = b.hand_actor[env];
-      succ = b.successes[env];
-      tobj = b.true_objective[env];
     }
   }
   if (fold) kuka_fold_warp(sf, blockIdx.x, tid, s.fold);
@@ -363,26 +372,8 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       if (copy_actions) b.actions[base + f] = av;
     }
   };
-  if (m_any == 0u) {
-    if (!reset_only) element_pass(0u);
-    HA_TRACE_POINT(0, 6);                               // element pass stored
-  } else {
-    // tiles with a reset (uniform over the CTA): the re-randomisation FIRST -- it is the longest dependent chain of the launch --
-    // one warp per env (kuka_reset_env), envs of rank 0, 1, 2, 3 -> warps 0, 2, 3, 1 (warp 1 carries the forces, warp 3 the
-    // lists); then the element pass, which leaves the rows of the full resets alone, so the two need no ordering.
-    unsigned m = m_any;
-    int rank = 0;
-    while (m) {
-      const int e = __ffs(m) - 1;
-      m &= m - 1;
-      if (((0x1320 >> ((rank++ & 3) * 4)) & 3) == warp) kuka_reset_env(p, b, R, s, actions, env0 + e, lane, (m_rst >> e) & 1u, reset_only);
-    }
-    HA_TRACE_POINT(0, 10);                              // warp 0: its envs are done
-    if (!reset_only) element_pass(m_rst);
-    HA_TRACE_POINT(0, 6);                               // element pass stored
-  }
-
-  // ---------------- warp 1: random forces on the object body, random_force_prob of reset envs ----------------
+  // ---------------- warp 1: random forces on the object body, random_force_prob of reset envs.  FIRST: its inputs arrive with the
+  // masks, its generator pass then runs while the tile's vectors are still in flight ----------------
   if (warp == 1) {
     float prob = f_prob;
     if (rst) {                                           // (:1265-1269)
@@ -392,16 +383,19 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     if (do_force) {
       // Bernoulli test per env (lane = env), then the force row is decayed / kicked (:1401-1414)
       bool hit = false;
-      if (valid) hit = R.u(env, HA_KUKA_RND_FORCE_TEST) < prob;
+      if (valid) hit = R.ui(env, HA_KUKA_RND_FORCE_TEST) < prob;
       const unsigned m_hit = __ballot_sync(0xffffffffu, hit);
       const float decay = p.force_decay_pow, g0 = p.force_gain[0], g1 = p.force_gain[1];
+      // the three normals of a kicked env: its row of the parity table, or ONE counter block in fast mode (lane = env)
+      float nrm[3] = {0.f, 0.f, 0.f};
+      if (hit) R.nrm3(env, HA_KUKA_RND_FORCE_NORMAL, nrm);
       if (force_planes) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           if (valid) {
             float v = rst ? 0.f : f_v[c];                          // rb_forces[env_ids] = 0 (:1255)
             v *= decay;                                            // (:1402)
-            if (hit) v = R.nrm(env, HA_KUKA_RND_FORCE_NORMAL, c) * g0 * g1;   // (:1405-1410)
+            if (hit) v = nrm[c] * g0 * g1;                         // (:1405-1410)
             fplane[(size_t)c * n] = v;
           }
         }
@@ -409,10 +403,15 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
           const int idx = lane + 32 * i, e = idx / 3, c = idx - 3 * e;
+          float kick = 0.f;
+          if (m_hit != 0u) {                                       // (uniform) component c of env e lives in lane e
+            const float k0 = __shfl_sync(0xffffffffu, nrm[0], e & 31), k1 = __shfl_sync(0xffffffffu, nrm[1], e & 31), k2 = __shfl_sync(0xffffffffu, nrm[2], e & 31);
+            kick = c == 0 ? k0 : (c == 1 ? k1 : k2);
+          }
           if (e < nvalid) {
             float v = ((m_rst >> e) & 1u) ? 0.f : f_v[i];          // rb_forces[env_ids] = 0 (:1255)
             v *= decay;                                            // (:1402)
-            if ((m_hit >> e) & 1u) v = R.nrm(env0 + e, HA_KUKA_RND_FORCE_NORMAL, c) * g0 * g1;   // (:1405-1410)
+            if ((m_hit >> e) & 1u) v = kick * g0 * g1;             // (:1405-1410)
             b.rb_forces[frow + (size_t)e * fstride + c] = v;
           }
         }
@@ -427,8 +426,38 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     }
   }
 
-  // ---------------- tiles with a reset: what stays per tile (lane = env) -- accumulators, episode bookkeeping, actor-row lists ----------------
-  if (m_any) {
+  if (m_any == 0u) {
+    if (!reset_only) element_pass(0u);
+    HA_TRACE_POINT(0, 6);                               // element pass stored
+  } else {
+    // tiles with a reset (uniform over the CTA): the re-randomisation FIRST -- it is the longest dependent chain of the launch --
+    // two warps per env (kuka_reset_env: rotations / the rest; warp 1 also carries the forces, warp 3 the lists); then the element pass, which leaves the rows of the full resets alone, so the two need no ordering.
+    float succ = 0.f, tobj = 0.f;
+    int hand_row = 0;
+    if (warp == 3 && rst) {                              // bookkeeping inputs: in flight under the re-randomisation
+      hand_row = b.hand_actor[env];
+      succ = b.successes[env];
+      tobj = b.true_objective[env];
+    }
+    unsigned m = m_any;
+    int rank = 0;
+    while (m) {
+      const int e = __ffs(m) - 1;
+      m &= m - 1;
+#if HA_PRE_SPLIT_ROT
+      // env of even rank: warp 0 rotations, warp 2 the rest; odd rank: the other way round (warps 1 and 3 keep to their own parts)
+      const int w_rot = (rank & 1) ? 2 : 0, w_rest = (rank & 1) ? 0 : 2;
+      ++rank;
+      if (warp == w_rot || warp == w_rest) kuka_reset_env(p, b, R, s, actions, env0 + e, lane, (m_rst >> e) & 1u, reset_only, warp == w_rot ? 0 : 1);
+#else
+      // envs of rank 0, 1, 2, 3 -> warps 0, 2, 3, 1 (warp 1 also carries the forces, warp 3 the lists)
+      if (((0x1320 >> ((rank++ & 3) * 4)) & 3) == warp) kuka_reset_env(p, b, R, s, actions, env0 + e, lane, (m_rst >> e) & 1u, reset_only, 2);
+#endif
+    }
+    HA_TRACE_POINT(0, 10);                              // warp 0: its envs are done
+    if (!reset_only) element_pass(m_rst);
+    HA_TRACE_POINT(0, 6);                               // element pass stored
+    // what stays per tile (lane = env): accumulators, episode bookkeeping, actor-row lists
     if (warp == 2) {
       if (rst) {
 #pragma unroll
@@ -460,6 +489,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       HA_TRACE_POINT_IF(0, 8, tid == 96);
     }
   }
+
   HA_TRACE_POINT(0, 9);
 #ifdef HA_TRACE
   if (tid == 0 && blockIdx.x < kTraceMaxCtas) g_ha_trace[0][blockIdx.x].c[13] = m_any ? (m_rst ? 2 : 1) : 0;

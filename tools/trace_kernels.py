@@ -98,7 +98,7 @@ for k, label in ((0, "kuka_pre_kernel"), (1, "kuka_post_kernel")):
     for cname, m in cats:
         if m.sum() == 0:
             continue
-        print(f"   -- {cname}: {int(m.sum())} CTAs; time since CTA start [us at {a.ghz} GHz]")
+        print(f"   -- {cname}: {int(m.sum())} CTAs; time since CTA start [us at {a.ghz} GHz]; last warp's end (globaltimer) {pct((r['gt1'][m] - r['gt0'][m]) / 1e3)}")
         for i, nm in enumerate(names[k]):
             idx = i
             v = r["c"][m][:, idx]
