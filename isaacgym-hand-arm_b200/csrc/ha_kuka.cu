@@ -190,7 +190,7 @@ int ha_kuka_pre_step(const HaKukaParams* p, const HaKukaBuffers* b, const float*
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
   if (grid < ha::kNPart) { rc = ha_kuka_stats_finalize(p, b, stream); if (rc) return rc; }      // too few CTAs to fold a statistic each
   if (p->n_arms == 2) {
-    HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING, "two arms: only the regrasping reset path is built (subtask %d)", p->subtask);
+    HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING || p->subtask == HA_KUKA_REORIENTATION, "two arms: regrasping or reorientation (subtask %d)", p->subtask);
     return ha::check_cuda(ha::launch(ha::kuka2_pre_kernel, grid, ha::kThreads, 0, (cudaStream_t)stream, *p, *b, actions, ext_rand,
                                      (int)ha::kPreFull), "kuka2_pre_kernel launch");
   }
@@ -205,7 +205,7 @@ int ha_kuka_reset_idx(const HaKukaParams* p, const HaKukaBuffers* b, const float
   const int grid = (p->n_envs + ha::kEnvsPerCta - 1) / ha::kEnvsPerCta;
   if (grid < ha::kNPart) { rc = ha_kuka_stats_finalize(p, b, stream); if (rc) return rc; }      // too few CTAs to fold a statistic each
   if (p->n_arms == 2) {
-    HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING, "two arms: only the regrasping reset path is built (subtask %d)", p->subtask);
+    HA_REQUIRE(p->subtask == HA_KUKA_REGRASPING || p->subtask == HA_KUKA_REORIENTATION, "two arms: regrasping or reorientation (subtask %d)", p->subtask);
     ha::kuka2_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);
   } else {
     ha::kuka_pre_kernel<<<grid, ha::kThreads, 0, (cudaStream_t)stream>>>(*p, *b, nullptr, ext_rand, ha::kPreResetOnly);

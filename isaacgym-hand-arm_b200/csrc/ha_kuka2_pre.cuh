@@ -161,9 +161,14 @@ kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   // ---------------- warp 0: per-env scalar reset work, lane = env ----------------
   if (warp != 0 || m_any == 0u) return;
   const int n_any = __popc(m_any), n_rst = __popc(m_rst);
+  // reorientation (allegro_kuka_two_arms_reorientation.py:97-137): a new goal is a position + a rotation and leaves the object alone,
+  // so a goal-only reset contributes one actor row; regrasping (allegro_kuka_two_arms_regrasping.py:75-110) also puts the object back
+  const bool reorient = p.subtask == HA_KUKA_REORIENTATION;
+  const unsigned m_goal_only = m_any & ~m_rst;
+  const int rows_goal_only = reorient ? 1 : 2;
   int root_base = 0, hand_base = 0;
   if (lane == 0) {
-    root_base = atomicAdd(b.reset_counts + 0, 2 * n_any);
+    root_base = atomicAdd(b.reset_counts + 0, 2 * n_rst + rows_goal_only * __popc(m_goal_only));
     if (n_rst) { hand_base = atomicAdd(b.reset_counts + 1, 2 * n_rst); atomicAdd(b.reset_counts + 2, n_rst); }
     atomicAdd(b.reset_counts + 3, n_any);
   }
@@ -173,7 +178,7 @@ kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
   const int goal_row = p.root_regular ? env * p.actors_per_env + p.goal_slot : b.goal_actor[env];
   const int obj_row = p.root_regular ? env * p.actors_per_env + p.object_slot : b.object_actor[env];
   {
-    // _reset_target (regrasping): target position in the volume, shifted towards one of the arms
+    // _reset_target: target position in the volume, shifted towards one of the arms
     const int g = rst ? HA_KUKA2_RND_RESET_GOAL : HA_KUKA2_RND_GOAL;
     float coords[3];
 #pragma unroll
@@ -184,6 +189,14 @@ kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     float* rr = b.root_state + (size_t)goal_row * 13;
 #pragma unroll
     for (int c = 0; c < 3; ++c) { gs[c] = coords[c]; rr[c] = coords[c]; }
+    if (reorient) {                                        // get_random_quat (allegro_kuka_two_arms.py:1139-1150), goal row velocities = 0
+      const f4 gq = random_quat(R.u(env, g + 4), R.u(env, g + 5), R.u(env, g + 6));
+      gs[3] = gq.x; gs[4] = gq.y; gs[5] = gq.z; gs[6] = gq.w;
+      rr[3] = gq.x; rr[4] = gq.y; rr[5] = gq.z; rr[6] = gq.w;
+#pragma unroll
+      for (int c = 7; c < 13; ++c) rr[c] = 0.0f;
+    }
+    if (!reorient || rst) {
     // reset_object_pose: the draws of the last call win (goal block for a goal-only reset, the reset_idx block otherwise)
     const int ob = rst ? HA_KUKA2_RND_RESET_OBJ : g + 4;
     const float oside = 2.0f * R.u(env, ob) + -1.0f;
@@ -200,14 +213,15 @@ kuka2_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 8) = make_float4(-1.f, -1.f, -1.f, -1.f);
     *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 8 + 4) = make_float4(-1.f, -1.f, -1.f, -1.f);
     b.lifted_object[env] = 0;
+    }
     b.reset_goal_buf[env] = 0;
     b.near_goal_steps[env] = 0;
     b.closest_keypoint_max_dist[env] = -1.0f;
   }
   const unsigned below = (1u << lane) - 1u;
-  const int k = root_base + 2 * __popc(m_any & below);
-  b.root_reset_indices[k] = obj_row;
-  b.root_reset_indices[k + 1] = goal_row;
+  int k = root_base + 2 * __popc(m_rst & below) + rows_goal_only * __popc(m_goal_only & below);
+  if (rst || !reorient) b.root_reset_indices[k++] = obj_row;
+  b.root_reset_indices[k] = goal_row;
   if (rst) {
     b.random_force_prob[env] = force_prob_from(p, R.u(env, HA_KUKA2_RND_FORCE_PROB));
     b.progress_buf[env] = 0;

@@ -1,6 +1,6 @@
 """Task registry (subset of ``isaacgymenvs/tasks/__init__.py:66-123`` that lies on the hot path)."""
 from .allegro_kuka import (AllegroKukaBase, AllegroKukaRegrasping, AllegroKukaReorientation, AllegroKukaThrow,
-                           AllegroKukaTwoArmsRegrasping)
+                           AllegroKukaTwoArmsRegrasping, AllegroKukaTwoArmsReorientation)
 from .dextreme import AllegroHandDextremeADR
 from .hand import AllegroHand, ShadowHand
 
@@ -17,7 +17,7 @@ def resolve_allegro_kuka(cfg, *args, **kwargs):
 def resolve_allegro_kuka_two_arms(cfg, *args, **kwargs):
     """``tasks/__init__.py:80-90``."""
     subtask = cfg["env"]["subtask"]
-    table = {"regrasping": AllegroKukaTwoArmsRegrasping}
+    table = {"regrasping": AllegroKukaTwoArmsRegrasping, "reorientation": AllegroKukaTwoArmsReorientation}
     if subtask not in table:
         raise ValueError(f"Unknown subtask={subtask} in {list(table)}")
     return table[subtask](cfg, *args, **kwargs)

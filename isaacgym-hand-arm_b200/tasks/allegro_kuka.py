@@ -588,3 +588,13 @@ class AllegroKukaTwoArmsRegrasping(AllegroKukaReorientation):
 
     def _object_keypoint_offsets(self):
         return [[0, 0, 0]]
+
+
+class AllegroKukaTwoArmsReorientation(AllegroKukaTwoArmsRegrasping):
+    """allegro_kuka_two_arms_reorientation.py:18-158: the two-arm task with a goal POSE -- four keypoints (:25-31), 196-wide
+    observation, ``_reset_target`` draws a position, a side and a rotation and leaves the object where it is (:97-137); tolerance
+    curriculum and true objective as in the single-arm reorientation (:142-158)."""
+    subtask_id = C["HA_KUKA_REORIENTATION"]
+
+    def _object_keypoint_offsets(self):
+        return [[1, 1, 1], [1, 1, -1], [-1, -1, 1], [-1, -1, -1]]

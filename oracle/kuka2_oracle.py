@@ -1,4 +1,4 @@
-"""ORACLE (test infrastructure, not product code) -- CPU restatement of the two-arm AllegroKuka regrasping hot path.
+"""ORACLE (test infrastructure, not product code) -- CPU restatement of the two-arm AllegroKuka hot path (regrasping, reorientation).
 
 Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU legs may import this.
 
@@ -6,7 +6,9 @@ Restates, op for op in the reference's association order,
 
 * ``pre_step``  <- ``allegro_kuka_two_arms.py:1298-1351`` (pre_physics_step), ``:1215-1296`` (reset_idx), ``:1152-1157``
                    (reset_target_pose), ``:1159-1193`` (reset_object_pose, +-0.35 m side flip), ``:1139-1150`` (get_random_quat),
-                   ``allegro_kuka_two_arms_regrasping.py:75-110`` (_reset_target: +-0.75 m side flip, the object is reset too)
+                   ``allegro_kuka_two_arms_regrasping.py:75-110`` (_reset_target: +-0.75 m side flip, the object is reset too),
+                   ``allegro_kuka_two_arms_reorientation.py:97-137`` (_reset_target: side flip + random rotation, goal row velocities
+                   zeroed, the object stays; four keypoints ``:25-31``, 196-wide row)
 * ``post_step`` <- ``allegro_kuka_two_arms.py:1353-1370`` (post_physics_step), ``:939-1133`` (observations, 169-wide row),
                    ``:743-878`` (rewards: no finger coefficients, no lifted gate on the fingertip term, no hand / action penalties),
                    ``allegro_kuka_utils.py:128-158`` (true objective), ``vec_task.py:424`` (timeout_buf)
@@ -29,8 +31,9 @@ Tensor = torch.Tensor
 
 # per-env random table (include/handarm_b200.h, HA_KUKA2_RND_*)
 RND_GOAL, RND_RESET_GOAL, RND_RESET_OBJ, RND_FORCE_PROB, RND_FORCE_TEST, RND_FORCE_NORMAL, RND_DOF_POS = 0, 11, 22, 29, 30, 31, 34
-# inside a goal block: target position 3, target side 1, object side 1, object position 3, object rotation 3
-G_POS, G_SIDE, G_OBJ = 0, 3, 4
+# inside a goal block: target position 3, target side 1, then (regrasping) object side 1, object position 3, object rotation 3
+# or (reorientation) target rotation uvw 3
+G_POS, G_SIDE, G_OBJ, G_ROT = 0, 3, 4, 4
 # inside an object block: side 1, position 3, rotation 3
 O_SIDE, O_POS, O_ROT = 0, 1, 4
 
@@ -85,10 +88,15 @@ class Kuka2Consts:
     target_volume_extent: Tuple[Tuple[float, float], ...] = ((-0.2, 0.2), (-0.5, 0.5), (-0.12, 0.25))
     goal_x_ofs: float = 0.75
     obj_x_ofs: float = 1.1 / 2 - 0.2
+    subtask: str = "regrasping"               # or "reorientation" (allegro_kuka_two_arms_reorientation.py)
+
+    @property
+    def n_keypoints(self) -> int:
+        return 4 if self.subtask == "reorientation" else 1
 
     @property
     def obs_dim(self) -> int:
-        return 169                             # K = 1 (allegro_kuka_two_arms.py:176-211)
+        return 169 + 9 * (self.n_keypoints - 1)   # K = 1: 169, K = 4: 196 (allegro_kuka_two_arms.py:176-211)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -111,7 +119,8 @@ def _reset_object_pose(st, c: Kuka2Consts, ids: Tensor, blk: Tensor) -> None:
 
 
 def _reset_target_pose(st, c: Kuka2Consts, ids: Tensor, blk: Tensor) -> None:
-    """reset_target_pose (:1152-1157) with the regrasping ``_reset_target`` (allegro_kuka_two_arms_regrasping.py:75-110)."""
+    """reset_target_pose (:1152-1157) with the subtask's ``_reset_target`` (allegro_kuka_two_arms_regrasping.py:75-110,
+    allegro_kuka_two_arms_reorientation.py:97-137)."""
     org = torch.tensor(c.target_volume_origin, dtype=torch.float32)
     ext = torch.tensor(c.target_volume_extent, dtype=torch.float32)
     lo = org + ext[:, 0]
@@ -121,9 +130,15 @@ def _reset_target_pose(st, c: Kuka2Consts, ids: Tensor, blk: Tensor) -> None:
     x_pos = torch.where(left_right > 0, c.goal_x_ofs * torch.ones_like(left_right), -c.goal_x_ofs * torch.ones_like(left_right))
     coords[:, 0] += x_pos.squeeze(dim=1)
     st["goal_states"][ids, 0:3] = coords
-    st["root_state"][st["goal_object_indices"][ids], 0:3] = st["goal_states"][ids, 0:3]
-    _reset_object_pose(st, c, ids, blk[:, G_OBJ:G_OBJ + 7])
-    st["lifted_object"][ids] = False
+    rows = st["goal_object_indices"][ids]
+    st["root_state"][rows, 0:3] = st["goal_states"][ids, 0:3]
+    if c.subtask == "reorientation":          # allegro_kuka_two_arms_reorientation.py:125-134
+        st["goal_states"][ids, 3:7] = random_quat(blk[:, G_ROT:G_ROT + 3])
+        st["root_state"][rows, 3:7] = st["goal_states"][ids, 3:7]
+        st["root_state"][rows, 7:13] = 0.0
+    else:                                     # allegro_kuka_two_arms_regrasping.py:100-106
+        _reset_object_pose(st, c, ids, blk[:, G_OBJ:G_OBJ + 7])
+        st["lifted_object"][ids] = False
     st["reset_goal_buf"][ids] = 0
     st["near_goal_steps"][ids] = 0
     st["closest_keypoint_max_dist"][ids] = -1.0
@@ -137,12 +152,13 @@ def pre_step(st: Dict[str, Tensor], c: Kuka2Consts, actions: Tensor, rnd: Tensor
     ids = st["reset_buf"].nonzero(as_tuple=False).squeeze(-1)
     goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
     root_lists: List[Tensor] = []
+    moves_object = c.subtask != "reorientation"      # regrasping's _reset_target defers the object row as well
     _reset_target_pose(st, c, goal_ids, rnd[goal_ids, RND_GOAL:RND_GOAL + 11])
-    root_lists += [st["object_indices"][goal_ids], st["goal_object_indices"][goal_ids]]
+    root_lists += ([st["object_indices"][goal_ids]] if moves_object else []) + [st["goal_object_indices"][goal_ids]]
     hand_rows = torch.zeros(0, dtype=torch.int32)
     if len(ids) > 0:
         _reset_target_pose(st, c, ids, rnd[ids, RND_RESET_GOAL:RND_RESET_GOAL + 11])
-        root_lists += [st["object_indices"][ids], st["goal_object_indices"][ids]]
+        root_lists += ([st["object_indices"][ids]] if moves_object else []) + [st["goal_object_indices"][ids]]
         st["rb_forces"][ids] = 0.0
         _reset_object_pose(st, c, ids, rnd[ids, RND_RESET_OBJ:RND_RESET_OBJ + 7])
         hand_rows = st["arm_indices"][ids].to(torch.int32).flatten()
@@ -322,7 +338,12 @@ def make_state(n: int, seed: int, c: Kuka2Consts = Kuka2Consts(), fresh: bool = 
     st["goal_states"] = goal
     scales = torch.tensor([[1.0, 1.0, 1.0], [4.0, 0.75, 1.0], [1.0, 2.5, 1.0], [1.25, 0.66, 3.0], [0.5, 2.0, 1.5]])
     st["object_scales"] = scales[torch.arange(n) % len(scales)].contiguous()
-    st["object_keypoint_offsets"] = torch.zeros(n, 1, 3)                # regrasping: one keypoint at the object centre
+    if c.subtask == "reorientation":          # four corners (allegro_kuka_two_arms_reorientation.py:25-31), scaled (:692-700)
+        corners = torch.tensor([[1, 1, 1], [1, 1, -1], [-1, -1, 1], [-1, -1, -1]], dtype=torch.float32)
+        st["object_keypoint_offsets"] = (corners[None] * (st["object_scales"][:, None, :] * 0.05 * c.keypoint_scale / 2)).contiguous()
+        goal[:, 3:7] = unit(n)
+    else:
+        st["object_keypoint_offsets"] = torch.zeros(n, 1, 3)            # regrasping: one keypoint at the object centre
     root = torch.zeros(n, A, 13)
     root[..., 0:3] = torch.tensor([0.0, 0.0, 0.63]) + 0.15 * G(n, A, 3)
     root[..., 3:7] = unit(n, A)

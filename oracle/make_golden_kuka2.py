@@ -24,6 +24,8 @@ SCENARIOS = {
     "kuka2_regrasp_fresh": (24, 21, True, 2, {}),
     "kuka2_regrasp_mid": (40, 22, False, 3, {}),
     "kuka2_regrasp_hold1_noforce_ema": (24, 23, False, 2, dict(success_steps=1, force_scale=0.0, act_moving_average=0.4)),
+    "kuka2_reorient_fresh": (24, 24, True, 2, dict(subtask="reorientation")),
+    "kuka2_reorient_mid": (40, 25, False, 3, dict(subtask="reorientation")),
 }
 STATE_KEYS = ["root_state", "dof_state", "goal_states", "obs_buf", "rew_buf", "reset_buf", "reset_goal_buf", "progress_buf",
               "randomize_buf", "timeout_buf", "successes", "prev_episode_successes", "true_objective", "prev_episode_true_objective",
@@ -78,7 +80,8 @@ def main():
     if not rl.reference_available():
         raise SystemExit("the reference is not present here; golden vectors can only be generated in the build container")
     torch.manual_seed(0)
-    for name in SCENARIOS:
+    import sys
+    for name in (sys.argv[1:] or SCENARIOS):           # optional: only the named scenarios
         p = generate(name)
         print(f"{name}: {os.path.getsize(p) / 1024:.0f} KiB")
 

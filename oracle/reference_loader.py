@@ -105,6 +105,7 @@ def load_reference() -> Dict[str, types.ModuleType]:
     _loaded["vt"] = importlib.import_module("isaacgymenvs.tasks.base.vec_task")
     _loaded["ak2"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms")
     _loaded["ak2g"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms_regrasping")
+    _loaded["ak2r"] = importlib.import_module("isaacgymenvs.tasks.allegro_kuka.allegro_kuka_two_arms_reorientation")
     _loaded["sh"] = importlib.import_module("isaacgymenvs.tasks.shadow_hand")
     _loaded["ah"] = importlib.import_module("isaacgymenvs.tasks.allegro_hand")
     _loaded["adrv"] = importlib.import_module("isaacgymenvs.tasks.dextreme.adr_vec_task")
@@ -257,7 +258,7 @@ def scripted_randoms(queue: List[torch.Tensor]):
         return pop(shape)
 
     saved = {}
-    patched = [k for k in ("akb", "akr", "akg", "akt", "sh", "ah", "ak2", "ak2g", "dx") if k in mods and hasattr(mods[k], "torch_rand_float")]
+    patched = [k for k in ("akb", "akr", "akg", "akt", "sh", "ah", "ak2", "ak2g", "ak2r", "dx") if k in mods and hasattr(mods[k], "torch_rand_float")]
     for key in patched:
         saved[key] = mods[key].torch_rand_float
         mods[key].torch_rand_float = fake_rand_float
@@ -430,10 +431,13 @@ def harvest_hand(env, st: Dict[str, torch.Tensor], c) -> Dict[str, torch.Tensor]
 # AllegroKukaTwoArmsRegrasping (allegro_kuka_two_arms.py, allegro_kuka_two_arms_regrasping.py)
 # ---------------------------------------------------------------------------------------------
 def make_reference_kuka2(st: Dict[str, torch.Tensor], c) -> object:
-    """A reference ``AllegroKukaTwoArmsRegrasping`` instance aliasing the tensors of ``st`` (``oracle/kuka2_oracle.make_state``)."""
+    """A reference ``AllegroKukaTwoArmsRegrasping`` / ``AllegroKukaTwoArmsReorientation`` instance (``c.subtask``) aliasing the tensors
+    of ``st`` (``oracle/kuka2_oracle.make_state``)."""
     from .kuka2_oracle import EPISODE_TERMS
     mods = load_reference()
-    env = object.__new__(mods["ak2g"].AllegroKukaTwoArmsRegrasping)
+    cls = (mods["ak2r"].AllegroKukaTwoArmsReorientation if getattr(c, "subtask", "regrasping") == "reorientation"
+           else mods["ak2g"].AllegroKukaTwoArmsRegrasping)
+    env = object.__new__(cls)
     N = st["reset_buf"].shape[0]
     K = st["object_keypoint_offsets"].shape[1]
     env.__dict__.update(
@@ -495,7 +499,9 @@ def kuka2_random_queue(st: Dict[str, torch.Tensor], c, rnd: torch.Tensor) -> Lis
     goal_ids = st["reset_goal_buf"].nonzero(as_tuple=False).squeeze(-1)
     ids = st["reset_buf"].nonzero(as_tuple=False).squeeze(-1)
 
-    def goal_block(rows, base):       # _reset_target: position, side; reset_object_pose: side, position, rotation
+    def goal_block(rows, base):       # _reset_target: position, side; then reset_object_pose: side, position, rotation (regrasping)
+        if getattr(c, "subtask", "regrasping") == "reorientation":            # ... or get_random_quat: uvw (reorientation)
+            return [rnd[rows, base:base + 3], rnd[rows, base + 3:base + 4], rnd[rows, base + 4:base + 7]]
         return [rnd[rows, base:base + 3], rnd[rows, base + 3:base + 4], rnd[rows, base + 4:base + 5], rnd[rows, base + 5:base + 8],
                 rnd[rows, base + 8:base + 11]]
 

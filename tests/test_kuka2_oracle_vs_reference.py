@@ -1,5 +1,6 @@
-"""CPU, build container only: the two-arm regrasping restatement (``oracle/kuka2_oracle.py``) against the reference's real
-``AllegroKukaTwoArmsRegrasping`` class on identical inputs and identical random tables -- bit-exact."""
+"""CPU, build container only: the two-arm restatement (``oracle/kuka2_oracle.py``) against the reference's real
+``AllegroKukaTwoArmsRegrasping`` / ``AllegroKukaTwoArmsReorientation`` classes on identical inputs and identical random tables --
+bit-exact."""
 import pytest
 import torch
 
@@ -15,9 +16,10 @@ KEYS = ["obs_buf", "rew_buf", "reset_buf", "reset_goal_buf", "progress_buf", "ra
 
 
 @pytest.mark.parametrize("fresh", [False, True])
+@pytest.mark.parametrize("subtask", ["regrasping", "reorientation"])
 @pytest.mark.parametrize("over", [{}, dict(success_steps=1, force_scale=0.0, act_moving_average=0.4, success_tolerance=0.04)])
-def test_kuka2_restatement_is_bit_exact(fresh, over):
-    c = k2.Kuka2Consts(**over)
+def test_kuka2_restatement_is_bit_exact(fresh, over, subtask):
+    c = k2.Kuka2Consts(subtask=subtask, **over)
     n = 193
     st_ref = k2.make_state(n, 7, c, fresh=fresh)
     st = {k: v.clone() for k, v in st_ref.items()}
