@@ -16,9 +16,6 @@
 namespace ha {
 
 enum { kPreFull = 0, kPreResetOnly = 1 };
-#ifndef HA_PRE_SPLIT_ROT
-#define HA_PRE_SPLIT_ROT 0   // 1: two warps per reset env (measured slower in-step, kept for the trace tool)
-#endif
 
 struct KukaRand {
   const float* ext;   // [n_envs, stride] or nullptr
@@ -105,48 +102,47 @@ __device__ __forceinline__ float kuka_dof_target(float av, float pv, int d, floa
 
 // The whole re-randomisation of ONE env by ONE warp, one independent piece per lane: every piece starts with one Philox block (or
 // its row of the parity table), so a single pass of the generator serves all of them and the dependent chain of the reset -- which
-// bounds the launch, the tiles with a reset are its last ones to finish -- is one generator pass + one random_quat + a few stores.
+// bounds the launch, the tiles with a reset are its last ones to finish -- is one generator pass + half a random_quat + a few stores.
 //   lanes 0..22  DOF d: reset_idx DOF re-randomisation (:1271-1290), prev_targets = cur_targets = pos (:1289-1290), then the
 //                action pass on that position                                                          [full resets only]
 //   lane 23      goal position, reset_target_pose (:1191-1196) with the subtask's _reset_target:
-//                  reorientation  allegro_kuka_reorientation.py:104-128  position in the target volume (+ rotation: lane 24)
+//                  reorientation  allegro_kuka_reorientation.py:104-128  position in the target volume (+ rotation: lanes 25, 26)
 //                  regrasping     allegro_kuka_regrasping.py:76-100      position only (the goal ball keeps its rotation)
 //                  throw          allegro_kuka_throw.py:90-117           bucket left / right of the table (4 draws), goal = bucket + 5 cm
 //                an env that is in both sets is drawn twice by the reference and the reset_idx draw wins:
 //                `full` selects the RESET_GOAL slots
-//   lane 24      goal rotation (reorientation), goal row velocities = 0
-//   lane 25      object position, reset_object_pose (:1198-1224) and its tail (:1221-1224) + lifted_object
-//   lane 26      object rotation, object row velocities = 0
+//   lane 24      object position, reset_object_pose (:1198-1224) and its tail (:1221-1224) + lifted_object
+//   lanes 25,26  goal rotation (reorientation): get_random_quat (:1178-1189) has two independent halves, (x, w) = sqrt(1 - u) *
+//                (cos, sin)(2 pi v) and (y, z) = sqrt(u) * (sin, cos)(2 pi w) -- one lane each; goal row velocities = 0
+//   lanes 27,28  object rotation, same split; object row velocities = 0
 //                (regrasping / throw also put the object back on the table on a goal-only reset)
 __device__ __forceinline__ void kuka_reset_env(const HaKukaParams& p, const HaKukaBuffers& b, const KukaRand R, const KukaPreSmem& s,
                                             const float* __restrict__ actions, const int env, const int lane, const bool full,
-                                            const bool reset_only, const int part) {
+                                            const bool reset_only) {
   constexpr int D = 23;
-  enum { kGoalPos = D, kGoalRot = D + 1, kObjPos = D + 2, kObjRot = D + 3 };
   const bool reorient = p.subtask == HA_KUKA_REORIENTATION;
   const bool with_object = full || !reorient;
-  // lane roles without branches: special lanes r = 0..3 (goal position, goal rotation, object position, object rotation)
+  // lane roles without branches: special lanes r = 0..5
   static_assert(HA_KUKA_RND_GOAL_POS == 0 && HA_KUKA_RND_GOAL_ROT == 3 && HA_KUKA_RND_RESET_GOAL_POS == 6 && HA_KUKA_RND_RESET_GOAL_ROT == 9 &&
                 HA_KUKA_RND_OBJ_POS == 12 && HA_KUKA_RND_OBJ_ROT == 15, "slot arithmetic below");
   const int r = lane - D;
-  // part: 0 = the rotations (random_quat is the longest piece), 1 = everything else, 2 = both
-  const bool rot_lane = r == 1 || r == 3;
-  const bool active = (part == 2 || rot_lane == (part == 0)) && (lane < D ? full : ((unsigned)r < 4u && (r == 0 || (r == 1 ? reorient : with_object))));
-  const int slot = ((r < 2 && !full) ? 0 : 6) + 3 * r;
+  const bool rot_lane = r >= 2 && r < 6, goal_lane = r == 0 || r == 2 || r == 3;
+  const bool active = lane < D ? full : ((unsigned)r < 6u && (r == 0 || (goal_lane ? reorient : with_object)));
+  const int slot = goal_lane ? (full ? 6 : 0) + (rot_lane ? 3 : 0) : (rot_lane ? 15 : 12);
   if (!active) return;
   // the two loads of the chain go first (object_init_state is cold: a DRAM round trip)
   float act_v = 0.f, init0 = 0.f, init1 = 0.f, init2 = 0.f;
   if (lane < D) {
     if (!reset_only) act_v = __ldg(actions + (size_t)env * D + lane);
-  } else if (lane == kObjPos) {
+  } else if (r == 1) {
     const float* init = b.object_init_state + (size_t)env * 13;
     init0 = __ldg(init + 0); init1 = __ldg(init + 1); init2 = __ldg(init + 2);
   }
   float4 u;
   if (R.ext) {
-    const float* r = R.ext + (size_t)env * R.stride;
-    if (lane < D) u = make_float4(__ldg(r + HA_KUKA_RND_DOF_POS + lane), __ldg(r + HA_KUKA_RND_DOF_POS + D + lane), 0.f, 0.f);
-    else u = make_float4(__ldg(r + slot), __ldg(r + slot + 1), __ldg(r + slot + 2), __ldg(r + slot + 3));
+    const float* t = R.ext + (size_t)env * R.stride;
+    if (lane < D) u = make_float4(__ldg(t + HA_KUKA_RND_DOF_POS + lane), __ldg(t + HA_KUKA_RND_DOF_POS + D + lane), 0.f, 0.f);
+    else u = make_float4(__ldg(t + slot), __ldg(t + slot + 1), __ldg(t + slot + 2), __ldg(t + slot + 3));
   } else {
     u = R.rng.uniform4(env, lane < D ? 64 + lane : 32 + slot);   // DOF d: block 64 + d, (.x, .y) = (pos, vel) draws
   }
@@ -167,18 +163,24 @@ __device__ __forceinline__ void kuka_reset_env(const HaKukaParams& p, const HaKu
     HA_TRACE_POINT_IF(0, 3, threadIdx.x == 0);           // DOF rows stored
     return;
   }
-  const bool goal_lane = lane == kGoalPos || lane == kGoalRot;
   const RootRow rr = goal_lane ? root_row(p, b, kuka_goal_row(p, b, env), env, p.goal_slot)
                                : root_row(p, b, kuka_object_row(p, b, env), env, p.object_slot);
   float* gs = b.goal_states + (size_t)env * 13;
-  if (lane == kGoalRot || lane == kObjRot) {
-    const f4 q = random_quat(u.x, u.y, u.z);
-    rr.at(3) = q.x; rr.at(4) = q.y; rr.at(5) = q.z; rr.at(6) = q.w;
-#pragma unroll
-    for (int c = 7; c < 13; ++c) rr.at(c) = 0.0f;
-    if (lane == kGoalRot) { gs[3] = q.x; gs[4] = q.y; gs[5] = q.z; gs[6] = q.w; }
-    HA_TRACE_POINT_IF(0, 11, threadIdx.x == 24);         // rotations stored
-  } else if (lane == kGoalPos) {
+  if (rot_lane) {
+    // one half of get_random_quat (the arithmetic of random_quat, ha_device.cuh)
+    const float two_pi = 6.2831854820251465f;  // float32(2*pi)
+    const bool second = r & 1;                 // lanes 25 / 27: (x, w) from (u, v); lanes 26 / 28: (z, y) from (u, w)
+    const float sq = second ? sqrtf(u.x) : sqrtf(1.0f - u.x);
+    float sn, cs;
+    sincosf(two_pi * (second ? u.z : u.y), &sn, &cs);
+    const float q_cos = sq * cs, q_sin = sq * sn;          // (x, w) or (z, y)
+    const int i_cos = second ? 5 : 3, i_sin = second ? 4 : 6;
+    rr.at(i_cos) = q_cos; rr.at(i_sin) = q_sin;
+    const int v0 = second ? 10 : 7;
+    rr.at(v0) = 0.0f; rr.at(v0 + 1) = 0.0f; rr.at(v0 + 2) = 0.0f;
+    if (goal_lane) { gs[i_cos] = q_cos; gs[i_sin] = q_sin; }
+    HA_TRACE_POINT_IF(0, 11, threadIdx.x == 25);         // rotations stored
+  } else if (r == 0) {
     float x, y, z, gz;
     if (p.subtask == HA_KUKA_THROW) {
       // torch_rand_float(lo, hi) = (hi - lo) * u + lo
@@ -200,8 +202,8 @@ __device__ __forceinline__ void kuka_reset_env(const HaKukaParams& p, const HaKu
     b.reset_goal_buf[env] = 0;
     b.near_goal_steps[env] = 0;
     b.closest_keypoint_max_dist[env] = -1.0f;
-  } else {   // kObjPos; torch_rand_float(-1, 1) = 2 u - 1
-    HA_TRACE_POINT_IF(0, 12, threadIdx.x == 25 && init0 != 123456.f);   // object_init_state arrived
+  } else {   // r == 1: object position; torch_rand_float(-1, 1) = 2 u - 1
+    HA_TRACE_POINT_IF(0, 12, threadIdx.x == 24 && init0 != 123456.f);   // object_init_state arrived
     rr.at(0) = init0 + p.reset_pos_noise[0] * (2.0f * u.x + -1.0f);
     rr.at(1) = init1 + p.reset_pos_noise[1] * (2.0f * u.y + -1.0f);
     rr.at(2) = init2 + p.reset_pos_noise[2] * (2.0f * u.z + -1.0f);
@@ -426,12 +428,57 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     }
   }
 
+  // The same pass by warps 1..3 only (a tile with ONE reset env: warp 0 carries that env's chain and nothing else): 96 threads x 2
+  // vectors cover the 184 of a tile; the vectors come back from L1 / L2 under the new thread mapping.
+  auto element_pass_by3 = [&](const unsigned skip) {
+    constexpr int kT3 = kThreads - 32;
+    static_assert(2 * kT3 >= kVecPerTile, "two vectors per thread must cover the tile");
+    const int t3 = tid - 32;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int q = t3 + i * kT3;
+      if (q >= nvec) continue;
+      const float4 av = __ldg(reinterpret_cast<const float4*>(actions + base) + q);
+      const float4 pv = *(reinterpret_cast<const float4*>(b.prev_targets + base) + q);
+      const int f0 = 4 * q;
+      const int e0 = f0 / D;
+      const int d0 = f0 - e0 * D;
+      int d = d0;
+      float ov[4];
+      ov[0] = kuka_dof_target(av.x, pv.x, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
+      ov[1] = kuka_dof_target(av.y, pv.y, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
+      ov[2] = kuka_dof_target(av.z, pv.z, d, s.lim[d], ema, one_m_ema, gain); d = (d + 1 == D) ? 0 : d + 1;
+      ov[3] = kuka_dof_target(av.w, pv.w, d, s.lim[d], ema, one_m_ema, gain);
+      int e = e0, dd = d0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (!((skip >> e) & 1u)) {
+          b.cur_targets[base + f0 + j] = ov[j];
+          b.prev_targets[base + f0 + j] = ov[j];
+        }
+        if (++dd == D) { dd = 0; ++e; }
+      }
+      if (copy_actions) *(reinterpret_cast<float4*>(b.actions + base) + q) = av;
+    }
+    const int f = (nvec << 2) + t3;                      // ragged last tile: up to 3 trailing elements
+    if (f < total) {
+      const int e = f / D, d = f - e * D;
+      const float av = __ldg(actions + base + f);
+      if (!((skip >> e) & 1u)) {
+        const float x = kuka_dof_target(av, b.prev_targets[base + f], d, s.lim[d], ema, one_m_ema, gain);
+        b.cur_targets[base + f] = x;
+        b.prev_targets[base + f] = x;
+      }
+      if (copy_actions) b.actions[base + f] = av;
+    }
+  };
   if (m_any == 0u) {
     if (!reset_only) element_pass(0u);
     HA_TRACE_POINT(0, 6);                               // element pass stored
   } else {
     // tiles with a reset (uniform over the CTA): the re-randomisation FIRST -- it is the longest dependent chain of the launch --
-    // two warps per env (kuka_reset_env: rotations / the rest; warp 1 also carries the forces, warp 3 the lists); then the element pass, which leaves the rows of the full resets alone, so the two need no ordering.
+    // one warp per env (kuka_reset_env); then the element pass, which leaves the rows of the full resets alone, so the two need no
+    // ordering.
     float succ = 0.f, tobj = 0.f;
     int hand_row = 0;
     if (warp == 3 && rst) {                              // bookkeeping inputs: in flight under the re-randomisation
@@ -444,18 +491,14 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     while (m) {
       const int e = __ffs(m) - 1;
       m &= m - 1;
-#if HA_PRE_SPLIT_ROT
-      // env of even rank: warp 0 rotations, warp 2 the rest; odd rank: the other way round (warps 1 and 3 keep to their own parts)
-      const int w_rot = (rank & 1) ? 2 : 0, w_rest = (rank & 1) ? 0 : 2;
-      ++rank;
-      if (warp == w_rot || warp == w_rest) kuka_reset_env(p, b, R, s, actions, env0 + e, lane, (m_rst >> e) & 1u, reset_only, warp == w_rot ? 0 : 1);
-#else
       // envs of rank 0, 1, 2, 3 -> warps 0, 2, 3, 1 (warp 1 also carries the forces, warp 3 the lists)
-      if (((0x1320 >> ((rank++ & 3) * 4)) & 3) == warp) kuka_reset_env(p, b, R, s, actions, env0 + e, lane, (m_rst >> e) & 1u, reset_only, 2);
-#endif
+      if (((0x1320 >> ((rank++ & 3) * 4)) & 3) == warp) kuka_reset_env(p, b, R, s, actions, env0 + e, lane, (m_rst >> e) & 1u, reset_only);
     }
     HA_TRACE_POINT(0, 10);                              // warp 0: its envs are done
-    if (!reset_only) element_pass(m_rst);
+    if (!reset_only) {
+      if ((m_any & (m_any - 1u)) != 0u) element_pass(m_rst);          // several envs: every warp keeps its share
+      else if (warp != 0) element_pass_by3(m_rst);                     // one env (warp 0's): the other three warps take the whole pass
+    }
     HA_TRACE_POINT(0, 6);                               // element pass stored
     // what stays per tile (lane = env): accumulators, episode bookkeeping, actor-row lists
     if (warp == 2) {

@@ -73,7 +73,7 @@ def pct(x):
 
 
 names = {0: ["start", "loads issued, masks in", "ballots", "reset w0: DOF rows stored", "reset w0: draws in hand", "barrier", "element pass stored", "reset w3: bookkeeping stored", "reset w3: lists written", "end",
-             "reset w0: its envs done", "reset w0: rotations stored", "reset w0: object_init_state arrived"],
+             "reset w0: its envs done", "reset w0: rotation half stored", "reset w0: object_init_state arrived"],
          1: ["start", "prologue+issue", "t0 B1 inputs", "t0 role0 tips done", "t0 role1 keypoints done", "t0 role2 dofs done", "t0 role3 copies done",
              "t0 B2", "t0 reward chain done", "t0 B3", "t1 B1 inputs", "t1 B2", "t1 B3", "end"]}
 spans = {}
