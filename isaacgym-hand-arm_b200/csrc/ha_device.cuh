@@ -148,10 +148,12 @@ __device__ __forceinline__ float warp_sum(float v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// Warp reductions on the redux unit (one instruction per 32-bit word instead of five dependent shuffle + op rounds: at the end of a
+// persistent CTA these sit on the launch's critical path).  Maximum of floats through an order-preserving unsigned key (no NaNs here).
 __device__ __forceinline__ float warp_max(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
+  const unsigned b = __float_as_uint(v);
+  const unsigned k = __reduce_max_sync(0xffffffffu, (b & 0x80000000u) ? ~b : (b | 0x80000000u));
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
 __device__ __forceinline__ float ldg(const float* p) { return __ldg(p); }
@@ -196,16 +198,16 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 
+// 64-bit sum (two's complement, exact mod 2^64): four 16-bit limbs, each limb sum of 32 lanes fits 21 bits
 __device__ __forceinline__ long long warp_sum_ll(long long v) {
-#pragma unroll
-  for (int ofs = 16; ofs > 0; ofs >>= 1) v += __shfl_xor_sync(0xffffffffu, v, ofs);
-  return v;
+  const unsigned long long u = (unsigned long long)v;
+  const unsigned long long s0 = __reduce_add_sync(0xffffffffu, (unsigned)(u & 0xffffu));
+  const unsigned long long s1 = __reduce_add_sync(0xffffffffu, (unsigned)((u >> 16) & 0xffffu));
+  const unsigned long long s2 = __reduce_add_sync(0xffffffffu, (unsigned)((u >> 32) & 0xffffu));
+  const unsigned long long s3 = __reduce_add_sync(0xffffffffu, (unsigned)(u >> 48));
+  return (long long)(s0 + (s1 << 16) + (s2 << 32) + (s3 << 48));
 }
-__device__ __forceinline__ int warp_sum_i(int v) {
-#pragma unroll
-  for (int ofs = 16; ofs > 0; ofs >>= 1) v += __shfl_xor_sync(0xffffffffu, v, ofs);
-  return v;
-}
+__device__ __forceinline__ int warp_sum_i(int v) { return __reduce_add_sync(0xffffffffu, v); }
 
 
 // a / b with r = RN(1 / b) precomputed on the host: one Newton-style residual step (Markstein) gives the

@@ -283,16 +283,14 @@ hand_post_kernel(const __grid_constant__ HaHandParams p, const __grid_constant__
   const int s_n = warp_sum_i(a_n), s_rs = warp_sum_i(a_resets), s_gl = warp_sum_i(a_goal), s_to = warp_sum_i(a_timeouts);
   long long* accum = reinterpret_cast<long long*>(b.stat_accum);
   long long val = 0;
-  switch (lane) {
-    case HA_HAND_STAT_N: val = s_n; break;
-    case HA_HAND_STAT_SUM_REWARD: val = s_rew; break;
-    case HA_HAND_STAT_SUM_RESETS: val = s_rs; break;
-    case HA_HAND_STAT_SUM_FINISHED_SUCCESSES: val = s_fin; break;
-    case HA_HAND_STAT_SUM_GOAL_RESETS: val = s_gl; break;
-    case HA_HAND_STAT_SUM_SUCCESSES: val = s_succ; break;
-    case HA_HAND_STAT_SUM_TIMEOUTS: val = s_to; break;
-    default: break;
-  }
+  // selects, not a switch: a switch on the lane index is a divergent jump table (one serial pass per case)
+  val = lane == HA_HAND_STAT_N ? (long long)(s_n) : val;
+  val = lane == HA_HAND_STAT_SUM_REWARD ? (long long)(s_rew) : val;
+  val = lane == HA_HAND_STAT_SUM_RESETS ? (long long)(s_rs) : val;
+  val = lane == HA_HAND_STAT_SUM_FINISHED_SUCCESSES ? (long long)(s_fin) : val;
+  val = lane == HA_HAND_STAT_SUM_GOAL_RESETS ? (long long)(s_gl) : val;
+  val = lane == HA_HAND_STAT_SUM_SUCCESSES ? (long long)(s_succ) : val;
+  val = lane == HA_HAND_STAT_SUM_TIMEOUTS ? (long long)(s_to) : val;
   if (gridDim.x <= HA_HAND_STAT_SLOTS) {                                        // deferred: see hand_fold_*
     if (lane < kHandNPart) accum[(size_t)lane * HA_HAND_STAT_SLOTS + blockIdx.x] = val;
     if (blockIdx.x == 0 && lane == 0) {
