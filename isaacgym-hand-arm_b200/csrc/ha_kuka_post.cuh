@@ -125,6 +125,7 @@ struct KukaPostSmem {
   KukaPostStage<K> st[NS];
   float obs[kTile * kObs];            // row-major tile, leaves as one contiguous run
   float xch[8 * kTile];               // [q][e]: cur[0..3], kp_max, sum|vel| arm, sum|vel| hand
+  float terms[HA_KUKA_N_EPISODE_TERMS * kTile];   // [k][e]: this step's reward terms, state warp -> the warps that keep the per-episode sums
   unsigned long long mbar[2];         // transaction barriers of the bulk-copied stages
   const float* rowp[13 + 13 + kT1 * 7];   // component planes: source of staged row r at env 0 (palm 0..12, object 13..25, tips 26..53)
 };
@@ -409,7 +410,6 @@ struct KukaPostEnvState {
   int near;
   unsigned char lifted;
   float4 ctip, coef;
-  float acc[HA_KUKA_N_EPISODE_TERMS];
 };
 
 template <int OBS, int REW_SLOT>
@@ -431,9 +431,6 @@ __device__ __forceinline__ void kuka_post_load_env(const HaKukaParams& p, const 
   if (mode == kPostObserveOnly) {
     r.old_rew_obs = b.obs_buf[(size_t)env * OBS + REW_SLOT];
   } else {
-    const int n = p.n_envs;
-#pragma unroll
-    for (int k = 0; k < HA_KUKA_N_EPISODE_TERMS; ++k) r.acc[k] = b.rewards_episode[(size_t)k * n + env];
     if (b.randomize_buf) r.randomize = b.randomize_buf[env];
   }
 }
@@ -506,6 +503,18 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     }
     KukaPostEnvState r;
     if (warp == 3) kuka_post_load_env<OBS, L.reward>(p, b, env, mode, r);
+    // per-episode reward sums (rewards_episode[k] += term, :871-874, :923-926): kept by roles 0 and 1, half of the terms each -- their loads
+    // fly with the tile, the sums leave after B3 with the terms the state warp parked in shared memory (its B2 -> B3 chain is the
+    // CTA's critical path; this takes 32 memory instructions and twelve registers out of it)
+    constexpr int kHalfTerms = HA_KUKA_N_EPISODE_TERMS / 2;
+    static_assert(HA_KUKA_N_EPISODE_TERMS == 2 * kHalfTerms, "two roles x half of the terms");
+    float accv[kHalfTerms];
+#pragma unroll
+    for (int j = 0; j < kHalfTerms; ++j) accv[j] = 0.f;
+    if (warp < 2 && mode != kPostObserveOnly) {
+#pragma unroll
+      for (int j = 0; j < kHalfTerms; ++j) accv[j] = b.rewards_episode[(size_t)(kHalfTerms * warp + j) * n + env];
+    }
     if (HA_BULK_STORE && tid == 0) bulk_wait_read0();   // the previous tile's bulk store has read the obs tile
     cp_async_wait<(NS == 2 && !HA_LATE_PREFETCH) ? 1 : 0>();
     if (kuka_post_bulk_tile(SOA, n, env0)) mbar_wait(&sm.mbar[NS == 2 ? (it & 1) : 0], NS == 2 ? (it >> 1) & 1 : it & 1);
@@ -729,14 +738,9 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
           b.closest_keypoint_max_dist[env] = ckp;
           b.furthest_hand_dist[env] = furthest;
           *reinterpret_cast<float4*>(b.closest_fingertip_dist + (size_t)env * 4) = make_float4(ctip[0], ctip[1], ctip[2], ctip[3]);
-          // rewards_episode[k] += term (:871-874, :923-926)
+          // the terms of this step: parked for the other roles (rewards_episode, episode_cumulative; after B3)
 #pragma unroll
-          for (int k = 0; k < HA_KUKA_N_EPISODE_TERMS; ++k) b.rewards_episode[(size_t)k * n + env] = r.acc[k] + t[k];
-          // episode_cumulative[k] = term, in the reference's list order (:912-921)
-          constexpr int cum_src[HA_KUKA_N_STEP_TERMS] = {HA_KUKA_FINGERTIP_DELTA, HA_KUKA_HAND_DELTA, HA_KUKA_LIFTING, HA_KUKA_LIFT_BONUS,
-                                                         HA_KUKA_KEYPOINT, HA_KUKA_KUKA_PENALTY, HA_KUKA_ALLEGRO_PENALTY, HA_KUKA_BONUS};
-#pragma unroll
-          for (int k = 0; k < HA_KUKA_N_STEP_TERMS; ++k) b.episode_cumulative[(size_t)k * n + env] = t[cum_src[k]];
+          for (int k = 0; k < HA_KUKA_N_EPISODE_TERMS; ++k) sm.terms[k * kTile + lane] = t[k];
           // statistics partials (fixed point: order-independent sums)
           acc.rew += __float2ll_rn(reward * stat_scale(HA_KUKA_STAT_SUM_REWARD));
           acc.prev_ep += __float2ll_rn(r.prev_ep * stat_scale(HA_KUKA_STAT_SUM_PREV_EP_SUCCESSES));
@@ -752,6 +756,17 @@ kuka_post_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__
     HA_TRACE_POINT_IF(1, 8, it == 0 && warp == 3 && lane == 0);   // reward chain of tile 0 done
     __syncthreads();                                    // B3: the observation tile is complete
     HA_TRACE_POINT(1, it == 0 ? 9 : (it == 1 ? 12 : 13));
+    if (mode != kPostObserveOnly && valid) {
+      if (warp < 2) {                                   // rewards_episode[k] += term (:871-874, :923-926)
+#pragma unroll
+        for (int j = 0; j < kHalfTerms; ++j) b.rewards_episode[(size_t)(kHalfTerms * warp + j) * n + env] = accv[j] + sm.terms[(kHalfTerms * warp + j) * kTile + lane];
+      } else if (warp == 2) {                           // episode_cumulative[k] = term, in the reference's list order (:912-921)
+        constexpr int cum_src[HA_KUKA_N_STEP_TERMS] = {HA_KUKA_FINGERTIP_DELTA, HA_KUKA_HAND_DELTA, HA_KUKA_LIFTING, HA_KUKA_LIFT_BONUS,
+                                                       HA_KUKA_KEYPOINT, HA_KUKA_KUKA_PENALTY, HA_KUKA_ALLEGRO_PENALTY, HA_KUKA_BONUS};
+#pragma unroll
+        for (int k = 0; k < HA_KUKA_N_STEP_TERMS; ++k) b.episode_cumulative[(size_t)k * n + env] = sm.terms[cum_src[k] * kTile + lane];
+      }
+    }
     if (bulk_store) {
       if (tid == 0) {                                   // the whole [32, OBS] tile leaves as one bulk copy
         bulk_s2g(b.obs_buf + (size_t)env0 * OBS, sm.obs, kTile * OBS * 4);
