@@ -79,7 +79,13 @@ class RLGPUAlgoObserver:
     def after_init(self, algo):
         self.algo = algo
         self.writer = algo.writer
-        self.games_to_track = getattr(algo, "games_to_track", self.games_to_track)
+        tracked = getattr(algo, "games_to_track", self.games_to_track)
+        if self._keys is not None and tracked != self.games_to_track:
+            # the device rings were sized by an earlier process_infos: a different window needs new rings (the deques of the
+            # reference are created lazily with algo.games_to_track, :168)
+            self._keys = None
+            self._logged = 0
+        self.games_to_track = tracked
 
     # ---- device state ---------------------------------------------------------------------------------------------------
     def _setup(self, terms: Dict[str, torch.Tensor]):
@@ -159,16 +165,26 @@ class RLGPUAlgoObserver:
                 self.writer.add_scalar("Episode/" + key, torch.mean(torch.cat(vals)), epoch_num)
             self.ep_infos.clear()
         appended = self.episodes_finished()
-        if appended > getattr(self, "_logged", 0):            # new finished episodes since the last print (:197)
+        if appended > getattr(self, "_logged", 0):            # the reference sets the flag per finished env in process_infos (:164);
+            self.new_finished_episodes = True                 # here the finished envs are counted on the device and read once per print
             self._logged = appended
+        if self.new_finished_episodes:                        # log these if and only if we have new finished episodes (:196-202)
             for key, (mean, mn, mx) in self.episode_cumulative_summary().items():
                 self.writer.add_scalar(f"episode_cumulative/{key}", mean, frame)
                 self.writer.add_scalar(f"episode_cumulative_min/{key}_min", mn, frame)
                 self.writer.add_scalar(f"episode_cumulative_max/{key}_max", mx, frame)
+            self.new_finished_episodes = False
         for k, v in self.direct_info.items():
             self.writer.add_scalar(f"{k}/frame", v, frame)
             self.writer.add_scalar(f"{k}/iter", v, epoch_num)
             self.writer.add_scalar(f"{k}/time", v, total_time)
+        # custom data of the env (:206-214)
+        env = getattr(getattr(self.algo, "vec_env", None), "env", None)
+        if env is not None and hasattr(env, "log_data"):
+            for k, v in env.log_data.items():
+                self.writer.add_scalar(k + "/frame", v, frame)
+                self.writer.add_scalar(k + "/iter", v, epoch_num)
+                self.writer.add_scalar(k + "/time", v, total_time)
 
 
 def _flatten_dict(d, prefix="", separator="/"):

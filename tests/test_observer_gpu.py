@@ -81,3 +81,46 @@ def test_observer_on_task_extras():
     for k in want.episode_cumulative:
         assert torch.equal(obs.episode_cumulative[k].cpu(), want.episode_cumulative[k])
     assert obs.episodes_finished() == n_done
+
+
+def test_observer_print_hooks():
+    """after_print_stats: episode_cumulative scalars appear if and only if episodes finished since the last print (the reference's
+    new_finished_episodes flag, rlgames_utils.py:196-202), the env's log_data is flushed (:206-214), and a games_to_track that
+    after_init learns later re-sizes the device rings."""
+    from types import SimpleNamespace
+    from handarm_b200.rlgames_adapter import RLGPUAlgoObserver
+
+    class Writer:
+        def __init__(self):
+            self.rows = []
+
+        def add_scalar(self, tag, value, step):
+            self.rows.append((tag, float(value), step))
+
+    n, k = 256, 3
+    env = SimpleNamespace(log_data={"custom/x": 1.5})
+    algo = SimpleNamespace(writer=Writer(), games_to_track=7, vec_env=SimpleNamespace(env=env), device="cuda:0")
+    obs = RLGPUAlgoObserver(games_to_track=100)
+    terms = {f"t{i}": torch.full((n,), float(i + 1), device="cuda") for i in range(k)}
+    dones = torch.zeros(n, dtype=torch.int64, device="cuda")
+    obs.process_infos({"episode_cumulative": terms, "dones": dones}, None)       # sized with the constructor's window ...
+    obs.after_init(algo)                                                         # ... then rl_games tells the real one
+    assert obs.games_to_track == 7
+    obs.process_infos({"episode_cumulative": terms, "dones": dones}, None)
+    assert obs.ring.shape == (k, 7)
+    obs.after_print_stats(10, 1, 0.5)
+    tags = [t for t, _, _ in algo.writer.rows]
+    assert not any(t.startswith("episode_cumulative") for t in tags), "nothing finished yet"
+    assert "custom/x/frame" in tags and "custom/x/iter" in tags and "custom/x/time" in tags
+    algo.writer.rows.clear()
+    dones[5] = 1
+    obs.process_infos({"episode_cumulative": terms, "dones": dones}, None)
+    obs.after_print_stats(20, 2, 1.0)
+    got = {t: v for t, v, _ in algo.writer.rows}
+    assert got["episode_cumulative/t0"] == 2.0 and got["episode_cumulative_max/t2_max"] == 6.0      # two steps summed since the re-size
+    assert obs.new_finished_episodes is False
+    algo.writer.rows.clear()
+    dones.zero_()
+    obs.process_infos({"episode_cumulative": terms, "dones": dones}, None)
+    obs.after_print_stats(30, 3, 1.5)
+    assert not any(t.startswith("episode_cumulative") for t, _, _ in algo.writer.rows), "no new finished episodes since the last print"
