@@ -142,6 +142,13 @@ class AllegroKukaBase(VecTask):
         super().__init__(cfg, rl_device, sim_device, graphics_device_id, headless, virtual_screen_capture, force_render)
         self._allocate_task_state()
         self._build_abi()
+        # recorded initial states (allegro_kuka_base.py:98-101, :545-546; the two-arm base has no such option)
+        self.should_load_initial_states = bool(env.get("loadInitialStates", False)) and self.num_arms == 1
+        self.load_states_filename = env.get("loadStatesFile", "")
+        self.initial_root_state_tensors = self.initial_dof_state_tensors = None
+        self.initial_state_idx = self.num_initial_states = 0
+        if self.should_load_initial_states:
+            self.load_initial_states()
 
     # ---- subtask interface (allegro_kuka_base.py:396-470) ---------------------------------------
     def _object_keypoint_offsets(self):
@@ -444,6 +451,42 @@ class AllegroKukaBase(VecTask):
         self._params.use_fast_rng = 1
         return ctypes.c_void_p(0)
 
+    # ---- loadInitialStates (allegro_kuka_base.py:1545-1592 file, :1292-1313 use; off in the shipped configs) ----
+    def load_initial_states(self):
+        from .. import state_io
+        root, dof = state_io.load_initial_states(self.load_states_filename)
+        self.initial_root_state_tensors = root.to(self.device, torch.float32)
+        self.initial_dof_state_tensors = dof.to(self.device, torch.float32)
+        self.num_initial_states = int(root.shape[0])
+        print(f"{self.num_initial_states} states loaded from file {self.load_states_filename}!")
+
+    def _initial_state_ids(self) -> Optional[torch.Tensor]:
+        """The reset envs in ascending order, read BEFORE the kernel consumes the mask.  The recorded states are handed out
+        consecutively in that order, which needs the ids on the host exactly like the reference's ``nonzero()``: the one place
+        where this option costs a sync (and why it cannot be captured in a CUDA graph)."""
+        if not self.should_load_initial_states:
+            return None
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("loadInitialStates reads the reset ids on the host (allegro_kuka_base.py:1292-1313): not capturable")
+        return self.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+
+    def _apply_initial_states(self, env_ids: torch.Tensor) -> None:
+        """allegro_kuka_base.py:1292-1313, after the kernel's re-randomisation: every DOF state and the object's root row of the reset
+        envs come from the file; prev / cur targets keep the re-randomised position."""
+        k = int(env_ids.numel())
+        if k == 0:
+            return
+        if k > self.num_initial_states:
+            print(f"Not enough initial states to load {k}/{self.num_initial_states}...")
+            return
+        if self.initial_state_idx + k > self.num_initial_states:
+            self.initial_state_idx = 0
+        i0 = self.initial_state_idx
+        self.sim.dof_state.view(self.num_envs, -1, 2)[env_ids] = self.initial_dof_state_tensors[i0:i0 + k]
+        slot = self.sim.layout.object_actor                # cube_object_idx = self.object_indices[0] (:1308)
+        self.sim.root_rows()[env_ids, slot] = self.initial_root_state_tensors[i0:i0 + k, slot]
+        self.initial_state_idx += k
+
     def pre_physics_step(self, actions: torch.Tensor):
         """allegro_kuka_base.py:1355-1424 as one kernel (masks consumed in place, no nonzero()/unique())."""
         self._require_engine()
@@ -451,8 +494,11 @@ class AllegroKukaBase(VecTask):
             actions = actions.float().contiguous()
         self._rebind_sim_state()
         rnd = self._rand_ptr()
+        load_ids = self._initial_state_ids()
         _lib.check(self._lib.ha_kuka_pre_step(ctypes.byref(self._params), ctypes.byref(self._buffers), ctypes.c_void_p(actions.data_ptr()),
                                               rnd, self._stream()))
+        if load_ids is not None:
+            self._apply_initial_states(load_ids)
         self._stats_pending = False       # the pre launch folded the previous step's statistic slots
         # what the reference hands to PhysX after this point (recorded, not executed):
         sim = self.sim
@@ -527,6 +573,8 @@ class AllegroKukaBase(VecTask):
         self.reset_buf[env_ids] = 1
         self._rebind_sim_state()
         _lib.check(self._lib.ha_kuka_reset_idx(ctypes.byref(self._params), ctypes.byref(self._buffers), self._rand_ptr(), self._stream()))
+        if self.should_load_initial_states:
+            self._apply_initial_states(torch.as_tensor(env_ids, device=self.device).reshape(-1))      # in the caller's order, as the reference
         self._stats_pending = False
         saved[env_ids] = 0
         self.reset_buf.copy_(saved)

@@ -194,7 +194,24 @@ def _reset_target(st: Dict[str, Tensor], c: KukaConsts, ids: Tensor, rnd: Tensor
     st["closest_keypoint_max_dist"][ids] = -1.0
 
 
-def pre_step(st: Dict[str, Tensor], c: KukaConsts, actions: Tensor, rnd: Tensor) -> Dict[str, Tensor]:
+def load_initial_states(st: Dict[str, Tensor], ids: Tensor, initial: Dict[str, object]) -> None:
+    """The ``should_load_initial_states`` branch of ``reset_idx`` (allegro_kuka_base.py:1292-1313): the reset envs, in ascending
+    order, take consecutive recorded states -- every DOF state and the object's root row; the targets keep the re-randomised
+    position.  ``initial`` = {"root": [T, actors, 13], "dof": [T, dofs_per_env, 2], "idx": cursor (mutated)}."""
+    T, k = initial["root"].shape[0], len(ids)
+    if k > T:
+        return                                        # "Not enough initial states to load"
+    if initial["idx"] + k > T:
+        initial["idx"] = 0
+    i0 = initial["idx"]
+    st["dof_state"][ids] = initial["dof"][i0:i0 + k].clone()
+    N = st["reset_buf"].shape[0]
+    slot = int(st["object_indices"][0])               # cube_object_idx = self.object_indices[0] (:1308)
+    st["root_state"].view(N, -1, 13)[ids, slot] = initial["root"][i0:i0 + k, slot].clone()
+    initial["idx"] = i0 + k
+
+
+def pre_step(st: Dict[str, Tensor], c: KukaConsts, actions: Tensor, rnd: Tensor, initial: Dict[str, object] = None) -> Dict[str, Tensor]:
     """One ``pre_physics_step``; mutates ``st`` in place and returns the simulator-facing index lists."""
     D, A = c.n_dofs, c.n_arm_dofs
     lo, hi = st["dof_lower"], st["dof_upper"]
@@ -232,6 +249,8 @@ def pre_step(st: Dict[str, Tensor], c: KukaConsts, actions: Tensor, rnd: Tensor)
         st["dof_state"][ids, :D, 1] = vel
         st["prev_targets"][ids, :D] = pos
         st["cur_targets"][ids, :D] = pos
+        if initial is not None:
+            load_initial_states(st, ids, initial)
         root_lists.append(st["object_indices"][ids])
         # episode bookkeeping (:1323-1347)
         st["progress_buf"][ids] = 0

@@ -260,3 +260,37 @@ def test_kuka_fast_rng_statistics():
     task3.seed_rng(124)
     task3.pre_physics_step(act)
     assert not torch.equal(first, task3.goal_states)
+
+
+@pytest.mark.parametrize("layout", ["isaacgym", "soa"])
+def test_kuka_load_initial_states(layout, tmp_path):
+    """``env.loadInitialStates`` (allegro_kuka_base.py:1292-1313, file format :1506-1592): the reset envs take consecutive recorded
+    states in ascending env order after the kernel's re-randomisation; cursor wrap and the too-few-states case as the oracle
+    (pinned to the live reference by tests/test_oracle_vs_reference.py::test_initial_state_loading_matches_reference)."""
+    from handarm_b200 import state_io
+    n, seed, n_states = 513, 21, 60
+    c = ko.KukaConsts()
+    g = torch.Generator().manual_seed(9)
+    root = torch.randn(n_states, 4, 13, generator=g)
+    dof = torch.randn(n_states, c.n_dofs, 2, generator=g)
+    path = str(tmp_path / "states.bin")
+    state_io.append_states(path, [(root[:25], dof[:25]), (root[25:], dof[25:])])
+    task = kh.make_task(n, state_layout=layout, overrides={"env.loadInitialStates": True, "env.loadStatesFile": path})
+    assert task.num_initial_states == n_states
+    st = ks.make_state(n, seed=seed, c=c, fresh=False)
+    kh.load_state(task, st)
+    initial = {"root": root, "dof": dof, "idx": 0}
+    for step in range(4):
+        if step == 2:                                   # more resets than the file holds: nothing is loaded, the cursor stays
+            st["reset_buf"][:] = 1
+            task.reset_buf.fill_(1)
+        act, rnd = ks.make_actions(n, seed + step), ks.make_rnd(n, seed + step)
+        ko.pre_step(st, c, act, rnd, initial=initial)
+        task.ext_rand = rnd.cuda()
+        task.pre_physics_step(act.cuda())
+        got = kh.dump_state(task)
+        for k in ("dof_state", "root_state", "prev_targets", "cur_targets"):
+            assert torch.allclose(got[k].float().reshape(-1), st[k].float().reshape(-1), rtol=RTOL, atol=ATOL), f"step {step} {k}"
+        assert task.initial_state_idx == initial["idx"], f"step {step}: cursor"
+        ko.post_step(st, c)
+        task.post_physics_step()

@@ -56,3 +56,37 @@ def test_reference_quaternion_helpers_match_restatement():
     x = torch.randn(512, 7, generator=g)
     assert torch.equal(tju.unscale(x, lo, hi), ko.unscale(x, lo, hi))
     assert torch.equal(tju.scale(x, lo, hi), ko.scale(x, lo, hi))
+
+
+@pytest.mark.parametrize("n_states", [40, 700, 3])
+def test_initial_state_loading_matches_reference(n_states):
+    """``loadInitialStates`` (allegro_kuka_base.py:1292-1313): consecutive recorded states for the reset envs in ascending order, the
+    cursor wraps when the file runs out, nothing is loaded when one reset needs more states than the file holds."""
+    c = ko.KukaConsts()
+    n, seed = 257, 11
+    st = ks.make_state(n, seed=seed, c=c, fresh=False)
+    st_ref = ks.clone_state(st)
+    g = torch.Generator().manual_seed(5)
+    actors = st["root_state"].shape[0] // n
+    root = torch.randn(n_states, actors, 13, generator=g)
+    dof = torch.randn(n_states, c.n_dofs, 2, generator=g)
+    initial = {"root": root, "dof": dof, "idx": 0}
+    env = rl.make_reference_kuka(st_ref, c)
+    env.should_load_initial_states = True
+    env.initial_root_state_tensors, env.initial_dof_state_tensors = root.clone(), dof.clone()
+    env.num_initial_states, env.initial_state_idx = n_states, 0
+    for step in range(4):
+        if step == 2:                                   # one step in which every env resets: more resets than a small file holds
+            st["reset_buf"][:] = 1
+            st_ref["reset_buf"][:] = 1
+            env.reset_buf = st_ref["reset_buf"]
+        act, rnd = ks.make_actions(n, seed + step), ks.make_rnd(n, seed + step)
+        ko.pre_step(st, c, act, rnd, initial=initial)
+        ko.post_step(st, c)
+        rl.reference_kuka_step(env, c, act, rnd, st_ref)
+        out = rl.harvest(env, st_ref)
+        for k in ("dof_state", "root_state", "prev_targets", "cur_targets", "obs_buf", "reset_buf"):
+            assert torch.equal(st[k].float().reshape(-1), out[k].float().reshape(-1)), f"step {step} {k}"
+        assert initial["idx"] == env.initial_state_idx, f"step {step}: cursor"
+        for k in ("reset_buf", "reset_goal_buf", "random_force_prob"):
+            st_ref[k] = out[k]
