@@ -45,6 +45,12 @@ def reward_operands(want):
             + DISTANCE_DELTA_REW_SCALE * 2.0 * want["closest_fingertip_dist"].abs().float().reshape(len(want["rew_buf"]), -1).sum(dim=1))
 
 
+# How many elements actually NEED the operand-based slack (outside the plain 1e-5 / 2e-6 test, inside the widened one), over the
+# whole module: a real regression must not be able to hide in it, so the share is asserted (last test of the file).
+SLACK_USE = {k: [0, 0] for k in REWARD_KEYS}          # key -> [elements that needed the slack, elements compared]
+SLACK_MAX_SHARE = 1e-4                                # measured: 2e-5 (rew_buf), 3e-6 (the sums)
+
+
 def assert_state_close(got, want, keys_exact=EXACT, keys_float=FLOAT, ctx=""):
     for k in keys_exact:
         assert torch.equal(got[k].long(), want[k].long()), f"{ctx}{k}: {(got[k].long() != want[k].long()).sum()} mismatches"
@@ -57,7 +63,10 @@ def assert_state_close(got, want, keys_exact=EXACT, keys_float=FLOAT, ctx=""):
             slack = operand[None, :].expand(g.numel() // n, n).reshape(-1)
             if k != "rew_buf":
                 slack = slack + w.abs()         # running per-episode sums: held + term
-            bad &= (g - w).abs() > ATOL + RTOL * slack
+            strict_bad = bad
+            bad = bad & ((g - w).abs() > ATOL + RTOL * slack)
+            SLACK_USE[k][0] += int((strict_bad & ~bad).sum())
+            SLACK_USE[k][1] += g.numel()
         assert not bad.any(), f"{ctx}{k}: {int(bad.sum())} of {g.numel()} beyond tolerance, worst |d|={(g - w).abs().max():.3e}"
 
 
@@ -294,3 +303,15 @@ def test_kuka_load_initial_states(layout, tmp_path):
         assert task.initial_state_idx == initial["idx"], f"step {step}: cursor"
         ko.post_step(st, c)
         task.post_physics_step()
+
+
+def test_zz_share_of_elements_that_need_the_operand_slack():
+    """Collected last in this file: over every comparison the module made, the share of reward-type elements that passed only
+    because of the operand-based tolerance ('keep a count ... assert it stays a tiny fraction')."""
+    compared = sum(v[1] for v in SLACK_USE.values())
+    if compared == 0:
+        pytest.skip("no reward comparisons ran in this session (test selected alone)")
+    for k, (used, total) in SLACK_USE.items():
+        share = used / max(total, 1)
+        print(f"{k}: {used} of {total} elements needed the slack ({100 * share:.4f} %)")
+        assert share <= SLACK_MAX_SHARE, f"{k}: {100 * share:.3f} % of the elements pass only with the operand slack"
