@@ -57,7 +57,6 @@ __device__ __forceinline__ float force_prob_from(const HaKukaParams& p, float u)
 
 struct KukaPreSmem {
   float2 lim[24];                  // (lower, upper) limit per DOF
-  float dflt[24], noise[24];
   long long fold[kThreads / 32];   // statistics fold of the CTAs below kNPart (kuka_fold_*)
 };
 
@@ -150,7 +149,9 @@ __device__ __forceinline__ void kuka_reset_env(const HaKukaParams& p, const HaKu
   if (lane < D) {
     const int d = lane;
     const size_t idx = (size_t)env * D + d;
-    const float lo = s.lim[d].x, hi = s.lim[d].y, dflt = s.dflt[d], noise = s.noise[d];
+    // (default position and noise coefficient: read here, not staged with the limits -- only this path needs them, and every
+    // parameter line a kernel touches in its prologue is a constant-cache miss in EVERY tile)
+    const float lo = s.lim[d].x, hi = s.lim[d].y, dflt = p.dof_default[d], noise = p.dof_reset_noise[d];
     const float delta_max = hi - dflt, delta_min = lo - dflt;
     const float rand_delta = delta_min + (delta_max - delta_min) * u.x;
     const float pos = dflt + noise * rand_delta;
@@ -290,7 +291,6 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
   }
   if (tid < D) {
     s.lim[tid] = make_float2(p.dof_lower[tid], p.dof_upper[tid]);
-    s.dflt[tid] = p.dof_default[tid]; s.noise[tid] = p.dof_reset_noise[tid];
   }
   HA_TRACE_POINT(0, 1);                                 // loads issued
   const bool rst = raw_rst != 0, grst = raw_goal != 0;
