@@ -243,6 +243,9 @@ def build_blocks(args, device, layout):
     from handarm_b200.tasks.allegro_kuka import AllegroKukaReorientation
     rank = int(os.environ.get("RANK", "0"))
     tasks, actions = [], []
+    pad_kb = int(os.environ.get("HA_BENCH_PAD_KB", "0"))      # diagnostic: shifts every later allocation (the two timing states)
+    if pad_kb:
+        build_blocks.pad = torch.empty(pad_kb * 1024, dtype=torch.uint8, device=device)
     for b in range(args.blocks):
         cfg = hcfg.load_task_config("AllegroKuka", num_envs=args.envs, sim_device=device)
         sim = SyntheticSim(args.envs, KUKA_LAYOUT, device, seed=1234 + 100 * rank + b, snapshots=args.snapshots, state_layout=layout)
