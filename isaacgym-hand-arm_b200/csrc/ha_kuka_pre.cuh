@@ -428,16 +428,12 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     }
   }
 
-  // The same pass by warps 1..3 only (a tile with ONE reset env: warp 0 carries that env's chain and nothing else): 96 threads x 2
-  // vectors cover the 184 of a tile; the vectors come back from L1 / L2 under the new thread mapping.
-  auto element_pass_by3 = [&](const unsigned skip) {
-    constexpr int kT3 = kThreads - 32;
-    static_assert(2 * kT3 >= kVecPerTile, "two vectors per thread must cover the tile");
-    const int t3 = tid - 32;
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int q = t3 + i * kT3;
-      if (q >= nvec) continue;
+  // The same pass by the warps that carry no reset env (a tile with one, two or three of them: envs of rank 0, 1, 2 go to warps 0, 2,
+  // 3, so warps {1, 2, 3}, {1, 3} or {1} are free): `n_free` warps x 32 lanes stride the 184 vectors of the tile, which come back
+  // from L1 / L2 under the new thread mapping.  The launch ends with its slowest tile, and that is one with several resets.
+  auto element_pass_free = [&](const unsigned skip, const int free_idx, const int n_free) {
+    const int t = free_idx * 32 + lane, step = 32 * n_free;
+    for (int q = t; q < nvec; q += step) {
       const float4 av = __ldg(reinterpret_cast<const float4*>(actions + base) + q);
       const float4 pv = *(reinterpret_cast<const float4*>(b.prev_targets + base) + q);
       const int f0 = 4 * q;
@@ -460,7 +456,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
       }
       if (copy_actions) *(reinterpret_cast<float4*>(b.actions + base) + q) = av;
     }
-    const int f = (nvec << 2) + t3;                      // ragged last tile: up to 3 trailing elements
+    const int f = (nvec << 2) + t;                       // ragged last tile: up to 3 trailing elements
     if (f < total) {
       const int e = f / D, d = f - e * D;
       const float av = __ldg(actions + base + f);
@@ -496,8 +492,13 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
     }
     HA_TRACE_POINT(0, 10);                              // warp 0: its envs are done
     if (!reset_only) {
-      if ((m_any & (m_any - 1u)) != 0u) element_pass(m_rst);          // several envs: every warp keeps its share
-      else if (warp != 0) element_pass_by3(m_rst);                     // one env (warp 0's): the other three warps take the whole pass
+      const int n_env = __popc(m_any);
+      if (n_env > 3) element_pass(m_rst);                              // every warp carries an env: every warp keeps its share
+      else {
+        // busy warps: 0 | 0, 2 | 0, 2, 3  ->  free warps: 1, 2, 3 | 1, 3 | 1
+        const int free_idx = n_env == 1 ? warp - 1 : (n_env == 2 ? (warp == 1 ? 0 : (warp == 3 ? 1 : -1)) : (warp == 1 ? 0 : -1));
+        if (free_idx >= 0) element_pass_free(m_rst, free_idx, 4 - n_env);
+      }
     }
     HA_TRACE_POINT(0, 6);                               // element pass stored
     // what stays per tile (lane = env): accumulators, episode bookkeeping, actor-row lists
@@ -535,7 +536,7 @@ kuka_pre_kernel(const __grid_constant__ HaKukaParams p, const __grid_constant__ 
 
   HA_TRACE_POINT(0, 9);
 #ifdef HA_TRACE
-  if (tid == 0 && blockIdx.x < kTraceMaxCtas) g_ha_trace[0][blockIdx.x].c[13] = m_any ? (m_rst ? 2 : 1) : 0;
+  if (tid == 0 && blockIdx.x < kTraceMaxCtas) g_ha_trace[0][blockIdx.x].c[13] = (m_any ? (m_rst ? 2 : 1) : 0) + 16 * __popc(m_any);   // kind + 16 x number of envs with a reset
 #endif
   HA_TRACE_END(0);
 }

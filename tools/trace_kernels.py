@@ -90,8 +90,9 @@ for k, label in ((0, "kuka_pre_kernel"), (1, "kuka_post_kernel")):
     print(f"   CTA lifetime (globaltimer) [us]    : {pct((r['gt1'] - r['gt0']) / 1e3)}")
     cats = [("all", np.ones(len(r), bool))]
     if k == 0:
-        kind = r["c"][:, 13]
-        cats += [("no reset", kind == 0), ("goal reset only", kind == 1), ("full reset", kind == 2)]
+        kind, n_reset = r["c"][:, 13] % 16, r["c"][:, 13] // 16
+        cats += [("no reset", kind == 0), ("goal reset only", kind == 1), ("full reset", kind == 2),
+                 ("1 env with a reset", n_reset == 1), ("2 envs", n_reset == 2), ("3+ envs", n_reset >= 3)]
     else:
         ntile = np.where(r["c"][:, 10] > 0, 2, 1)
         cats += [("1 tile", ntile == 1), ("2+ tiles", ntile == 2)]
